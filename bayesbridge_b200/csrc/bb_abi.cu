@@ -1,0 +1,810 @@
+// bb_abi.cu -- host side of libbayesbridge_b200.so: device buffers, kernel dispatch, the
+// BridgeRegression-shaped sampler objects and the extern "C" boundary (include/bayesbridge_b200.h).
+//
+// Reference interfaces replaced (paths under /root/reference/Code/C/):
+//   BridgeWrapper.h:164-226 / BridgeWrapper.cpp:572-732  -> bridge_regression, bridge_reg_stable
+//   BridgeWrapper.cpp:80-537 (the four Gibbs drivers)     -> run_driver()
+//   BridgeRegression.h:81-166 (class BridgeRegression)    -> struct bb_model + struct bb_chains
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <string>
+#include <vector>
+
+#include "../../include/bayesbridge_b200.h"
+#include "bb_common.cuh"
+#include "bb_pre.cuh"
+#include "bb_stb.cuh"
+#include "bb_tri.cuh"
+#include "bb_ortho.cuh"
+#include "bb_stb_large.cuh"
+
+namespace {
+
+thread_local std::string g_err;
+long long g_launches = 0;
+unsigned long long g_seed = 20121027ULL;
+int g_device = 0;
+int g_verbose = 0;
+
+void set_err(const std::string& s) { g_err = s; }
+
+template <typename T>
+T* dalloc(size_t n) {
+  T* p = nullptr;
+  BB_CUDA_CHECK(cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)));
+  return p;
+}
+template <typename T>
+void dfree(T*& p) { if (p) cudaFree((void*)p); p = nullptr; }
+
+inline void launched(int n = 1) { g_launches += n; }
+inline void check_launch() { BB_CUDA_CHECK(cudaGetLastError()); }
+
+}  // namespace
+
+// ===========================================================================================
+// bb_model : chain-independent factors (BridgeRegression.cpp:13-69)
+// ===========================================================================================
+struct bb_model {
+  int device = 0, N = 0, P = 0, ldv = 0;
+  bool own_X = false;
+  double *X = nullptr, *y = nullptr;   // may be null (Gram-only construction)
+  double *XX = nullptr, *Xy = nullptr, *bhat = nullptr, *tV = nullptr, *Vc = nullptr, *Wc = nullptr;
+  double *d = nullptr, *a = nullptr, *mean = nullptr, *zc = nullptr, *d2 = nullptr, *gc = nullptr, *bc = nullptr, *bz = nullptr;
+  double r0z = 0, r0b = 0, yy = 0;
+  bool singular = false;
+  double precompute_ms = 0;
+  cudaStream_t stream = nullptr;
+
+  bb::DeviceModel view() const {
+    bb::DeviceModel m;
+    m.N = N; m.P = P; m.ldv = ldv; m.X = X; m.y = y; m.XX = XX; m.Xy = Xy; m.bhat = bhat; m.tV = tV; m.Vc = Vc; m.Wc = Wc;
+    m.d = d; m.mean = mean; m.zc = zc; m.d2 = d2; m.gc = gc; m.bc = bc; m.r0z = r0z; m.r0b = r0b; m.yy = yy;
+    return m;
+  }
+  ~bb_model() {
+    cudaSetDevice(device);
+    if (own_X) { dfree(X); dfree(y); }
+    dfree(XX); dfree(Xy); dfree(bhat); dfree(tV); dfree(Vc); dfree(Wc); dfree(d); dfree(a); dfree(mean); dfree(zc); dfree(d2);
+    dfree(gc); dfree(bc); dfree(bz);
+    if (stream) cudaStreamDestroy(stream);
+  }
+};
+
+namespace {
+
+void model_alloc(bb_model* m) {
+  const size_t P = m->P;
+  m->ldv = (int)((P + 31) / 32 * 32);
+  m->XX = dalloc<double>(P * P); m->Xy = dalloc<double>(P); m->bhat = dalloc<double>(P);
+  m->tV = dalloc<double>(P * P); m->Vc = dalloc<double>(P * m->ldv); m->Wc = dalloc<double>(P * m->ldv);
+  m->d = dalloc<double>(P); m->a = dalloc<double>(P); m->mean = dalloc<double>(P); m->zc = dalloc<double>(P); m->d2 = dalloc<double>(P);
+  m->gc = dalloc<double>(P); m->bc = dalloc<double>(P); m->bz = dalloc<double>(P);
+}
+
+// G = [X y]'[X y] on the FP64 tensor cores.  X, y device pointers.
+void gram_device(const double* X, const double* y, int N, int P, double* G, cudaStream_t st) {
+  const int PA = P + 1;
+  const int nt = (PA + bb::GR_T - 1) / bb::GR_T;
+  const int ntile = nt * (nt + 1) / 2;
+  // split K so that the grid covers the 148 SMs a few times over
+  int nsplit = std::max(1, std::min((N + 4 * bb::GR_K - 1) / (4 * bb::GR_K), (148 * 4 + ntile - 1) / ntile));
+  int rows = (N + nsplit - 1) / nsplit;
+  rows = (rows + bb::GR_K - 1) / bb::GR_K * bb::GR_K;
+  nsplit = (N + rows - 1) / rows;
+  if (nsplit < 1) nsplit = 1;
+  double* part = dalloc<double>((size_t)nsplit * ntile * bb::GR_T * bb::GR_T);
+  bb::gram_kernel<<<dim3(ntile, 1, nsplit), 256, 0, st>>>(X, y, N, P, rows, part);
+  check_launch();
+  bb::gram_reduce_kernel<<<296, 256, 0, st>>>(part, P, nsplit, G);
+  check_launch();
+  launched(2);
+  BB_CUDA_CHECK(cudaStreamSynchronize(st));
+  dfree(part);
+}
+
+// round-robin tournament schedule: n even, n-1 rounds of n/2 pairs
+std::vector<int> tournament(int P, int& rounds, int& npairs) {
+  const int n = P + (P & 1);
+  rounds = n - 1; npairs = n / 2;
+  std::vector<int> out((size_t)rounds * npairs * 2);
+  std::vector<int> ring(n);
+  for (int i = 0; i < n; ++i) ring[i] = i;
+  for (int r = 0; r < rounds; ++r) {
+    for (int k = 0; k < npairs; ++k) {
+      int p = ring[k], q = ring[n - 1 - k];
+      if (p > q) std::swap(p, q);
+      if (q >= P) { p = -1; q = -1; }   // padding column
+      out[((size_t)r * npairs + k) * 2] = p; out[((size_t)r * npairs + k) * 2 + 1] = q;
+    }
+    // rotate all but the first
+    int last = ring[n - 1];
+    for (int i = n - 1; i > 1; --i) ring[i] = ring[i - 1];
+    ring[1] = last;
+  }
+  return out;
+}
+
+// One-sided Jacobi on W (M x P, destroyed): on return W = W0 V, V orthogonal, columns of W orthogonal.
+void jacobi_device(double* W, double* V, int M, int P, cudaStream_t st) {
+  int rounds, npairs;
+  std::vector<int> sched = tournament(P, rounds, npairs);
+  int* d_sched = dalloc<int>(sched.size());
+  BB_CUDA_CHECK(cudaMemcpyAsync(d_sched, sched.data(), sched.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+  unsigned long long* d_conv = dalloc<unsigned long long>(1);
+  bb::set_identity_kernel<<<296, 256, 0, st>>>(V, P); check_launch(); launched();
+  for (int sweep = 0; sweep < 40 && P > 1; ++sweep) {
+    BB_CUDA_CHECK(cudaMemsetAsync(d_conv, 0, sizeof(unsigned long long), st));
+    for (int r = 0; r < rounds; ++r) {
+      bb::jacobi_round_kernel<<<npairs, 256, 0, st>>>(W, V, M, P, d_sched + (size_t)r * npairs * 2, d_conv);
+    }
+    check_launch(); launched(rounds);
+    unsigned long long conv = 0;
+    BB_CUDA_CHECK(cudaMemcpyAsync(&conv, d_conv, sizeof(conv), cudaMemcpyDeviceToHost, st));
+    BB_CUDA_CHECK(cudaStreamSynchronize(st));
+    if (conv == 0) break;   // no pair needed a rotation in this sweep
+  }
+  dfree(d_sched); dfree(d_conv);
+}
+
+double resid_device(const double* X, const double* y, const double* b, int N, int P, cudaStream_t st) {
+  const int nb = std::max(1, std::min(592, (N + 255) / 256));
+  double* part = dalloc<double>(nb);
+  bb::resid_kernel<<<nb, 256, 0, st>>>(X, y, b, N, P, part); check_launch(); launched();
+  std::vector<double> h(nb);
+  BB_CUDA_CHECK(cudaMemcpyAsync(h.data(), part, nb * sizeof(double), cudaMemcpyDeviceToHost, st));
+  BB_CUDA_CHECK(cudaStreamSynchronize(st));
+  dfree(part);
+  double s = 0; for (double v : h) s += v;
+  return s;
+}
+
+// After tV/Vc/Wc/d/a/mean/zc/d2, XX, Xy, bhat are in place: expansion centres and residuals.
+void model_finish(bb_model* m, bool have_rows) {
+  const int P = m->P; cudaStream_t st = m->stream;
+  // z-space centre zc -> beta-space bz = V zc
+  bb::vz_kernel<<<(P + 127) / 128, 128, 0, st>>>(m->Vc, m->zc, P, m->ldv, m->bz); check_launch(); launched();
+  // beta-space centre for the stable path: bhat (0 if singular)
+  BB_CUDA_CHECK(cudaMemcpyAsync(m->bc, m->bhat, P * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  bb::grad_kernel<<<(P + 127) / 128, 128, 0, st>>>(m->XX, m->Xy, m->bc, P, m->gc); check_launch(); launched();
+  if (have_rows) {
+    m->r0z = resid_device(m->X, m->y, m->bz, m->N, P, st);
+    m->r0b = resid_device(m->X, m->y, m->bc, m->N, P, st);
+  }
+}
+
+// singular values / vectors from the Jacobi result; sorts descending; fills every derived array.
+void model_factor(bb_model* m, double* W, int M, bool w_is_gram) {
+  const int P = m->P; cudaStream_t st = m->stream;
+  double* V = dalloc<double>((size_t)P * P);
+  jacobi_device(W, V, M, P, st);
+  double* nrm = dalloc<double>(P);
+  bb::colnorm_kernel<<<P, 128, 0, st>>>(W, M, P, nrm); check_launch(); launched();
+  std::vector<double> h(P);
+  BB_CUDA_CHECK(cudaMemcpyAsync(h.data(), nrm, P * sizeof(double), cudaMemcpyDeviceToHost, st));
+  BB_CUDA_CHECK(cudaStreamSynchronize(st));
+  // W = X V   : column norm = d_i ;   W = (X'X) V : column norm = d_i^2
+  double dmax = 0;
+  for (int i = 0; i < P; ++i) { if (w_is_gram) h[i] = std::sqrt(h[i]); dmax = std::max(dmax, h[i]); }
+  const int rank_cap = std::min(m->N, P);
+  std::vector<int> perm(P);
+  for (int i = 0; i < P; ++i) perm[i] = i;
+  std::stable_sort(perm.begin(), perm.end(), [&](int x, int y) { return h[x] > h[y]; });
+  // numerically zero directions are exactly zero (the reference takes the flat branch when d <= 1e-16, :272-281)
+  const double tol = w_is_gram ? 1e-7 * dmax : 1e-13 * dmax;
+  double dmin = dmax;
+  for (int i = 0; i < P; ++i) { if (i >= rank_cap || h[perm[i]] <= tol) h[perm[i]] = 0.0; dmin = std::min(dmin, h[perm[i]]); }
+  m->singular = !(dmin > 0.0);
+  int* d_perm = dalloc<int>(P);
+  BB_CUDA_CHECK(cudaMemcpyAsync(d_perm, perm.data(), P * sizeof(int), cudaMemcpyHostToDevice, st));
+  BB_CUDA_CHECK(cudaMemcpyAsync(nrm, h.data(), P * sizeof(double), cudaMemcpyHostToDevice, st));
+  bb::derive_kernel<<<P, 128, 0, st>>>(V, d_perm, nrm, m->Xy, P, m->ldv, m->tV, m->Vc, m->Wc, m->d, m->a, m->mean, m->d2, m->zc);
+  check_launch(); launched();
+  // least squares start: V (a / d^2), or 0 when X'X is singular (BridgeRegression.cpp:79-91)
+  if (m->singular) BB_CUDA_CHECK(cudaMemsetAsync(m->bhat, 0, P * sizeof(double), st));
+  else { bb::vz_kernel<<<(P + 127) / 128, 128, 0, st>>>(m->Vc, m->zc, P, m->ldv, m->bhat); check_launch(); launched(); }
+  BB_CUDA_CHECK(cudaStreamSynchronize(st));
+  dfree(V); dfree(nrm); dfree(d_perm);
+}
+
+bb_model* model_new(int N, int P, int device) {
+  if (N < 1 || P < 1) { set_err("bb_model: N and P must be positive"); return nullptr; }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { set_err("bb_model: no CUDA device (there is no CPU fallback)"); return nullptr; }
+  if (device < 0 || device >= ndev) { set_err("bb_model: bad device index"); return nullptr; }
+  BB_CUDA_CHECK(cudaSetDevice(device));
+  bb_model* m = new bb_model();
+  m->device = device; m->N = N; m->P = P;
+  BB_CUDA_CHECK(cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking));
+  model_alloc(m);
+  return m;
+}
+
+void model_take_rows(bb_model* m, const double* X, const double* y, int mem) {
+  const size_t N = m->N, P = m->P;
+  if (mem == BB_MEM_DEVICE) { m->X = const_cast<double*>(X); m->y = const_cast<double*>(y); m->own_X = false; return; }
+  m->X = dalloc<double>(N * P); m->y = dalloc<double>(N); m->own_X = true;
+  BB_CUDA_CHECK(cudaMemcpyAsync(m->X, X, N * P * sizeof(double), cudaMemcpyHostToDevice, m->stream));
+  BB_CUDA_CHECK(cudaMemcpyAsync(m->y, y, N * sizeof(double), cudaMemcpyHostToDevice, m->stream));
+}
+
+void model_gram(bb_model* m) {
+  const int P = m->P;
+  double* G = dalloc<double>((size_t)(P + 1) * (P + 1));
+  gram_device(m->X, m->y, m->N, P, G, m->stream);
+  double* d_yy = dalloc<double>(1);
+  bb::gram_unpack_kernel<<<296, 256, 0, m->stream>>>(G, P, m->XX, m->Xy, d_yy); check_launch(); launched();
+  BB_CUDA_CHECK(cudaMemcpyAsync(&m->yy, d_yy, sizeof(double), cudaMemcpyDeviceToHost, m->stream));
+  BB_CUDA_CHECK(cudaStreamSynchronize(m->stream));
+  dfree(G); dfree(d_yy);
+}
+
+}  // namespace
+
+// ===========================================================================================
+// bb_chains : per-chain state in HBM + the draw buffer
+// ===========================================================================================
+struct bb_chains {
+  const bb_model* m = nullptr;
+  int method = BB_TRI, ortho = 0, nchains = 0;
+  unsigned long long seed = 0;
+  unsigned int chain0 = 0;
+  bool z_valid = false;
+  double *beta = nullptr, *u = nullptr, *aux = nullptr, *shape = nullptr, *z = nullptr;
+  double *sig2 = nullptr, *tau = nullptr, *alpha = nullptr;
+  uint32_t* status = nullptr;
+  double *A = nullptr, *sdel = nullptr;     // large-P stable workspace
+  // draw buffer
+  long long nslots = 0; int out_mask = 0;
+  double *o_beta = nullptr, *o_u = nullptr, *o_omega = nullptr, *o_shape = nullptr, *o_lambda = nullptr;
+  double *o_sig2 = nullptr, *o_tau = nullptr, *o_alpha = nullptr;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+
+  void free_draws() { dfree(o_beta); dfree(o_u); dfree(o_omega); dfree(o_shape); dfree(o_lambda); dfree(o_sig2); dfree(o_tau); dfree(o_alpha); nslots = 0; out_mask = 0; }
+  ~bb_chains() {
+    cudaSetDevice(m->device);
+    dfree(beta); dfree(u); dfree(aux); dfree(shape); dfree(z); dfree(sig2); dfree(tau); dfree(alpha); dfree(status); dfree(A); dfree(sdel);
+    free_draws();
+    if (ev0) cudaEventDestroy(ev0);
+    if (ev1) cudaEventDestroy(ev1);
+    if (stream) cudaStreamDestroy(stream);
+  }
+};
+
+namespace {
+
+bb::Hyper to_hyper(const bb_hyper* h) {
+  bb::Hyper o;
+  o.sig2_shape = h->sig2_shape; o.sig2_scale = h->sig2_scale; o.nu_shape = h->nu_shape; o.nu_rate = h->nu_rate;
+  o.alpha_a = h->alpha_a; o.alpha_b = h->alpha_b; o.true_sig2 = h->true_sig2; o.true_tau = h->true_tau; o.true_alpha = h->true_alpha;
+  o.betaburn = h->betaburn;
+  return o;
+}
+
+bb::DrawSink make_sink(const bb_chains* c, int thin, long long slot0) {
+  bb::DrawSink s;
+  s.beta = c->o_beta; s.u = c->o_u; s.omega = c->o_omega; s.shape = c->o_shape; s.lambda = c->o_lambda;
+  s.sig2 = c->o_sig2; s.tau = c->o_tau; s.alpha = c->o_alpha;
+  s.chain_stride = c->nslots; s.s0 = slot0; s.thin = (c->nslots > 0) ? thin : 0; s.sum = nullptr; s.sumsq = nullptr;
+  return s;
+}
+
+__global__ void fill_kernel(double* p, size_t n, double v) {
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x) p[e] = v;
+}
+__global__ void bcast_rows_kernel(double* dst, const double* src, int P, int nchains) {
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < (size_t)P * nchains; e += (size_t)gridDim.x * blockDim.x) dst[e] = src[e % P];
+}
+// copy the current state of every chain into slot `slot` of the draw buffer
+__global__ void store_state_kernel(const double* src, double* dst, int width, long long stride, long long slot, int nchains) {
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < (size_t)width * nchains; e += (size_t)gridDim.x * blockDim.x) {
+    const size_t c = e / width, j = e % width;
+    dst[(c * stride + slot) * width + j] = src[e];
+  }
+}
+// gather a slot range of the draw buffer into a dense [chain][nslots][width] array
+__global__ void gather_kernel(const double* src, double* dst, int width, long long stride, long long slot0, long long ns, int nchains) {
+  const size_t per = (size_t)ns * width;
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < per * nchains; e += (size_t)gridDim.x * blockDim.x) {
+    const size_t c = e / per, r = e % per;
+    dst[e] = src[(c * stride + slot0) * width + r];
+  }
+}
+
+void fill(double* p, size_t n, double v, cudaStream_t st) { fill_kernel<<<296, 256, 0, st>>>(p, n, v); check_launch(); launched(); }
+
+// ---------------- triangle launch: pick J (coordinates per lane) and C (chains per CTA) ----------------
+template <int J, int C>
+void launch_tri_jc(const bb::TriLaunch& L, int W, cudaStream_t st) {
+  const int threads = 32 * (W + C);
+  const size_t smem = ((size_t)2 * C * L.m.P + 2 * C * 32 + 4 * C) * sizeof(double);
+  const int grid = (L.nchains + C - 1) / C;
+  if (threads <= 384) {
+    auto kern = bb::tri_sweep_kernel<J, C, 384>;
+    BB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<grid, threads, smem, st>>>(L);
+  } else {
+    auto kern = bb::tri_sweep_kernel<J, C, 1024>;
+    BB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<grid, threads, smem, st>>>(L);
+  }
+  check_launch(); launched();
+}
+template <int J>
+void launch_tri_j(const bb::TriLaunch& L, int W, int C, cudaStream_t st) {
+  if (C >= 4) launch_tri_jc<J, 4>(L, W, st);
+  else if (C >= 2) launch_tri_jc<J, 2>(L, W, st);
+  else launch_tri_jc<J, 1>(L, W, st);
+}
+void launch_tri(const bb::TriLaunch& L, cudaStream_t st) {
+  const int P = L.m.P;
+  if (P > 8 * 32 * 24) throw std::string("tri: P too large for the on-chip sweep (max 6144)");
+  // compute warps W and coordinates per lane J with 32*W*J >= P
+  int W = std::min(8, (P + 31) / 32);
+  int J = (P + 32 * W - 1) / (32 * W);
+  while (J > 8) { W += 4; J = (P + 32 * W - 1) / (32 * W); }
+  const int Jt = J <= 1 ? 1 : J <= 2 ? 2 : J <= 4 ? 4 : 8;
+  // chains per CTA: fill the 148 SMs first, then stack chains (they share each column of V in registers)
+  int C = 1;
+  if (L.nchains > 148) C = 2;
+  if (L.nchains > 2 * 148) C = 4;
+  if (Jt == 8 && C > 2) C = 2;   // register budget
+  switch (Jt) {
+    case 1: launch_tri_j<1>(L, W, C, st); break;
+    case 2: launch_tri_j<2>(L, W, C, st); break;
+    case 4: launch_tri_j<4>(L, W, C, st); break;
+    default: launch_tri_j<8>(L, W, C, st); break;
+  }
+}
+
+template <int TB>
+void launch_stb_small(const bb::StbLaunch& L, cudaStream_t st) {
+  constexpr int PP = bb::STB_NB * TB;
+  const size_t smem = ((size_t)PP * PP + 2 * (PP + TB) + 4 * PP + 24 + 2) * sizeof(double) + (size_t)(2 * PP + 2 + PP) * sizeof(int);
+  auto kern = bb::stb_small_kernel<TB>;
+  BB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<L.nchains, bb::STB_THREADS, smem, st>>>(L);
+  check_launch(); launched();
+}
+
+}  // namespace
+
+// ===========================================================================================
+// run: advance all chains (the body of the four Gibbs drivers, BridgeWrapper.cpp:80-537)
+// ===========================================================================================
+namespace {
+
+void chains_run(bb_chains* c, const bb_hyper* hh, unsigned iter0, int niter, int stages, int pre_tau, int pre_sig2,
+                int thin, long long slot0, double* kernel_ms) {
+  const bb_model* m = c->m;
+  BB_CUDA_CHECK(cudaSetDevice(m->device));
+  if (!(hh->true_alpha > 0)) throw std::string("alpha must be fixed (> 0); the alpha Metropolis step is not on the device path yet");
+  const bb::Hyper h = to_hyper(hh);
+  const bb::RngKey key{(uint32_t)c->seed, (uint32_t)(c->seed >> 32)};
+  cudaStream_t st = c->stream;
+  if (c->nslots > 0 && thin > 0) {
+    const long long last = slot0 + niter / thin - 1;
+    if (slot0 < 0 || last >= c->nslots) throw std::string("bb_chains_run: draw buffer too small for slot0 + niter/thin");
+  }
+  BB_CUDA_CHECK(cudaEventRecord(c->ev0, st));
+  const int P = m->P;
+  if (c->ortho) {
+    bb::OrthoLaunch L;
+    L.m = m->view(); L.h = h; L.key = key; L.nchains = c->nchains; L.chain0 = c->chain0; L.iter0 = iter0; L.niter = niter;
+    L.pre_tau = pre_tau; L.pre_sig2 = pre_sig2; L.stages = stages;
+    L.beta = c->beta; L.u = c->u; L.aux = c->aux; L.shape = c->shape; L.sig2 = c->sig2; L.tau = c->tau; L.alpha = c->alpha; L.status = c->status;
+    L.sink = make_sink(c, thin, slot0);
+    const size_t smem = ((size_t)4 * P + 24 + 4) * sizeof(double) + ((size_t)3 * P + 2) * sizeof(int);
+    if (c->method == BB_TRI) {
+      BB_CUDA_CHECK(cudaFuncSetAttribute(bb::ortho_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      bb::ortho_kernel<false><<<c->nchains, bb::ORT_T, smem, st>>>(L);
+    } else {
+      BB_CUDA_CHECK(cudaFuncSetAttribute(bb::ortho_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      bb::ortho_kernel<true><<<c->nchains, bb::ORT_T, smem, st>>>(L);
+    }
+    check_launch(); launched();
+  } else if (c->method == BB_TRI) {
+    bb::TriLaunch L;
+    L.m = m->view(); L.h = h; L.key = key; L.nchains = c->nchains; L.chain0 = c->chain0; L.iter0 = iter0; L.niter = niter;
+    L.pre_tau = pre_tau; L.init_z = c->z_valid ? 0 : 1; L.stages = stages;
+    L.beta = c->beta; L.u = c->u; L.omega = c->aux; L.shape = c->shape; L.z = c->z; L.sig2 = c->sig2; L.tau = c->tau; L.alpha = c->alpha;
+    L.status = c->status; L.sink = make_sink(c, thin, slot0);
+    launch_tri(L, st);
+    c->z_valid = (stages & BB_ST_BETA) != 0 || c->z_valid;
+  } else if (P <= 128) {
+    bb::StbLaunch L;
+    L.m = m->view(); L.h = h; L.key = key; L.nchains = c->nchains; L.chain0 = c->chain0; L.iter0 = iter0; L.niter = niter;
+    L.pre_tau = pre_tau; L.stages = stages;
+    L.beta = c->beta; L.lambda = c->aux; L.sig2 = c->sig2; L.tau = c->tau; L.alpha = c->alpha; L.status = c->status;
+    L.sink = make_sink(c, thin, slot0);
+    if (P <= 64) launch_stb_small<4>(L, st); else launch_stb_small<8>(L, st);
+  } else {
+    if (!c->A) { c->A = dalloc<double>((size_t)c->nchains * P * P); c->sdel = dalloc<double>((size_t)c->nchains * P); }
+    bb::StbLargeLaunch L;
+    L.m = m->view(); L.h = h; L.key = key; L.nchains = c->nchains; L.chain0 = c->chain0; L.stages = stages;
+    L.beta = c->beta; L.lambda = c->aux; L.sig2 = c->sig2; L.tau = c->tau; L.alpha = c->alpha; L.status = c->status;
+    L.A = c->A; L.sdel = c->sdel; L.sink = make_sink(c, thin, slot0);
+    const size_t smem_sc = ((size_t)P + 26) * sizeof(double) + ((size_t)3 * P + 2) * sizeof(int);
+    const size_t smem_sv = (size_t)P * sizeof(double);
+    BB_CUDA_CHECK(cudaFuncSetAttribute(bb::stbl_scalar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sc));
+    BB_CUDA_CHECK(cudaFuncSetAttribute(bb::stbl_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));
+    const size_t smem_sy = (size_t)2 * bb::SL_NB * bb::SL_LD * sizeof(double);
+    BB_CUDA_CHECK(cudaFuncSetAttribute(bb::stbl_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
+    const int nblk = (P + bb::SL_NB - 1) / bb::SL_NB;
+    for (int it = -pre_tau; it < niter; ++it) {
+      L.pre = it < 0; L.iter = iter0 + (it < 0 ? 0 : it);
+      const bool store = c->nslots > 0 && thin > 0 && it >= 0 && ((it + 1) % thin) == 0;
+      L.slot = store ? slot0 + (it + 1) / thin - 1 : -1;
+      bb::stbl_scalar_kernel<<<c->nchains, bb::SL_T, smem_sc, st>>>(L); launched();
+      if (L.pre || !(stages & BB_ST_BETA)) continue;
+      bb::stbl_build_kernel<<<dim3(64, c->nchains), 256, 0, st>>>(L); launched();
+      for (int kb = 0; kb < nblk; ++kb) {
+        bb::stbl_potrf_kernel<<<c->nchains, bb::SL_T, 0, st>>>(c->A, P, kb, c->status); launched();
+        const int rem = nblk - kb - 1;
+        if (rem > 0) {
+          bb::stbl_trsm_kernel<<<dim3(rem, c->nchains), bb::SL_NB, 0, st>>>(c->A, P, kb); launched();
+          bb::stbl_syrk_kernel<<<dim3(rem * (rem + 1) / 2, c->nchains), 256, smem_sy, st>>>(c->A, P, kb); launched();
+        }
+      }
+      bb::stbl_solve_kernel<<<c->nchains, bb::SL_T, smem_sv, st>>>(L); launched();
+    }
+    check_launch();
+  }
+  BB_CUDA_CHECK(cudaEventRecord(c->ev1, st));
+  BB_CUDA_CHECK(cudaStreamSynchronize(st));
+  if (kernel_ms) { float ms = 0; BB_CUDA_CHECK(cudaEventElapsedTime(&ms, c->ev0, c->ev1)); *kernel_ms = ms; }
+}
+
+template <typename F>
+int guarded(F&& f) {
+  try { f(); return 0; }
+  catch (const bb::CudaError& e) { set_err(std::string("CUDA error: ") + cudaGetErrorString(e.code)); }
+  catch (const std::string& s) { set_err(s); }
+  catch (const std::exception& e) { set_err(e.what()); }
+  catch (...) { set_err("unknown error"); }
+  return 1;
+}
+
+}  // namespace
+
+// ===========================================================================================
+// extern "C" boundary
+// ===========================================================================================
+extern "C" {
+
+const char* bb_last_error(void) { return g_err.c_str(); }
+int bb_device_count(void) { int n = 0; if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; } return n; }
+long long bb_launch_count(void) { return g_launches; }
+void bb_set_seed(unsigned long long seed) { g_seed = seed; }
+void bb_set_device(int device) { g_device = device; }
+void bb_set_verbose(int v) { g_verbose = v; }
+
+bb_model* bb_model_create(const double* X, const double* y, int N, int P, int device, int mem) {
+  bb_model* m = nullptr;
+  const int rc = guarded([&] {
+    auto t0 = std::chrono::steady_clock::now();
+    m = model_new(N, P, device);
+    if (!m) throw std::string(g_err);
+    model_take_rows(m, X, y, mem);
+    model_gram(m);
+    // SVD factors by one-sided Jacobi: on a copy of X when N >= P (most accurate), else on X'X
+    if (N >= P) {
+      double* W = dalloc<double>((size_t)N * P);
+      BB_CUDA_CHECK(cudaMemcpyAsync(W, m->X, (size_t)N * P * sizeof(double), cudaMemcpyDeviceToDevice, m->stream));
+      model_factor(m, W, N, false);
+      dfree(W);
+    } else {
+      double* W = dalloc<double>((size_t)P * P);
+      BB_CUDA_CHECK(cudaMemcpyAsync(W, m->XX, (size_t)P * P * sizeof(double), cudaMemcpyDeviceToDevice, m->stream));
+      model_factor(m, W, P, true);
+      dfree(W);
+    }
+    model_finish(m, true);
+    BB_CUDA_CHECK(cudaStreamSynchronize(m->stream));
+    m->precompute_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  });
+  if (rc) { delete m; return nullptr; }
+  return m;
+}
+
+bb_model* bb_model_create_factors(const double* X, const double* y, int N, int P, const double* tV, const double* d,
+                                  const double* a, const double* bhat, int device, int mem) {
+  bb_model* m = nullptr;
+  const int rc = guarded([&] {
+    m = model_new(N, P, device);
+    if (!m) throw std::string(g_err);
+    model_take_rows(m, X, y, mem);
+    model_gram(m);
+    cudaStream_t st = m->stream;
+    BB_CUDA_CHECK(cudaMemcpyAsync(m->tV, tV, (size_t)P * P * sizeof(double), cudaMemcpyHostToDevice, st));
+    BB_CUDA_CHECK(cudaMemcpyAsync(m->d, d, P * sizeof(double), cudaMemcpyHostToDevice, st));
+    BB_CUDA_CHECK(cudaMemcpyAsync(m->a, a, P * sizeof(double), cudaMemcpyHostToDevice, st));
+    bb::derive_from_tv_kernel<<<P, 128, 0, st>>>(m->tV, m->d, m->a, P, m->ldv, m->Vc, m->Wc, m->mean, m->d2, m->zc); check_launch(); launched();
+    if (bhat) BB_CUDA_CHECK(cudaMemcpyAsync(m->bhat, bhat, P * sizeof(double), cudaMemcpyHostToDevice, st));
+    else { bb::vz_kernel<<<(P + 127) / 128, 128, 0, st>>>(m->Vc, m->zc, P, m->ldv, m->bhat); check_launch(); launched(); }
+    model_finish(m, true);
+    BB_CUDA_CHECK(cudaStreamSynchronize(st));
+  });
+  if (rc) { delete m; return nullptr; }
+  return m;
+}
+
+int bb_gram(const double* X_dev, const double* y_dev, int n_rows, int P, double* G_dev, int device) {
+  return guarded([&] {
+    BB_CUDA_CHECK(cudaSetDevice(device));
+    gram_device(X_dev, y_dev, n_rows, P, G_dev, nullptr);
+  });
+}
+
+bb_model* bb_model_create_gram(const double* G_dev, int N, int P, int device) {
+  bb_model* m = nullptr;
+  const int rc = guarded([&] {
+    auto t0 = std::chrono::steady_clock::now();
+    m = model_new(N, P, device);
+    if (!m) throw std::string(g_err);
+    double* d_yy = dalloc<double>(1);
+    bb::gram_unpack_kernel<<<296, 256, 0, m->stream>>>(G_dev, P, m->XX, m->Xy, d_yy); check_launch(); launched();
+    BB_CUDA_CHECK(cudaMemcpyAsync(&m->yy, d_yy, sizeof(double), cudaMemcpyDeviceToHost, m->stream));
+    double* W = dalloc<double>((size_t)P * P);
+    BB_CUDA_CHECK(cudaMemcpyAsync(W, m->XX, (size_t)P * P * sizeof(double), cudaMemcpyDeviceToDevice, m->stream));
+    model_factor(m, W, P, true);
+    dfree(W); dfree(d_yy);
+    model_finish(m, false);
+    // without the rows: r0 from the normal equations (replaced by bb_model_set_r0 after the shard all-reduce)
+    BB_CUDA_CHECK(cudaStreamSynchronize(m->stream));
+    m->r0z = std::numeric_limits<double>::quiet_NaN(); m->r0b = m->r0z;
+    m->precompute_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  });
+  if (rc) { delete m; return nullptr; }
+  return m;
+}
+
+int bb_model_resid_partial(const bb_model* m, const double* X_dev, const double* y_dev, int n_rows, double* out_dev) {
+  return guarded([&] {
+    BB_CUDA_CHECK(cudaSetDevice(m->device));
+    const double r[2] = {resid_device(X_dev, y_dev, m->bz, n_rows, m->P, m->stream), resid_device(X_dev, y_dev, m->bc, n_rows, m->P, m->stream)};
+    BB_CUDA_CHECK(cudaMemcpy(out_dev, r, 2 * sizeof(double), cudaMemcpyHostToDevice));
+  });
+}
+int bb_model_set_r0(bb_model* m, double r0z, double r0b) { m->r0z = r0z; m->r0b = r0b; return 0; }
+void bb_model_free(bb_model* m) { delete m; }
+double bb_model_precompute_ms(const bb_model* m) { return m->precompute_ms; }
+
+int bb_model_get(const bb_model* m, double* XX, double* Xy, double* bhat, double* tV, double* d, double* a) {
+  return guarded([&] {
+    BB_CUDA_CHECK(cudaSetDevice(m->device));
+    const size_t P = m->P;
+    if (XX) BB_CUDA_CHECK(cudaMemcpy(XX, m->XX, P * P * sizeof(double), cudaMemcpyDeviceToHost));
+    if (Xy) BB_CUDA_CHECK(cudaMemcpy(Xy, m->Xy, P * sizeof(double), cudaMemcpyDeviceToHost));
+    if (bhat) BB_CUDA_CHECK(cudaMemcpy(bhat, m->bhat, P * sizeof(double), cudaMemcpyDeviceToHost));
+    if (tV) BB_CUDA_CHECK(cudaMemcpy(tV, m->tV, P * P * sizeof(double), cudaMemcpyDeviceToHost));
+    if (d) BB_CUDA_CHECK(cudaMemcpy(d, m->d, P * sizeof(double), cudaMemcpyDeviceToHost));
+    if (a) BB_CUDA_CHECK(cudaMemcpy(a, m->a, P * sizeof(double), cudaMemcpyDeviceToHost));
+  });
+}
+
+bb_chains* bb_chains_create(const bb_model* m, int method, int ortho, int nchains, unsigned long long seed, unsigned int chain0) {
+  bb_chains* c = nullptr;
+  const int rc = guarded([&] {
+    if (!m || nchains < 1) throw std::string("bb_chains_create: bad arguments");
+    BB_CUDA_CHECK(cudaSetDevice(m->device));
+    c = new bb_chains();
+    c->m = m; c->method = method; c->ortho = ortho; c->nchains = nchains; c->seed = seed; c->chain0 = chain0;
+    BB_CUDA_CHECK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    BB_CUDA_CHECK(cudaEventCreate(&c->ev0)); BB_CUDA_CHECK(cudaEventCreate(&c->ev1));
+    const size_t n = (size_t)nchains * m->P;
+    c->beta = dalloc<double>(n); c->u = dalloc<double>(n); c->aux = dalloc<double>(n); c->shape = dalloc<double>(n); c->z = dalloc<double>(n);
+    c->sig2 = dalloc<double>(nchains); c->tau = dalloc<double>(nchains); c->alpha = dalloc<double>(nchains);
+    c->status = dalloc<uint32_t>(nchains);
+    cudaStream_t st = c->stream;
+    // BridgeWrapper.cpp:120-125 / 241-246 and the fills at :603-605, :686
+    bcast_rows_kernel<<<296, 256, 0, st>>>(c->beta, m->bhat, m->P, nchains); check_launch(); launched();
+    fill(c->u, n, 0.5, st); fill(c->aux, n, 1.0, st); fill(c->shape, n, 0.0, st); fill(c->z, n, 0.0, st);
+    fill(c->sig2, nchains, 0.0, st); fill(c->tau, nchains, 0.0, st); fill(c->alpha, nchains, 0.5, st);
+    BB_CUDA_CHECK(cudaMemsetAsync(c->status, 0, nchains * sizeof(uint32_t), st));
+    BB_CUDA_CHECK(cudaStreamSynchronize(st));
+  });
+  if (rc) { delete c; return nullptr; }
+  return c;
+}
+void bb_chains_free(bb_chains* c) { delete c; }
+
+int bb_chains_set(bb_chains* c, const double* beta, const double* u, const double* aux, const double* sig2, const double* tau) {
+  return guarded([&] {
+    BB_CUDA_CHECK(cudaSetDevice(c->m->device));
+    const size_t n = (size_t)c->nchains * c->m->P * sizeof(double), ns = (size_t)c->nchains * sizeof(double);
+    if (beta) { BB_CUDA_CHECK(cudaMemcpy(c->beta, beta, n, cudaMemcpyHostToDevice)); c->z_valid = false; }
+    if (u) BB_CUDA_CHECK(cudaMemcpy(c->u, u, n, cudaMemcpyHostToDevice));
+    if (aux) BB_CUDA_CHECK(cudaMemcpy(c->aux, aux, n, cudaMemcpyHostToDevice));
+    if (sig2) BB_CUDA_CHECK(cudaMemcpy(c->sig2, sig2, ns, cudaMemcpyHostToDevice));
+    if (tau) BB_CUDA_CHECK(cudaMemcpy(c->tau, tau, ns, cudaMemcpyHostToDevice));
+  });
+}
+int bb_chains_get(const bb_chains* c, double* beta, double* u, double* aux, double* shape, double* sig2, double* tau, unsigned int* status) {
+  return guarded([&] {
+    BB_CUDA_CHECK(cudaSetDevice(c->m->device));
+    const size_t n = (size_t)c->nchains * c->m->P * sizeof(double), ns = (size_t)c->nchains * sizeof(double);
+    if (beta) BB_CUDA_CHECK(cudaMemcpy(beta, c->beta, n, cudaMemcpyDeviceToHost));
+    if (u) BB_CUDA_CHECK(cudaMemcpy(u, c->u, n, cudaMemcpyDeviceToHost));
+    if (aux) BB_CUDA_CHECK(cudaMemcpy(aux, c->aux, n, cudaMemcpyDeviceToHost));
+    if (shape) BB_CUDA_CHECK(cudaMemcpy(shape, c->shape, n, cudaMemcpyDeviceToHost));
+    if (sig2) BB_CUDA_CHECK(cudaMemcpy(sig2, c->sig2, ns, cudaMemcpyDeviceToHost));
+    if (tau) BB_CUDA_CHECK(cudaMemcpy(tau, c->tau, ns, cudaMemcpyDeviceToHost));
+    if (status) BB_CUDA_CHECK(cudaMemcpy(status, c->status, c->nchains * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+  });
+}
+
+int bb_chains_reserve(bb_chains* c, long long nslots, int out_mask) {
+  return guarded([&] {
+    BB_CUDA_CHECK(cudaSetDevice(c->m->device));
+    c->free_draws();
+    if (nslots <= 0) return;
+    const size_t nv = (size_t)c->nchains * nslots * c->m->P, ns = (size_t)c->nchains * nslots;
+    if (out_mask & BB_OUT_BETA) c->o_beta = dalloc<double>(nv);
+    if (out_mask & BB_OUT_U) c->o_u = dalloc<double>(nv);
+    if (out_mask & BB_OUT_OMEGA) c->o_omega = dalloc<double>(nv);
+    if (out_mask & BB_OUT_SHAPE) c->o_shape = dalloc<double>(nv);
+    if (out_mask & BB_OUT_LAMBDA) c->o_lambda = dalloc<double>(nv);
+    if (out_mask & BB_OUT_SIG2) c->o_sig2 = dalloc<double>(ns);
+    if (out_mask & BB_OUT_TAU) c->o_tau = dalloc<double>(ns);
+    if (out_mask & BB_OUT_ALPHA) c->o_alpha = dalloc<double>(ns);
+    c->nslots = nslots; c->out_mask = out_mask;
+  });
+}
+
+int bb_chains_run(bb_chains* c, const bb_hyper* h, unsigned int iter0, int niter, int stages, int pre_tau, int thin,
+                  long long slot0, double* kernel_ms) {
+  return guarded([&] { chains_run(c, h, iter0, niter, stages, pre_tau & 1, (pre_tau >> 1) & 1, thin, slot0, kernel_ms); });
+}
+
+int bb_chains_store_state(bb_chains* c, long long slot) {
+  return guarded([&] {
+    BB_CUDA_CHECK(cudaSetDevice(c->m->device));
+    if (slot < 0 || slot >= c->nslots) throw std::string("bb_chains_store_state: slot out of range");
+    const int P = c->m->P, n = c->nchains; cudaStream_t st = c->stream;
+    auto cp = [&](const double* src, double* dst, int w) {
+      if (dst) { store_state_kernel<<<296, 256, 0, st>>>(src, dst, w, c->nslots, slot, n); check_launch(); launched(); }
+    };
+    cp(c->beta, c->o_beta, P); cp(c->u, c->o_u, P);
+    cp(c->aux, c->method == BB_TRI ? c->o_omega : c->o_lambda, P); cp(c->shape, c->o_shape, P);
+    cp(c->sig2, c->o_sig2, 1); cp(c->tau, c->o_tau, 1); cp(c->alpha, c->o_alpha, 1);
+    BB_CUDA_CHECK(cudaStreamSynchronize(st));
+  });
+}
+
+int bb_chains_fetch(const bb_chains* c, int which, long long slot0, long long nslots, double* out) {
+  return guarded([&] {
+    BB_CUDA_CHECK(cudaSetDevice(c->m->device));
+    const double* src = nullptr; int w = c->m->P;
+    switch (which) {
+      case BB_OUT_BETA: src = c->o_beta; break;
+      case BB_OUT_U: src = c->o_u; break;
+      case BB_OUT_OMEGA: src = c->o_omega; break;
+      case BB_OUT_SHAPE: src = c->o_shape; break;
+      case BB_OUT_LAMBDA: src = c->o_lambda; break;
+      case BB_OUT_SIG2: src = c->o_sig2; w = 1; break;
+      case BB_OUT_TAU: src = c->o_tau; w = 1; break;
+      case BB_OUT_ALPHA: src = c->o_alpha; w = 1; break;
+      default: break;
+    }
+    if (!src) throw std::string("bb_chains_fetch: that output was not reserved");
+    if (slot0 < 0 || slot0 + nslots > c->nslots) throw std::string("bb_chains_fetch: slot range out of bounds");
+    const size_t n = (size_t)c->nchains * nslots * w;
+    if (slot0 == 0 && nslots == c->nslots) { BB_CUDA_CHECK(cudaMemcpy(out, src, n * sizeof(double), cudaMemcpyDeviceToHost)); return; }
+    double* tmp = dalloc<double>(n);
+    gather_kernel<<<296, 256, 0, c->stream>>>(src, tmp, w, c->nslots, slot0, nslots, c->nchains); check_launch(); launched();
+    BB_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    BB_CUDA_CHECK(cudaMemcpy(out, tmp, n * sizeof(double), cudaMemcpyDeviceToHost));
+    dfree(tmp);
+  });
+}
+
+}  // extern "C"
+
+// ===========================================================================================
+// Drivers: the schedule of BridgeWrapper.cpp:80-204 (tri), 207-313 (stb), 320-431, 434-537 (ortho)
+// ===========================================================================================
+namespace {
+
+void nan_fill(double* p, size_t n) { if (p) for (size_t i = 0; i < n; ++i) p[i] = std::numeric_limits<double>::quiet_NaN(); }
+
+void run_driver(int method, int ortho, const double* X, const double* y, int N, int P, const bb_hyper* h,
+                int nchains, unsigned long long seed, unsigned int chain0, int burn, int nsamp, int thin, int device,
+                double* beta, double* aux1, double* aux2, double* aux3, double* sig2, double* tau, double* alpha,
+                unsigned int* status, double* runtime) {
+  if (nsamp < 1 || burn < 0 || nchains < 1) throw std::string("bridge driver: need nsamp >= 1, burn >= 0, nchains >= 1");
+  if (thin < 1) thin = 1;
+  struct Guard { bb_model* m = nullptr; bb_chains* c = nullptr; ~Guard() { delete c; delete m; } } g;
+  g.m = bb_model_create(X, y, N, P, device, BB_MEM_HOST);
+  if (!g.m) throw std::string(g_err);
+  g.c = bb_chains_create(g.m, method, ortho, nchains, seed, chain0);
+  if (!g.c) throw std::string(g_err);
+  int mask = BB_OUT_BETA | BB_OUT_SIG2 | BB_OUT_TAU | BB_OUT_ALPHA;
+  mask |= (method == BB_TRI) ? (BB_OUT_U | BB_OUT_OMEGA | BB_OUT_SHAPE) : BB_OUT_LAMBDA;
+  if (bb_chains_reserve(g.c, nsamp, mask)) throw std::string(g_err);
+  if (g_verbose) {
+    std::printf("Bridge Regression (%s): known alpha=%g", method == BB_TRI ? "mix. of triangles" : "mix. of normals", h->true_alpha);
+    if (h->true_sig2 > 0) std::printf(", sig2=%g", h->true_sig2);
+    if (h->true_tau > 0) std::printf(", tau=%g", h->true_tau);
+    std::printf("\nBurn-in: %i, Num. Samples: %i, Chains: %i\n", burn, nsamp, nchains);
+  }
+  // burn-in, in place (tri: burn iterations, :145 ; stb: burn+1, :266), preceded by the pre-draws
+  const int nburn = method == BB_TRI ? burn : burn + 1;
+  int pre = 0;
+  if (method == BB_TRI) pre = ortho ? 3 : 1;          // :142 / :379-380
+  else pre = ortho ? 0 : 1;                           // :262 / none (:490)
+  chains_run(g.c, h, 0u, nburn, BB_ST_ALL, pre & 1, (pre >> 1) & 1, 0, 0, nullptr);
+  if (bb_chains_store_state(g.c, 0)) throw std::string(g_err);     // sample 0 = state after burn-in
+  auto t0 = std::chrono::steady_clock::now();
+  const long long total = (long long)(nsamp - 1) * thin;
+  long long done = 0;
+  const long long chunk = 8192LL * thin;
+  while (done < total) {
+    const long long n = std::min(chunk, total - done);
+    chains_run(g.c, h, (unsigned)(nburn + done), (int)n, BB_ST_ALL, 0, 0, thin, 1 + done / thin, nullptr);
+    done += n;
+  }
+  const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  if (runtime) *runtime = secs;
+  auto fetch = [&](int which, double* out) { if (out && bb_chains_fetch(g.c, which, 0, nsamp, out)) throw std::string(g_err); };
+  fetch(BB_OUT_BETA, beta);
+  if (method == BB_TRI) { fetch(BB_OUT_U, aux1); fetch(BB_OUT_OMEGA, aux2); fetch(BB_OUT_SHAPE, aux3); }
+  else fetch(BB_OUT_LAMBDA, aux1);
+  fetch(BB_OUT_SIG2, sig2); fetch(BB_OUT_TAU, tau); fetch(BB_OUT_ALPHA, alpha);
+  if (status && bb_chains_get(g.c, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, status)) throw std::string(g_err);
+  if (g_verbose) std::printf("Sampling complete: %g sec. for %i iterations.\n", secs, nsamp);
+}
+
+}  // namespace
+
+extern "C" {
+
+int bb_bridge_batched(int method, int ortho, const double* X, const double* y, int N, int P, const bb_hyper* h,
+                      int nchains, unsigned long long seed, unsigned int chain0, int burn, int nsamp, int thin, int device,
+                      double* beta, double* aux1, double* aux2, double* aux3, double* sig2, double* tau, double* alpha,
+                      unsigned int* status, double* runtime) {
+  return guarded([&] {
+    run_driver(method, ortho, X, y, N, P, h, nchains, seed, chain0, burn, nsamp, thin, device, beta, aux1, aux2, aux3, sig2, tau,
+               alpha, status, runtime);
+  });
+}
+
+void bridge_regression(double* betap, double* up, double* omegap, double* shapep, double* sig2p, double* taup, double* alphap,
+                       const double* yp, const double* Xp, const double* sig2_shape, const double* sig2_scale,
+                       const double* nu_shape, const double* nu_rate, const double* alpha_a, const double* alpha_b,
+                       const double* true_sig2, const double* true_tau, const double* true_alpha, const int* P, const int* N,
+                       const int* M, const int* burn, double* runtime, const int* ortho, const int* betaburn, const int* use_hmc) {
+  (void)use_hmc;   // forced false in the reference (BridgeRegression.cpp:419)
+  bb_hyper h{*sig2_shape, *sig2_scale, *nu_shape, *nu_rate, *alpha_a, *alpha_b, *true_sig2, *true_tau, *true_alpha, *betaburn};
+  const int orth = (*reinterpret_cast<const unsigned char*>(ortho)) != 0;   // R logical: low byte, as the reference reads it
+  const int rc = bb_bridge_batched(BB_TRI, orth, Xp, yp, *N, *P, &h, 1, g_seed, 0u, *burn, *M, 1, g_device, betap, up, omegap, shapep,
+                                   sig2p, taup, alphap, nullptr, runtime);
+  if (rc) {
+    std::fprintf(stderr, "bridge_regression (bayesbridge_b200): %s\nAborting Gibbs sampler.\n", g_err.c_str());
+    const size_t n = (size_t)(*P) * (*M);
+    nan_fill(betap, n); nan_fill(up, n); nan_fill(omegap, n); nan_fill(shapep, n);
+    nan_fill(sig2p, *M); nan_fill(taup, *M); nan_fill(alphap, *M); nan_fill(runtime, 1);
+  }
+}
+
+void bridge_reg_stable(double* betap, double* lambdap, double* sig2p, double* taup, double* alphap, const double* yp,
+                       const double* Xp, const double* sig2_shape, const double* sig2_scale, const double* nu_shape,
+                       const double* nu_rate, const double* alpha_a, const double* alpha_b, const double* true_sig2,
+                       const double* true_tau, const double* true_alpha, const int* P, const int* N, const int* M, const int* burn,
+                       double* runtime, const int* ortho) {
+  bb_hyper h{*sig2_shape, *sig2_scale, *nu_shape, *nu_rate, *alpha_a, *alpha_b, *true_sig2, *true_tau, *true_alpha, 0};
+  const int orth = (*reinterpret_cast<const unsigned char*>(ortho)) != 0;
+  const int rc = bb_bridge_batched(BB_STB, orth, Xp, yp, *N, *P, &h, 1, g_seed, 0u, *burn, *M, 1, g_device, betap, lambdap, nullptr,
+                                   nullptr, sig2p, taup, alphap, nullptr, runtime);
+  if (rc) {
+    std::fprintf(stderr, "bridge_reg_stable (bayesbridge_b200): %s\nAborting Gibbs sampler.\n", g_err.c_str());
+    const size_t n = (size_t)(*P) * (*M);
+    nan_fill(betap, n); nan_fill(lambdap, n); nan_fill(sig2p, *M); nan_fill(taup, *M); nan_fill(alphap, *M); nan_fill(runtime, 1);
+  }
+}
+
+}  // extern "C"

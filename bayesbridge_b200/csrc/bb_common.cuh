@@ -1,0 +1,89 @@
+// bb_common.cuh -- shared device structs and small helpers.
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <cuda_runtime.h>
+#include "bb_rng.cuh"
+
+namespace bb {
+
+#define BB_CUDA_CHECK(expr)                                                                    \
+  do {                                                                                         \
+    cudaError_t _e = (expr);                                                                   \
+    if (_e != cudaSuccess) {                                                                   \
+      std::fprintf(stderr, "bayesbridge_b200: CUDA error %s at %s:%d: %s\n", cudaGetErrorName(_e), \
+                   __FILE__, __LINE__, cudaGetErrorString(_e));                               \
+      throw ::bb::CudaError(_e);                                                               \
+    }                                                                                          \
+  } while (0)
+
+struct CudaError { cudaError_t code; explicit CudaError(cudaError_t c) : code(c) {} };
+
+// Chain-independent factors resident in HBM (the role of the BridgeRegression constructor,
+// /root/reference/Code/C/BridgeRegression.cpp:13-69).  All column-major doubles.
+struct DeviceModel {
+  int N, P;
+  int ldv;             // leading dimension of Vc / Wc (P rounded up to a multiple of 32)
+  const double* X;     // N x P   (may be null when built from a Gram matrix only)
+  const double* y;     // N
+  const double* XX;    // P x P   X'X                         (:24)
+  const double* Xy;    // P       X'y                         (:25)
+  const double* bhat;  // P       least squares, 0 if singular (:41-42,:79-91)
+  const double* tV;    // P x P   tV[i + j*P] = V(j,i)        (:47-51)  (used for z = V'beta)
+  const double* Vc;    // P x ldv Vc[i*ldv + j] = V(j,i), zero padded  (sweep column i is contiguous)
+  const double* Wc;    // P x ldv 1/|V(j,i)|, +inf where V is 0 or padded
+  const double* d;     // P       singular values (0 beyond the rank)
+  const double* mean;  // P       a_i / d_i^2                  (:268)
+  const double* zc;    // P       centre of the rss expansion in z-space (a_i/d_i^2 where d_i>0, else 0)
+  const double* d2;    // P       d_i^2
+  const double* gc;    // P       X'(y - X bc)  for the beta-space rss expansion (stable path)
+  const double* bc;    // P       centre of the beta-space rss expansion (bhat, or 0 when singular)
+  double r0z;          // || y - X V zc ||^2
+  double r0b;          // || y - X bc ||^2
+  double yy;
+};
+
+// Prior / switch block shared by all drivers (BridgeWrapper.cpp:80-109, 207-232).
+struct Hyper {
+  double sig2_shape, sig2_scale, nu_shape, nu_rate, alpha_a, alpha_b;
+  double true_sig2, true_tau, true_alpha;  // > 0 means "known, keep fixed"
+  int betaburn;
+};
+
+// Where one launch writes its draws.  Sample s of chain c, coordinate j goes to
+// ptr[(c * chain_stride + (s0 + s)) * P + j]  (P fastest, like the .C arrays: BridgeWrapper.cpp:602-608).
+struct DrawSink {
+  double* beta; double* u; double* omega; double* shape; double* lambda;  // P-vectors per sample (any may be null)
+  double* sig2; double* tau; double* alpha;                               // scalars per sample
+  long long chain_stride;  // samples reserved per chain
+  long long s0;            // first sample slot written by this launch
+  int thin;                // store every thin-th iteration
+  // running per-coordinate moments over the stored iterations (summary mode): [chain][P] each, may be null
+  double* sum; double* sumsq;
+};
+
+// ---- named barriers (bar.sync / bar.arrive), ids 1..15; id 0 is __syncthreads ----
+__device__ __forceinline__ void bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+__device__ __forceinline__ void bar_arrive(int id, int nthreads) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ double warp_min(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+}  // namespace bb

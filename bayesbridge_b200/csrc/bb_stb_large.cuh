@@ -1,0 +1,294 @@
+// bb_stb_large.cuh -- the stable-mixture sweep when one chain's P x P system does not fit on chip
+// (P > 128): per-chain workspace in HBM, blocked right-looking Cholesky batched over chains with
+// FP64 tensor-core (DMMA) trailing updates.
+//
+//   stbl_scalar_kernel : tau, sig2, lambda            (BridgeRegression.cpp:453-465, 436-450, 506-510)
+//   stbl_build_kernel  : A_c = X'X + diag(lambda sig2/tau^2)          (:554-556)
+//   stbl_potrf_kernel / stbl_trsm_kernel / stbl_syrk_kernel : chol(A_c)   (:559-560)
+//   stbl_solve_kernel  : beta = L^-T (L^-1 Xy + sig eps)              (:563-574)
+#pragma once
+#include "bb_common.cuh"
+#include "bb_pre.cuh"
+#include "bb_retstable.cuh"
+
+namespace bb {
+
+struct StbLargeLaunch {
+  DeviceModel m;
+  Hyper h;
+  RngKey key;
+  int nchains;
+  uint32_t chain0, iter;   // iteration index of THIS iteration
+  int pre;                 // 1: only the tau pre-draw
+  int stages;
+  double *beta, *lambda, *sig2, *tau, *alpha;
+  uint32_t* status;
+  double* A;               // [nchains][P][P] column-major workspace (lower triangle holds L)
+  double* sdel;            // [nchains][P] scratch: X'X (beta - bc)
+  DrawSink sink;
+  long long slot;          // sink slot for this iteration, -1 = do not store
+};
+
+constexpr int SL_NB = 64;
+constexpr int SL_T = 256;
+
+// ---- tau, sig2, lambda: one CTA per chain -------------------------------------------------
+__global__ void __launch_bounds__(SL_T) stbl_scalar_kernel(const StbLargeLaunch L) {
+  extern __shared__ double smem[];
+  const int P = L.m.P, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double* dl_s = smem;                       // [P] beta - bc
+  double* red = dl_s + P;                    // [24]
+  double* sc = red + 24;                     // tau, sig2
+  int* q_s = reinterpret_cast<int*>(sc + 2); // [2][P]
+  int* qn_s = q_s + 2 * P;
+  uint32_t* kk_s = reinterpret_cast<uint32_t*>(qn_s + 2);
+  const int ch = blockIdx.x; if (ch >= L.nchains) return;
+  const uint32_t gch = L.chain0 + (uint32_t)ch, t = L.iter;
+  const double alpha = L.h.true_alpha;
+  const bool know_tau = L.h.true_tau > 0, know_sig2 = L.h.true_sig2 > 0;
+  const bool do_tau = ((L.stages & 1) || L.pre) && !know_tau, do_sig2 = (L.stages & 2) && !know_sig2 && !L.pre;
+  const bool do_lambda = (L.stages & 32) && !L.pre;
+  uint32_t status = 0;
+  const double* beta = L.beta + (size_t)ch * P;
+  for (int j = tid; j < P; j += SL_T) dl_s[j] = beta[j] - __ldg(L.m.bc + j);
+  if (tid == 0) { sc[0] = know_tau ? L.h.true_tau : L.tau[ch]; sc[1] = know_sig2 ? L.h.true_sig2 : L.sig2[ch]; qn_s[0] = 0; qn_s[1] = 0; }
+  __syncthreads();
+  double pt = 0.0, pq = 0.0, pg = 0.0;
+  for (int k = tid; k < P; k += SL_T) {
+    pt += exp(alpha * log(fabs(beta[k])));
+    if (do_sig2) {
+      double s = 0.0;   // (X'X delta)_k
+      for (int j = 0; j < P; ++j) s = fma(__ldg(L.m.XX + k + (size_t)j * P), dl_s[j], s);
+      pq = fma(dl_s[k], s, pq);
+      pg = fma(dl_s[k], __ldg(L.m.gc + k), pg);
+    }
+  }
+  pt = warp_sum(pt); pq = warp_sum(pq); pg = warp_sum(pg);
+  if (lane == 0) { red[warp] = pt; red[8 + warp] = pq; red[16 + warp] = pg; }
+  __syncthreads();
+  if (warp == 0 && do_tau) {
+    double st = lane < 8 ? red[lane] : 0.0; st = warp_sum(st);
+    Stream s(L.key, gch, t, L.pre ? ST_TAU_INIT : ST_TAU, 0);
+    const double nu = gamma_rate<true>(s, L.h.nu_shape + ((double)P) / alpha, L.h.nu_rate + st, status);
+    if (lane == 0) sc[0] = exp(-1.0 * log(nu) / alpha);
+  }
+  if (warp == 1 && do_sig2) {
+    double sq = lane < 8 ? red[8 + lane] : 0.0, sg = lane < 8 ? red[16 + lane] : 0.0;
+    sq = warp_sum(sq); sg = warp_sum(sg);
+    const double rss = L.m.r0b - 2.0 * sg + sq;
+    Stream s(L.key, gch, t, ST_SIG2, 0);
+    const double g = gamma_rate<true>(s, L.h.sig2_shape + 0.5 * L.m.N, 1.0, status);
+    if (lane == 0) sc[1] = (L.h.sig2_scale + 0.5 * rss) / g;
+  }
+  __syncthreads();
+  const double tau = sc[0];
+  if (tid == 0) { L.tau[ch] = sc[0]; L.sig2[ch] = sc[1]; L.alpha[ch] = alpha; }
+  double* lam = L.lambda + (size_t)ch * P;
+  int cur_q = 0, n_act = do_lambda ? P : 0;
+  bool first = true;
+  while (n_act > 0) {
+    for (int slot_ = tid; slot_ < n_act; slot_ += SL_T) {
+      const int j = first ? slot_ : q_s[cur_q * P + slot_];
+      uint32_t k = first ? 0u : kk_s[j];
+      const double b = beta[j];
+      RetConst rc; rc.init(b * b / (tau * tau), 0.5 * alpha);
+      Stream s(L.key, gch, t, ST_LAMBDA, (uint32_t)j);
+      double out = 0.0;
+      const int r = retstable_round(rc, s, k, out);
+      if (r == 2) lam[j] = 2 * out;
+      else if (k >= K_CAP - 8) { lam[j] = nan(""); status |= ST_TRIAL_CAP; }
+      else { kk_s[j] = k; q_s[(cur_q ^ 1) * P + atomicAdd(&qn_s[cur_q ^ 1], 1)] = j; }
+    }
+    __syncthreads();
+    cur_q ^= 1; n_act = qn_s[cur_q]; first = false;
+    if (tid == 0) qn_s[cur_q ^ 1] = 0;
+    __syncthreads();
+  }
+  status = __reduce_or_sync(0xffffffffu, status);
+  if (lane == 0 && status) atomicOr(L.status + ch, status);
+}
+
+// ---- A_c = X'X + diag(lambda sig2 / tau^2), lower triangle (and the diagonal blocks in full) ----
+__global__ void stbl_build_kernel(const StbLargeLaunch L) {
+  const int P = L.m.P, ch = blockIdx.y;
+  const double f = L.sig2[ch] / (L.tau[ch] * L.tau[ch]);
+  double* A = L.A + (size_t)ch * P * P;
+  const double* lam = L.lambda + (size_t)ch * P;
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < (size_t)P * P; e += (size_t)gridDim.x * blockDim.x) {
+    const int r = (int)(e % P), c = (int)(e / P);
+    if (r < c && r / SL_NB != c / SL_NB) continue;
+    A[e] = __ldg(L.m.XX + e) + (r == c ? lam[r] * f : 0.0);
+  }
+}
+
+// ---- Cholesky of the diagonal block kb (<= 64 x 64) in shared memory ----
+__global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, int P, int kb, uint32_t* status) {
+  __shared__ double S[SL_NB][SL_NB + 1];
+  const int ch = blockIdx.x, tid = threadIdx.x;
+  double* A = Aall + (size_t)ch * P * P;
+  const int k0 = kb * SL_NB, nb = min(SL_NB, P - k0);
+  for (int e = tid; e < nb * nb; e += SL_T) { const int r = e % nb, c = e / nb; S[r][c] = A[(k0 + r) + (size_t)(k0 + c) * P]; }
+  __syncthreads();
+  for (int k = 0; k < nb; ++k) {
+    const double piv = S[k][k];
+    __syncthreads();
+    if (tid == 0) { if (!(piv > 0.0)) atomicOr(status + ch, (uint32_t)ST_CHOL_FAIL); S[k][k] = sqrt(piv); }
+    const double rs = rsqrt(piv);
+    for (int r = k + 1 + tid; r < nb; r += SL_T) S[r][k] *= rs;
+    __syncthreads();
+    const int rem = nb - k - 1;
+    for (int e = tid; e < rem * rem; e += SL_T) {
+      const int r = k + 1 + e % rem, c = k + 1 + e / rem;
+      if (r >= c) S[r][c] = fma(-S[r][k], S[c][k], S[r][c]);
+    }
+    __syncthreads();
+  }
+  for (int e = tid; e < nb * nb; e += SL_T) { const int r = e % nb, c = e / nb; if (r >= c) A[(k0 + r) + (size_t)(k0 + c) * P] = S[r][c]; }
+}
+
+// ---- panel: rows below the diagonal block,  X L_kk' = A_panel  (one thread per row) ----
+__global__ void __launch_bounds__(SL_NB) stbl_trsm_kernel(double* Aall, int P, int kb) {
+  __shared__ double Lk[SL_NB][SL_NB + 1];
+  const int ch = blockIdx.y, tid = threadIdx.x;
+  double* A = Aall + (size_t)ch * P * P;
+  const int k0 = kb * SL_NB, nb = min(SL_NB, P - k0);
+  const int r0 = k0 + nb + blockIdx.x * SL_NB;
+  for (int e = tid; e < nb * nb; e += SL_NB) { const int r = e % nb, c = e / nb; Lk[r][c] = A[(k0 + r) + (size_t)(k0 + c) * P]; }
+  __syncthreads();
+  const int row = r0 + tid;
+  if (row >= P) return;
+  double x[SL_NB];
+#pragma unroll
+  for (int c = 0; c < SL_NB; ++c) x[c] = c < nb ? A[row + (size_t)(k0 + c) * P] : 0.0;
+#pragma unroll
+  for (int c = 0; c < SL_NB; ++c) {
+    if (c < nb) {
+      double s = x[c];
+#pragma unroll
+      for (int k = 0; k < SL_NB; ++k) if (k < c) s = fma(-x[k], Lk[c][k], s);
+      x[c] = s / Lk[c][c];
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < SL_NB; ++c) if (c < nb) A[row + (size_t)(k0 + c) * P] = x[c];
+}
+
+// ---- trailing update on the FP64 tensor cores: C(i,j) -= L(i,kb) L(j,kb)'  for i >= j > kb ----
+// CTA = one 64 x 64 tile of one chain; panels staged k-major in smem (ld 72: minimal 2-way pattern).
+constexpr int SL_LD = 72;
+__global__ void __launch_bounds__(256) stbl_syrk_kernel(double* Aall, int P, int kb) {
+  extern __shared__ double smem[];
+  double* As = smem;
+  double* Bs = smem + SL_NB * SL_LD;
+  const int ch = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double* A = Aall + (size_t)ch * P * P;
+  int tIdx = blockIdx.x, ti = 0;
+  while ((ti + 1) * (ti + 2) / 2 <= tIdx) ++ti;
+  const int tj = tIdx - ti * (ti + 1) / 2;
+  const int k0 = kb * SL_NB;
+  const int i0 = k0 + SL_NB + ti * SL_NB, j0 = k0 + SL_NB + tj * SL_NB;
+  for (int e = tid; e < SL_NB * SL_NB; e += 256) {
+    const int r = e % SL_NB, k = e / SL_NB;
+    As[k * SL_LD + r] = (i0 + r < P) ? A[(i0 + r) + (size_t)(k0 + k) * P] : 0.0;
+    Bs[k * SL_LD + r] = (j0 + r < P) ? A[(j0 + r) + (size_t)(k0 + k) * P] : 0.0;
+  }
+  __syncthreads();
+  double acc[8][2];
+#pragma unroll
+  for (int t = 0; t < 8; ++t) { acc[t][0] = 0.0; acc[t][1] = 0.0; }
+#pragma unroll 4
+  for (int kk = 0; kk < SL_NB; kk += 4) {
+    const double a = As[(kk + (lane & 3)) * SL_LD + warp * 8 + (lane >> 2)];
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+      const double b = Bs[(kk + (lane & 3)) * SL_LD + t * 8 + (lane >> 2)];
+      dmma_m8n8k4(acc[t][0], acc[t][1], a, b);
+    }
+  }
+#pragma unroll
+  for (int t = 0; t < 8; ++t) {
+    const int r = i0 + warp * 8 + (lane >> 2), c = j0 + t * 8 + 2 * (lane & 3);
+    if (r < P) {
+      if (c < P && (ti > tj || r >= c)) A[r + (size_t)c * P] -= acc[t][0];
+      if (c + 1 < P && (ti > tj || r >= c + 1)) A[r + (size_t)(c + 1) * P] -= acc[t][1];
+    }
+  }
+}
+
+// ---- beta = L^-T (L^-1 Xy + sig eps): one CTA per chain, blocked substitution ----
+__global__ void __launch_bounds__(SL_T) stbl_solve_kernel(const StbLargeLaunch L) {
+  extern __shared__ double smem[];
+  const int P = L.m.P, tid = threadIdx.x, ch = blockIdx.x;
+  if (ch >= L.nchains) return;
+  double* x = smem;   // [P]
+  const double* A = L.A + (size_t)ch * P * P;
+  const uint32_t gch = L.chain0 + (uint32_t)ch;
+  const double sig = sqrt(L.sig2[ch]);
+  for (int j = tid; j < P; j += SL_T) x[j] = __ldg(L.m.Xy + j);
+  __syncthreads();
+  // forward: L w = Xy, column-oriented
+  for (int k0 = 0; k0 < P; k0 += SL_NB) {
+    const int nb = min(SL_NB, P - k0);
+    if (tid < 32) {   // diagonal block by one warp
+      for (int k = k0; k < k0 + nb; ++k) {
+        const double xk = x[k] / A[k + (size_t)k * P];
+        __syncwarp();
+        if (tid == 0) x[k] = xk;
+        for (int r = k + 1 + tid; r < k0 + nb; r += 32) x[r] = fma(-A[r + (size_t)k * P], xk, x[r]);
+        __syncwarp();
+      }
+    }
+    __syncthreads();
+    for (int r = k0 + nb + tid; r < P; r += SL_T) {
+      double s = x[r];
+      for (int k = k0; k < k0 + nb; ++k) s = fma(-A[r + (size_t)k * P], x[k], s);
+      x[r] = s;
+    }
+    __syncthreads();
+  }
+  for (int j = tid; j < P; j += SL_T) { Stream s(L.key, gch, L.iter, ST_BETA_STB, (uint32_t)j); x[j] = fma(sig, s.norm(0), x[j]); }
+  __syncthreads();
+  // backward: L' b = x ; row-oriented over the stored lower triangle
+  const int nblk = (P + SL_NB - 1) / SL_NB;
+  for (int kbk = nblk - 1; kbk >= 0; --kbk) {
+    const int k0 = kbk * SL_NB, nb = min(SL_NB, P - k0);
+    // x[k0..k0+nb) -= L[r, k0..]' x[r] for r >= k0+nb : each thread handles one k and strides over r? use 4 threads per k
+    {
+      const int k = k0 + (tid & (SL_NB - 1)), part = tid / SL_NB;   // 4 parts
+      double s = 0.0;
+      if (k < k0 + nb) for (int r = k0 + nb + part; r < P; r += SL_T / SL_NB) s = fma(A[r + (size_t)k * P], x[r], s);
+      __shared__ double ps[SL_T];
+      ps[tid] = s;
+      __syncthreads();
+      if (tid < nb) x[k0 + tid] -= ps[tid] + ps[tid + SL_NB] + ps[tid + 2 * SL_NB] + ps[tid + 3 * SL_NB];
+      __syncthreads();
+    }
+    if (tid < 32) {
+      for (int k = k0 + nb - 1; k >= k0; --k) {
+        const double xk = x[k] / A[k + (size_t)k * P];
+        __syncwarp();
+        if (tid == 0) x[k] = xk;
+        for (int r = k0 + tid; r < k; r += 32) x[r] = fma(-A[k + (size_t)r * P], xk, x[r]);
+        __syncwarp();
+      }
+    }
+    __syncthreads();
+  }
+  double* beta = L.beta + (size_t)ch * P;
+  for (int j = tid; j < P; j += SL_T) {
+    beta[j] = x[j];
+    if (L.slot >= 0) {
+      const size_t o = ((size_t)ch * L.sink.chain_stride + L.slot) * P + j;
+      if (L.sink.beta) L.sink.beta[o] = x[j];
+      if (L.sink.lambda) L.sink.lambda[o] = L.lambda[(size_t)ch * P + j];
+    }
+  }
+  if (tid == 0 && L.slot >= 0) {
+    const size_t o = (size_t)ch * L.sink.chain_stride + L.slot;
+    if (L.sink.sig2) L.sink.sig2[o] = L.sig2[ch];
+    if (L.sink.tau) L.sink.tau[o] = L.tau[ch];
+    if (L.sink.alpha) L.sink.alpha[o] = L.alpha[ch];
+  }
+}
+
+}  // namespace bb

@@ -1,0 +1,168 @@
+/*
+ * bayesbridge_b200.h -- C ABI of libbayesbridge_b200.so
+ *
+ * A B200-native (sm_100a) implementation of BayesBridge's Gibbs sweep for bridge regression.
+ * Plain pointers and sizes only; no C++ or torch types cross this boundary.
+ * Citations are file:line under the reference tree (/root/reference/).
+ *
+ * Part 1 -- drop-in symbols: exactly what R's .C() binds in the reference package
+ *           (Code/C/BridgeWrapper.R:170-179 and :220-228; declared extern "C" at
+ *           Code/C/BridgeWrapper.h:164-226, defined at Code/C/BridgeWrapper.cpp:572-656, 659-732).
+ * Part 2 -- the sampler interface of class BridgeRegression (Code/C/BridgeRegression.h:81-166)
+ *           as handle-based calls: a model (chain-independent factors in HBM), a set of chains
+ *           (state in HBM) and `bb_chains_run`, which advances all chains by whole iterations or
+ *           by single conditionals (stage mask).
+ * Part 3 -- batched extension (not in the reference): many chains, seeds, thinning.
+ *
+ * There is no CPU fallback: every entry point fails (error string, NaN-filled outputs) when no
+ * CUDA device is usable.
+ */
+#ifndef BAYESBRIDGE_B200_H
+#define BAYESBRIDGE_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---------------------------------------------------------------------------------------- */
+/* Part 1: drop-in .C() entry points                                                         */
+/* ---------------------------------------------------------------------------------------- */
+
+/* Replaces bridge_regression, Code/C/BridgeWrapper.h:178-203 / BridgeWrapper.cpp:572-656.
+ * Argument ORDER is ABI (R reads results positionally, BridgeWrapper.R:181-183).
+ * betap,up,omegap,shapep: P*M doubles out (P fastest); sig2p,taup,alphap: M doubles out;
+ * yp: N; Xp: N*P column-major; true_* > 0 means known/fixed; runtime: seconds of the
+ * post-burn-in loop.  ortho/use_hmc are R logicals passed as 4-byte ints (BridgeWrapper.R:178);
+ * the reference types them `const bool*` and reads the low byte -- `const int*` is binary
+ * compatible and correct.  use_hmc is ignored (forced false at BridgeRegression.cpp:419). */
+void bridge_regression(double *betap, double *up, double *omegap, double *shapep,
+                       double *sig2p, double *taup, double *alphap,
+                       const double *yp, const double *Xp,
+                       const double *sig2_shape, const double *sig2_scale,
+                       const double *nu_shape, const double *nu_rate,
+                       const double *alpha_a, const double *alpha_b,
+                       const double *true_sig2, const double *true_tau, const double *true_alpha,
+                       const int *P, const int *N, const int *M, const int *burn,
+                       double *runtime, const int *ortho, const int *betaburn, const int *use_hmc);
+
+/* Replaces bridge_reg_stable, Code/C/BridgeWrapper.h:205-226 / BridgeWrapper.cpp:659-732. */
+void bridge_reg_stable(double *betap, double *lambdap,
+                       double *sig2p, double *taup, double *alphap,
+                       const double *yp, const double *Xp,
+                       const double *sig2_shape, const double *sig2_scale,
+                       const double *nu_shape, const double *nu_rate,
+                       const double *alpha_a, const double *alpha_b,
+                       const double *true_sig2, const double *true_tau, const double *true_alpha,
+                       const int *P, const int *N, const int *M, const int *burn,
+                       double *runtime, const int *ortho);
+
+/* Seed used by the two drop-in calls (the reference draws from R's global RNG between
+ * GetRNGstate/PutRNGstate, BridgeWrapper.cpp:610-612,636-638; an R binding would call this with
+ * one unif_rand() draw so that set.seed() governs the run).  Default 20121027. */
+void bb_set_seed(unsigned long long seed);
+/* Device used by the drop-in calls (default 0). */
+void bb_set_device(int device);
+/* Banner printing of the reference drivers (BridgeWrapper.cpp:112-117,162-163,200): 0 = quiet (default). */
+void bb_set_verbose(int verbose);
+
+/* ---------------------------------------------------------------------------------------- */
+/* Part 2: sampler interface                                                                 */
+/* ---------------------------------------------------------------------------------------- */
+typedef struct bb_model bb_model;   /* role of BridgeRegression::BridgeRegression(X,y), BridgeRegression.cpp:13-69 */
+typedef struct bb_chains bb_chains; /* the slices beta[i],u[i],... the drivers carry, BridgeWrapper.cpp:80-100 */
+
+typedef struct bb_hyper {           /* BridgeWrapper.cpp:89-100 */
+  double sig2_shape, sig2_scale, nu_shape, nu_rate, alpha_a, alpha_b;
+  double true_sig2, true_tau, true_alpha;   /* > 0: known, kept fixed (BridgeWrapper.cpp:107-109) */
+  int betaburn;                             /* extra rotated sweeps per iteration (BridgeRegression.cpp:421) */
+} bb_hyper;
+
+enum { BB_TRI = 0, BB_STB = 1 };
+enum { BB_MEM_HOST = 0, BB_MEM_DEVICE = 1 };
+
+/* stage mask for bb_chains_run (the conditionals of one Gibbs iteration, in driver order) */
+enum {
+  BB_ST_TAU = 1,     /* sample_tau_marg     BridgeRegression.cpp:453-465 */
+  BB_ST_SIG2 = 2,    /* sample_sig2         :436-450 */
+  BB_ST_OMEGA = 4,   /* sample_omega        :130-147   (tri) */
+  BB_ST_U = 8,       /* sample_u            :97-110    (tri) */
+  BB_ST_BETA = 16,   /* sample_beta :405-433 (tri) | sample_beta_stable :552-575 (stb) | the *_ortho forms */
+  BB_ST_LAMBDA = 32, /* sample_lambda       :506-510   (stb) */
+  BB_ST_ALL = 63
+};
+
+/* which per-iteration draws bb_chains_run keeps (bit mask) and bb_chains_fetch returns */
+enum { BB_OUT_BETA = 1, BB_OUT_U = 2, BB_OUT_OMEGA = 4, BB_OUT_SHAPE = 8, BB_OUT_LAMBDA = 16,
+       BB_OUT_SIG2 = 32, BB_OUT_TAU = 64, BB_OUT_ALPHA = 128 };
+
+const char *bb_last_error(void);
+int bb_device_count(void);
+
+/* X: N x P column-major, y: N; `mem` says where X,y live.  Builds X'X, X'y (FP64 tensor-core Gram),
+ * the SVD factors V,d,a (one-sided Jacobi) and the least-squares start on `device`. NULL on error. */
+bb_model *bb_model_create(const double *X, const double *y, int N, int P, int device, int mem);
+/* Same, with caller-supplied factors tV (P x P col-major, tV[i+j*P] = V(j,i)), d, a, bhat (host):
+ * used to run the sampler on exactly the reference's LAPACK factors.  bhat may be NULL. */
+bb_model *bb_model_create_factors(const double *X, const double *y, int N, int P,
+                                  const double *tV, const double *d, const double *a, const double *bhat,
+                                  int device, int mem);
+/* Row-sharded construction.  bb_gram: G = [X y]'[X y] of a row shard, (P+1) x (P+1) col-major,
+ * written to DEVICE memory G (to be all-reduced by the caller, e.g. NCCL).  Then
+ * bb_model_create_gram builds the model from the reduced G (device memory), N = total rows. */
+int bb_gram(const double *X_dev, const double *y_dev, int n_rows, int P, double *G_dev, int device);
+bb_model *bb_model_create_gram(const double *G_dev, int N, int P, int device);
+/* residual sums of squares of a row shard at the two expansion centres -> out_dev[0..1] (device);
+ * after the all-reduce, bb_model_set_r0 installs the totals. */
+int bb_model_resid_partial(const bb_model *m, const double *X_dev, const double *y_dev, int n_rows, double *out_dev);
+int bb_model_set_r0(bb_model *m, double r0z, double r0b);
+void bb_model_free(bb_model *m);
+/* copy factors to host (any pointer may be NULL) */
+int bb_model_get(const bb_model *m, double *XX, double *Xy, double *bhat, double *tV, double *d, double *a);
+double bb_model_precompute_ms(const bb_model *m);
+
+/* nchains chains with the drivers' initial state: beta = least squares, u = 0.5, omega = 1,
+ * lambda = 1, shape = 0 (BridgeWrapper.cpp:120-129, 241-250, 603-605, 686).  chain0 = global id of
+ * the first chain: the Philox stream of a chain depends only on (seed, chain0 + local index). */
+bb_chains *bb_chains_create(const bb_model *m, int method, int ortho, int nchains,
+                            unsigned long long seed, unsigned int chain0);
+void bb_chains_free(bb_chains *c);
+/* state vectors are [nchains][P] (P fastest) / [nchains], host memory; NULL = leave untouched.
+ * aux = omega (tri) or lambda (stb). */
+int bb_chains_set(bb_chains *c, const double *beta, const double *u, const double *aux,
+                  const double *sig2, const double *tau);
+int bb_chains_get(const bb_chains *c, double *beta, double *u, double *aux, double *shape,
+                  double *sig2, double *tau, unsigned int *status);
+/* reserve a device buffer for `nslots` stored iterations per chain of the outputs in out_mask */
+int bb_chains_reserve(bb_chains *c, long long nslots, int out_mask);
+/* Advance every chain by niter iterations; iteration index of the first = iter0 (RNG counter).
+ * stages: BB_ST_* mask (BB_ST_ALL = the full sweep).  pre_tau: draw tau once first
+ * (BridgeWrapper.cpp:142,262).  Every thin-th iteration is stored from slot `slot0` on (thin = 0:
+ * nothing stored).  kernel_ms (may be NULL) receives the device time of the launches. */
+int bb_chains_run(bb_chains *c, const bb_hyper *h, unsigned int iter0, int niter, int stages,
+                  int pre_tau, int thin, long long slot0, double *kernel_ms);
+/* copy current state into slot `slot` of the draw buffer (sample 0 of the drivers = state after burn-in) */
+int bb_chains_store_state(bb_chains *c, long long slot);
+/* copy stored draws to host: out[(chain*nslots + s)*P + j] (or [chain*nslots + s] for scalars) */
+int bb_chains_fetch(const bb_chains *c, int which, long long slot0, long long nslots, double *out);
+/* number of kernels launched by this library in this process so far */
+long long bb_launch_count(void);
+
+/* ---------------------------------------------------------------------------------------- */
+/* Part 3: batched extension                                                                 */
+/* ---------------------------------------------------------------------------------------- */
+/* Runs nchains chains: burn iterations (stb: burn+1, BridgeWrapper.cpp:266), then nsamp stored
+ * samples (sample 0 = state after burn-in, then every thin-th iteration), exactly the drivers'
+ * schedule.  Host buffers: beta/aux1/aux2/aux3 are [nchains][nsamp][P], scalars [nchains][nsamp];
+ * tri: aux1=u, aux2=omega, aux3=shape; stb: aux1=lambda. Any output pointer may be NULL.
+ * runtime: seconds of the post-burn-in loop.  Returns 0 on success. */
+int bb_bridge_batched(int method, int ortho,
+                      const double *X, const double *y, int N, int P, const bb_hyper *h,
+                      int nchains, unsigned long long seed, unsigned int chain0,
+                      int burn, int nsamp, int thin, int device,
+                      double *beta, double *aux1, double *aux2, double *aux3,
+                      double *sig2, double *tau, double *alpha, unsigned int *status, double *runtime);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -377,3 +377,20 @@ class RefModel:
 
     def retstable_LD(self, h, alpha, V0, seed, chain, it, item):
         return self.L.ref_retstable_LD(h, alpha, V0, seed, chain, it, item)
+
+
+def draw_many(kind, n, params=(), seed=1):
+    """bulk draws from the draw spec (bbo_draws.h) for distribution tests; see bbo_draw_many."""
+    L = Port().L
+    L.bbo_draw_many.argtypes = [C.c_int, C.c_int, _dp, C.c_uint64, _dp]
+    p = _f64(list(params) + [0.0])
+    out = np.zeros(n)
+    L.bbo_draw_many(kind, n, _p(p), seed, _p(out))
+    return out
+
+
+def philox(ctr, key):
+    L = Port().L
+    c = (C.c_uint32 * 4)(*ctr); k = (C.c_uint32 * 2)(*key); o = (C.c_uint32 * 4)()
+    L.bbo_philox(c, k, o)
+    return list(o)

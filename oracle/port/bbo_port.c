@@ -577,3 +577,29 @@ double bbo_bridge_reg_stable(const bbo_model *m, const bbo_opts *o, int M,
   }
   return now_sec() - start;
 }
+
+/* ------------------------------------------------------------------ bulk draw probes (distribution tests) */
+/* item i of (seed, chain 0, iter 0, stage SCALAR) -> out[i]; kind: 0 unif, 1 norm, 2 gamma(p0,p1),
+   3 tnorm(p0,p1,p2,p3), 4 tnorm_left(p0,p1,p2), 5 texpon_left(p0,p1), 6 texpon_both(p0,p1,p2),
+   7 rtgamma(p0,p1,p2), 8 retstable(h=p0, alpha=p1, V0=p2), 9 igamma(p0,p1) */
+void bbo_draw_many(int kind, int n, const double *p, uint64_t seed, double *out) {
+  bbo_rng r; bbo_rng_key(&r, seed, 0);
+  for (int i = 0; i < n; ++i) {
+    bbo_rng_at(&r, 0, BBO_ST_SCALAR, (uint32_t)i);
+    switch (kind) {
+      case 0: out[i] = bbo_unif(&r); break;
+      case 1: out[i] = bbo_norm(&r); break;
+      case 2: out[i] = bbo_gamma_rate(&r, p[0], p[1]); break;
+      case 3: out[i] = bbo_tnorm(&r, p[0], p[1], p[2], p[3]); break;
+      case 4: out[i] = bbo_tnorm_left(&r, p[0], p[1], p[2]); break;
+      case 5: out[i] = bbo_texpon_rate_left(&r, p[0], p[1]); break;
+      case 6: out[i] = bbo_texpon_rate_both(&r, p[0], p[1], p[2]); break;
+      case 7: out[i] = bbo_rtgamma_rate(&r, p[0], p[1], p[2]); break;
+      case 8: out[i] = bbo_retstable_LD(p[0], p[1], p[2], &r); break;
+      case 9: out[i] = bbo_igamma(&r, p[0], p[1]); break;
+      default: out[i] = NAN;
+    }
+  }
+}
+/* raw Philox block for known-answer tests */
+void bbo_philox(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) { bbo_philox4x32_10(ctr, key, out); }
