@@ -249,6 +249,7 @@ void model_gram(bb_model* m) {
 // ===========================================================================================
 struct bb_chains {
   const bb_model* m = nullptr;
+  int device = 0;   // copy: the model may be freed before its chains
   int method = BB_TRI, ortho = 0, nchains = 0;
   unsigned long long seed = 0;
   unsigned int chain0 = 0;
@@ -266,7 +267,7 @@ struct bb_chains {
 
   void free_draws() { dfree(o_beta); dfree(o_u); dfree(o_omega); dfree(o_shape); dfree(o_lambda); dfree(o_sig2); dfree(o_tau); dfree(o_alpha); nslots = 0; out_mask = 0; }
   ~bb_chains() {
-    cudaSetDevice(m->device);
+    cudaSetDevice(device);
     dfree(beta); dfree(u); dfree(aux); dfree(shape); dfree(z); dfree(sig2); dfree(tau); dfree(alpha); dfree(status); dfree(A); dfree(sdel);
     free_draws();
     if (ev0) cudaEventDestroy(ev0);
@@ -461,6 +462,7 @@ void chains_run(bb_chains* c, const bb_hyper* hh, unsigned iter0, int niter, int
 
 template <typename F>
 int guarded(F&& f) {
+  cudaGetLastError();   // drop any stale non-sticky error of an earlier call
   try { f(); return 0; }
   catch (const bb::CudaError& e) { set_err(std::string("CUDA error: ") + cudaGetErrorString(e.code)); }
   catch (const std::string& s) { set_err(s); }
@@ -593,7 +595,7 @@ bb_chains* bb_chains_create(const bb_model* m, int method, int ortho, int nchain
     if (!m || nchains < 1) throw std::string("bb_chains_create: bad arguments");
     BB_CUDA_CHECK(cudaSetDevice(m->device));
     c = new bb_chains();
-    c->m = m; c->method = method; c->ortho = ortho; c->nchains = nchains; c->seed = seed; c->chain0 = chain0;
+    c->m = m; c->device = m->device; c->method = method; c->ortho = ortho; c->nchains = nchains; c->seed = seed; c->chain0 = chain0;
     BB_CUDA_CHECK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     BB_CUDA_CHECK(cudaEventCreate(&c->ev0)); BB_CUDA_CHECK(cudaEventCreate(&c->ev1));
     const size_t n = (size_t)nchains * m->P;

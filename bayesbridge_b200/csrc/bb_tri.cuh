@@ -23,6 +23,7 @@
 //   * ||y - X beta||^2 (:440-443) is r0 + sum_i d_i^2 (z_i - zc_i)^2, which never touches X.
 #pragma once
 #include <cfloat>
+#include <math_constants.h>
 #include "bb_common.cuh"
 
 namespace bb {
@@ -226,7 +227,8 @@ __global__ void __launch_bounds__(MAXT, 1) tri_sweep_kernel(const TriLaunch L) {
         double v[J], w[J], vn[J], wn[J], vp[J];
 #pragma unroll
         for (int jj = 0; jj < J; ++jj) {
-          v[jj] = __ldg(L.m.Vc + tid + jj * nct); w[jj] = __ldg(L.m.Wc + tid + jj * nct);
+          const bool in = tid + jj * nct < ldv;   // coordinates beyond the padded row: v = 0, 1/|v| = inf
+          v[jj] = in ? __ldg(L.m.Vc + tid + jj * nct) : 0.0; w[jj] = in ? __ldg(L.m.Wc + tid + jj * nct) : CUDART_INF;
           vp[jj] = 0.0; vn[jj] = 0.0; wn[jj] = 0.0;
         }
 #pragma unroll
@@ -237,8 +239,9 @@ __global__ void __launch_bounds__(MAXT, 1) tri_sweep_kernel(const TriLaunch L) {
           if (i + 1 < P) {
 #pragma unroll
             for (int jj = 0; jj < J; ++jj) {
-              vn[jj] = __ldg(L.m.Vc + (size_t)(i + 1) * ldv + tid + jj * nct);
-              wn[jj] = __ldg(L.m.Wc + (size_t)(i + 1) * ldv + tid + jj * nct);
+              const bool in = tid + jj * nct < ldv;
+              vn[jj] = in ? __ldg(L.m.Vc + (size_t)(i + 1) * ldv + tid + jj * nct) : 0.0;
+              wn[jj] = in ? __ldg(L.m.Wc + (size_t)(i + 1) * ldv + tid + jj * nct) : CUDART_INF;
             }
           }
 #pragma unroll

@@ -394,3 +394,17 @@ def philox(ctr, key):
     c = (C.c_uint32 * 4)(*ctr); k = (C.c_uint32 * 2)(*key); o = (C.c_uint32 * 4)()
     L.bbo_philox(c, k, o)
     return list(o)
+
+
+def tnorm_at(seed, chain, it, stage, item, left, right, mu, sd):
+    L = Port().L
+    L.bbo_tnorm_at.restype = C.c_double
+    L.bbo_tnorm_at.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32] + [C.c_double] * 4
+    return L.bbo_tnorm_at(seed, chain, it, stage, item, left, right, mu, sd)
+
+
+def flat_at(seed, chain, it, stage, item, a, b):
+    L = Port().L
+    L.bbo_flat_at.restype = C.c_double
+    L.bbo_flat_at.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32] + [C.c_double] * 2
+    return L.bbo_flat_at(seed, chain, it, stage, item, a, b)

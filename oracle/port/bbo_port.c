@@ -603,3 +603,13 @@ void bbo_draw_many(int kind, int n, const double *p, uint64_t seed, double *out)
 }
 /* raw Philox block for known-answer tests */
 void bbo_philox(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) { bbo_philox4x32_10(ctr, key, out); }
+/* single derived draws at an explicit counter position (teacher-forced per-coordinate checks) */
+double bbo_tnorm_at(uint64_t seed, uint32_t chain, uint32_t iter, uint32_t stage, uint32_t item,
+                    double left, double right, double mu, double sd) {
+  bbo_rng r; bbo_rng_key(&r, seed, chain); bbo_rng_at(&r, iter, stage, item);
+  return bbo_tnorm(&r, left, right, mu, sd);
+}
+double bbo_flat_at(uint64_t seed, uint32_t chain, uint32_t iter, uint32_t stage, uint32_t item, double a, double b) {
+  bbo_rng r; bbo_rng_key(&r, seed, chain); bbo_rng_at(&r, iter, stage, item);
+  return bbo_flat(&r, a, b);
+}

@@ -21,3 +21,33 @@ def rel_err(a, b):
     a, b = np.asarray(a, dtype=float), np.asarray(b, dtype=float)
     scale = max(np.abs(b).max(), 1e-300)
     return np.abs(a - b).max() / scale
+
+
+def teacher_forced_sweep_error(f, beta0, b, sig2, seed, chain, it, beta_dev):
+    """Per-coordinate check of one rotated sweep (BridgeRegression.cpp:250-283): coordinate i of the
+    oracle is drawn from the DEVICE's state before step i (its z_0..z_{i-1}), on the same Philox block,
+    and compared with the device's z_i.  Returns max_i |z_i(oracle) - z_i(device)| / scale.
+    This isolates every single truncated-normal draw; rounding differences cannot compound."""
+    import bb_oracle as O
+    tV, d, a = np.asarray(f["tV"]), np.asarray(f["d"]), np.asarray(f["a"])
+    P = beta0.size
+    z = tV @ beta0
+    zdev = tV @ beta_dev
+    cur = beta0.astype(float).copy()
+    sig = np.sqrt(sig2)
+    worst, scale = 0.0, max(np.abs(zdev).max(), 1e-300)
+    for i in range(P):
+        v = tV[i, :]                       # V(j,i) over j
+        r = cur - v * z[i]
+        with np.errstate(divide="ignore", invalid="ignore"):
+            left = np.where(v > 0, -(b + r), -(b - r)) / np.abs(v)
+            right = np.where(v > 0, b - r, b + r) / np.abs(v)
+        lmax, rmin = np.nanmax(left), np.nanmin(right)
+        if d[i] > 1e-16:
+            want = O.tnorm_at(seed, chain, it, O.ST_BETA, i, lmax, rmin, a[i] / (d[i] * d[i]), sig / d[i])
+        else:
+            want = O.flat_at(seed, chain, it, O.ST_BETA, i, lmax, rmin)
+        worst = max(worst, abs(want - zdev[i]) / scale)
+        cur += v * (zdev[i] - z[i])
+        z[i] = zdev[i]
+    return worst
