@@ -365,7 +365,7 @@ void launch_tri(const bb::TriLaunch& L, cudaStream_t st) {
 template <int TB>
 void launch_stb_small(const bb::StbLaunch& L, cudaStream_t st) {
   constexpr int PP = bb::STB_NB * TB;
-  const size_t smem = ((size_t)PP * PP + 2 * (PP + TB) + 4 * PP + 24 + 2) * sizeof(double) + (size_t)(2 * PP + 2 + PP) * sizeof(int);
+  const size_t smem = ((size_t)PP * PP + 2 * (PP + TB) + 4 * PP + 24 + 2) * sizeof(double) + (size_t)(2 * PP + 2 + PP + 2) * sizeof(int) + (size_t)PP * sizeof(bb::RetConst);
   auto kern = bb::stb_small_kernel<TB>;
   BB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   kern<<<L.nchains, bb::STB_THREADS, smem, st>>>(L);

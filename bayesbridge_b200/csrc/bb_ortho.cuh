@@ -168,29 +168,8 @@ __global__ void __launch_bounds__(ORT_T) ortho_kernel(const OrthoLaunch L) {
         __syncthreads();
       }
     } else {
-      // lambda (BridgeRegression.cpp:506-510), rounds with a compacted retry queue
-      int cur_q = 0, n_act = do_lambda ? P : 0;
-      bool first = true;
-      while (n_act > 0) {
-        for (int slot_ = tid; slot_ < n_act; slot_ += ORT_T) {
-          const int j = first ? slot_ : q_s[cur_q * P + slot_];
-          uint32_t k = first ? 0u : kk_s[j];
-          const double b = beta_s[j];
-          RetConst rc; rc.init(b * b / (tau * tau), 0.5 * alpha);
-          Stream s(L.key, gch, t, ST_LAMBDA, (uint32_t)j);
-          double out = 0.0;
-          const int r = retstable_round(rc, s, k, out);
-          if (r == 2) b_s[j] = 2 * out;
-          else if (k >= K_CAP - 8) { b_s[j] = nan(""); status |= ST_TRIAL_CAP; }
-          else { kk_s[j] = k; q_s[(cur_q ^ 1) * P + atomicAdd(&qn_s[cur_q ^ 1], 1)] = j; }
-        }
-        __syncthreads();
-        cur_q ^= 1; n_act = qn_s[cur_q]; first = false;
-        if (tid == 0) qn_s[cur_q ^ 1] = 0;
-        __syncthreads();
-      }
-      if (tid == 0) { qn_s[0] = 0; qn_s[1] = 0; }
-      __syncthreads();
+      // lambda (BridgeRegression.cpp:506-510): retry queue + speculative look-ahead (bb_retstable.cuh)
+      if (do_lambda) lambda_stage_cta<ORT_T>(P, beta_s, b_s, tau, 0.5 * alpha, L.key, gch, t, nullptr, q_s, P, qn_s, kk_s, status);
       if (do_sig2) draw_sig2(t);
       const double sig2 = sc[1];
       if (do_beta) {

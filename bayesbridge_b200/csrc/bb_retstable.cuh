@@ -47,22 +47,28 @@ struct RetConst {
   }
 };
 
-// One round starting at block k.  Returns 2 = accepted (value in `out`), otherwise the number of
-// blocks consumed is added to k and the caller retries: 0 = inner rejected, 1 = outer rejected.
-__device__ inline int retstable_round(const RetConst& c, const Stream& s, uint32_t& k, double& out) {
+// One round starting at block k, as straight-line code: the inner trial (3 Philox blocks,
+// retstable.cpp:162-207) and the outer trial (2 more blocks, :212-256) are BOTH evaluated, the
+// outer one speculatively, so that its pow/exp chain overlaps the inner one instead of waiting
+// behind a branch (the kernels that call this are latency-bound, the FP64 pipe has room).
+// Returns 0 = inner trial rejected (3 blocks consumed), 1 = outer trial rejected (5 blocks),
+// 2 = accepted (value in `out`).  The blocks are the ones the sequential reference would consume
+// at that position of its stream, so the accepted value does not depend on scheduling.
+__device__ __forceinline__ int retstable_round_at(const RetConst& c, const Stream& s, uint32_t k, double& out) {
   const double alpha = c.alpha, Ialpha = 1. - alpha;
-  // ---- inner trial (retstable.cpp:162-207) ----
-  const double V = s.unif(k);
+  double u0, u0b, u1a, u1b, u2, u2b, u3, u3b, u4a, u4b;
+  s.block(k, u0, u0b); s.block(k + 1, u1a, u1b); s.block(k + 2, u2, u2b); s.block(k + 3, u3, u3b); s.block(k + 4, u4a, u4b);
+  // ---- inner trial ----
+  const double V = u0;
   double U;
   if (c.gamma >= 1) {
-    if (V < c.w1 / (c.w1 + c.w2)) U = fabs(s.norm(k + 1)) / c.sgamma;
-    else { const double W_ = s.unif(k + 1); U = RS_PI * (1. - W_ * W_); }
+    if (V < c.w1 / (c.w1 + c.w2)) U = fabs(box_muller(u1a, u1b)) / c.sgamma;
+    else U = RS_PI * (1. - u1a * u1a);
   } else {
-    const double W_ = s.unif(k + 1);
-    if (V < c.w3 / (c.w2 + c.w3)) U = RS_PI * W_;
-    else U = RS_PI * (1. - W_ * W_);
+    if (V < c.w3 / (c.w2 + c.w3)) U = RS_PI * u1a;
+    else U = RS_PI * (1. - u1a * u1a);
   }
-  const double W = s.unif(k + 2);
+  const double W = u2;
   const double sA = sinc_mm(alpha * U), sI = sinc_mm(Ialpha * U), sU = sinc_mm(U);
   const double den = pow(sA, alpha) * pow(sI, Ialpha);      // BdB0 (retstable.cpp:73-77)
   const double zeta = sqrt(sU / den);
@@ -74,28 +80,27 @@ __device__ inline int retstable_round(const RetConst& c, const Stream& s, uint32
   if (U >= 0 && U <= RS_PI && c.gamma < 1) d += c.xi;
   rho *= d;
   const double Z = W * rho;
-  if (!(U < RS_PI && Z <= 1.)) { k += 3; return 0; }
-  // ---- outer trial (retstable.cpp:212-256) ----
+  const bool inner_ok = (U < RS_PI && Z <= 1.);
+  // ---- outer trial (speculative) ----
   const double Aval = pow(Ialpha * sI, Ialpha) * pow(alpha * sA, alpha) / sU;   // A_ (retstable.cpp:40-47)
   const double a = pow(Aval, 1. / (1. - alpha));
   const double m = pow(c.b / a, alpha) * c.lambda_alpha;
   const double delta = sqrt(m * alpha / a);
   const double a1 = delta * RS_C1, a2 = delta, a3 = z / a;
   const double ssum = a1 + a2 + a3;
-  const double V_ = s.unif(k + 3);
+  const double V_ = u3;
   double N_ = 0., E_ = 0., X;
-  if (V_ < a1 / ssum) { N_ = s.norm(k + 4); X = m - delta * fabs(N_); }
-  else if (V_ < (a1 + a2) / ssum) X = m + delta * s.unif(k + 4);
-  else { E_ = -log(s.unif(k + 4)); X = m + delta + E_ * a3; }
+  if (V_ < a1 / ssum) { N_ = box_muller(u4a, u4b); X = m - delta * fabs(N_); }
+  else if (V_ < (a1 + a2) / ssum) X = m + delta * u4a;
+  else { E_ = -log(u4a); X = m + delta + E_ * a3; }
   const double E = -log(Z);
   double cc = a * (X - m);
   cc += (m != 0) ? c.h * (pow(X, -1. * c.b) - pow(m, -1. * c.b)) : 0.0;
   if (X < m) cc -= N_ * N_ / 2.;
   else if (X > m + delta) cc -= E_;
-  k += 5;
-  if (!(X >= 0 && cc <= E)) return 1;
   out = exp(-c.b * log(X));   // exp(1/alpha*log(V0) - b*log(X)) with V0 = 1 (retstable.cpp:270)
-  return 2;
+  if (!inner_ok) return 0;
+  return (X >= 0 && cc <= E) ? 2 : 1;
 }
 
 // sequential form, one thread per item
@@ -104,10 +109,97 @@ __device__ inline double retstable_scalar(const Stream& s, double h, double alph
   RetConst c; c.init(h, alpha);
   uint32_t k = 0; double out = 0.;
   while (k < K_CAP - 8) {
-    if (retstable_round(c, s, k, out) == 2) return out;
+    const int r = retstable_round_at(c, s, k, out);
+    if (r == 2) return out;
+    k += r == 0 ? 3u : 5u;
   }
   status |= ST_TRIAL_CAP;
   return nan("");
+}
+
+// ---------------------------------------------------------------------------------------------
+// CTA-wide lambda stage with a compacted retry queue and speculative look-ahead.
+//
+// The stream position of an item after some rejected rounds is k0 + 3a + 5b.  Every such offset
+// {0,3,5,6,8,9,10,...} can be evaluated independently because block indices are counters, so when
+// fewer items than threads are unfinished, G = 2..32 lanes take ONE item and evaluate the rounds
+// at the first G reachable offsets at once; a shuffle walk then follows the path the sequential
+// sampler would have taken (0 -> +3 on an inner rejection, +5 on an outer one) and either finds
+// the accepting round or leaves the item at the first offset that was not covered.  The result is
+// bit-identical to the one-round-at-a-time schedule; only the number of passes (each costing the
+// latency of one round, the bottleneck: the rejection tail of max_j trials_j) shrinks.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ int rs_reach(int i) { return i < 4 ? ((0x6530 >> (4 * i)) & 0xF) : i + 4; }     // 0,3,5,6,8,9,10,...
+__device__ __forceinline__ int rs_slot_of(int pos) { return pos >= 8 ? pos - 4 : (pos == 0 ? 0 : pos == 3 ? 1 : pos == 5 ? 2 : pos == 6 ? 3 : 64); }
+
+// NT: threads of the CTA (multiple of 32); every thread of the CTA must call.  beta: per-item
+// coordinate values (shared or global), lam_out: where 2*draw goes (shared or global).
+// q_s: [2][qld] ints, qn_s: [2] ints (both zero on entry and on exit), kk_s: [P] block positions.
+// rc_s: optional [P] cache of the per-item constants (nullptr: recompute every pass).
+template <int NT>
+__device__ inline void lambda_stage_cta(int P, const double* beta, double* lam_out, double tau, double alpha_half,
+                                        const RngKey key, uint32_t gch, uint32_t t, RetConst* rc_s,
+                                        int* q_s, int qld, int* qn_s, uint32_t* kk_s, uint32_t& status) {
+  const int tid = threadIdx.x;
+  int cur_q = 0, n_act = P;
+  bool first = true;
+  if (alpha_half == 1.) {   // point mass at V0 = 1 (retstable.cpp:104-110)
+    for (int j = tid; j < P; j += NT) lam_out[j] = 2.0;
+    __syncthreads();
+    return;
+  }
+  while (n_act > 0) {
+    int G = 1;
+    while (G < 32 && n_act * (G * 2) <= NT) G *= 2;
+    const int per_pass = NT / G;
+    const int sub = tid & (G - 1);
+    int nlvl = rs_reach(G - 1) / 3 + 1;
+    for (int base = 0; base < n_act; base += per_pass) {
+      const int slot = base + tid / G;
+      const bool valid = slot < n_act;
+      int j = 0; uint32_t k0 = 0; int code = 2; double out = 0.0;
+      if (valid) {
+        j = first ? slot : q_s[cur_q * qld + slot];
+        k0 = first ? 0u : kk_s[j];
+        RetConst rc;
+        if (rc_s && !first) rc = rc_s[j];
+        else {
+          const double b = beta[j];
+          rc.init(b * b / (tau * tau), alpha_half);   // h = beta_j^2 / tau^2 (BridgeRegression.cpp:509)
+          if (rc_s && sub == 0) rc_s[j] = rc;
+        }
+        Stream s(key, gch, t, ST_LAMBDA, (uint32_t)j);
+        code = retstable_round_at(rc, s, k0 + (uint32_t)rs_reach(sub), out);
+      }
+      // walk the sequential path through the G evaluated offsets (uniform trip count: shuffles)
+      int pos = 0, res = -1;
+      for (int lvl = 0; lvl < nlvl; ++lvl) {
+        const int idx = rs_slot_of(pos);
+        const bool covered = idx < G;
+        const int c = __shfl_sync(0xffffffffu, code, covered ? idx : 0, G);
+        if (res == -1) {
+          if (!covered) res = -2;
+          else if (c == 2) res = idx;
+          else pos += (c == 0) ? 3 : 5;
+        }
+      }
+      const double val = __shfl_sync(0xffffffffu, out, res >= 0 ? res : 0, G);
+      if (valid && sub == 0) {
+        if (res >= 0) lam_out[j] = 2 * val;
+        else if (k0 + (uint32_t)pos >= K_CAP - 64) { lam_out[j] = nan(""); status |= ST_TRIAL_CAP; }
+        else {
+          kk_s[j] = k0 + (uint32_t)pos;
+          q_s[(cur_q ^ 1) * qld + atomicAdd(&qn_s[cur_q ^ 1], 1)] = j;
+        }
+      }
+    }
+    __syncthreads();
+    cur_q ^= 1;
+    n_act = qn_s[cur_q];
+    first = false;
+    if (tid == 0) qn_s[cur_q ^ 1] = 0;   // the queue the next pass fills
+    __syncthreads();
+  }
 }
 
 }  // namespace bb

@@ -60,6 +60,7 @@ __global__ void __launch_bounds__(STB_THREADS, (TB == 4 ? 4 : 1)) stb_small_kern
   int* q_s = reinterpret_cast<int*>(sc_s + 2);   // [2][PP] retry queues
   int* qn_s = q_s + 2 * PP;                      // [2] counts
   uint32_t* kk_s = reinterpret_cast<uint32_t*>(qn_s + 2);   // [PP] next Philox block per coordinate
+  RetConst* rc_s = reinterpret_cast<RetConst*>(kk_s + PP + 2);   // [PP] per-coordinate constants of the tilted-stable draw (8-byte aligned: 3 PP + 4 ints)
 
   const int ch = blockIdx.x;
   if (ch >= L.nchains) return;
@@ -167,37 +168,8 @@ __global__ void __launch_bounds__(STB_THREADS, (TB == 4 ? 4 : 1)) stb_small_kern
     if (pre) continue;
     const double tau = sc_s[0], sig2 = sc_s[1];
 
-    // ---- lambda_j = 2 * retstable(beta_j^2 / tau^2, alpha/2): rounds with a compacted retry queue ----
-    {
-      int cur_q = 0;
-      int n_act = do_lambda ? P : 0;
-      bool first = true;
-      while (n_act > 0) {
-        for (int slot = tid; slot < n_act; slot += STB_THREADS) {
-          const int j = first ? slot : q_s[cur_q * PP + slot];
-          uint32_t k = first ? 0u : kk_s[j];
-          const double b = beta_s[j];
-          RetConst rc; rc.init(b * b / (tau * tau), 0.5 * alpha);
-          Stream s(L.key, gch, t, ST_LAMBDA, (uint32_t)j);
-          double out = 0.0;
-          const int r = retstable_round(rc, s, k, out);
-          if (r == 2) lam_s[j] = 2 * out;
-          else if (k >= K_CAP - 8) { lam_s[j] = nan(""); status |= ST_TRIAL_CAP; }
-          else {
-            kk_s[j] = k;
-            const int pos = atomicAdd(&qn_s[cur_q ^ 1], 1);
-            q_s[(cur_q ^ 1) * PP + pos] = j;
-          }
-        }
-        __syncthreads();
-        cur_q ^= 1;
-        n_act = qn_s[cur_q];
-        first = false;
-        if (tid == 0) qn_s[cur_q ^ 1] = 0;
-        __syncthreads();
-      }
-    }
-    __syncthreads();
+    // ---- lambda_j = 2 * retstable(beta_j^2 / tau^2, alpha/2): retry queue + speculative look-ahead ----
+    if (do_lambda) lambda_stage_cta<STB_THREADS>(P, beta_s, lam_s, tau, 0.5 * alpha, L.key, gch, t, rc_s, q_s, PP, qn_s, kk_s, status);
 
     if (do_beta) {
     // ---- A = X'X + diag(lambda sig2 / tau^2)   (BridgeRegression.cpp:554-556) ----

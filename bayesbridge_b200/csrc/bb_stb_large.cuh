@@ -84,26 +84,7 @@ __global__ void __launch_bounds__(SL_T) stbl_scalar_kernel(const StbLargeLaunch 
   const double tau = sc[0];
   if (tid == 0) { L.tau[ch] = sc[0]; L.sig2[ch] = sc[1]; L.alpha[ch] = alpha; }
   double* lam = L.lambda + (size_t)ch * P;
-  int cur_q = 0, n_act = do_lambda ? P : 0;
-  bool first = true;
-  while (n_act > 0) {
-    for (int slot_ = tid; slot_ < n_act; slot_ += SL_T) {
-      const int j = first ? slot_ : q_s[cur_q * P + slot_];
-      uint32_t k = first ? 0u : kk_s[j];
-      const double b = beta[j];
-      RetConst rc; rc.init(b * b / (tau * tau), 0.5 * alpha);
-      Stream s(L.key, gch, t, ST_LAMBDA, (uint32_t)j);
-      double out = 0.0;
-      const int r = retstable_round(rc, s, k, out);
-      if (r == 2) lam[j] = 2 * out;
-      else if (k >= K_CAP - 8) { lam[j] = nan(""); status |= ST_TRIAL_CAP; }
-      else { kk_s[j] = k; q_s[(cur_q ^ 1) * P + atomicAdd(&qn_s[cur_q ^ 1], 1)] = j; }
-    }
-    __syncthreads();
-    cur_q ^= 1; n_act = qn_s[cur_q]; first = false;
-    if (tid == 0) qn_s[cur_q ^ 1] = 0;
-    __syncthreads();
-  }
+  if (do_lambda) lambda_stage_cta<SL_T>(P, beta, lam, tau, 0.5 * alpha, L.key, gch, t, nullptr, q_s, P, qn_s, kk_s, status);
   status = __reduce_or_sync(0xffffffffu, status);
   if (lane == 0 && status) atomicOr(L.status + ch, status);
 }
