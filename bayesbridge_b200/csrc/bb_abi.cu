@@ -14,12 +14,7 @@
 #include <vector>
 
 #include "../../include/bayesbridge_b200.h"
-#include "bb_common.cuh"
-#include "bb_pre.cuh"
-#include "bb_stb.cuh"
-#include "bb_tri.cuh"
-#include "bb_ortho.cuh"
-#include "bb_stb_large.cuh"
+#include "bb_launch.h"
 
 namespace {
 
@@ -31,17 +26,11 @@ int g_verbose = 0;
 
 void set_err(const std::string& s) { g_err = s; }
 
-template <typename T>
-T* dalloc(size_t n) {
-  T* p = nullptr;
-  BB_CUDA_CHECK(cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)));
-  return p;
-}
-template <typename T>
-void dfree(T*& p) { if (p) cudaFree((void*)p); p = nullptr; }
+using bb::dalloc;
+using bb::dfree;
+using bb::check_launch;
 
 inline void launched(int n = 1) { g_launches += n; }
-inline void check_launch() { BB_CUDA_CHECK(cudaGetLastError()); }
 
 }  // namespace
 
@@ -85,94 +74,19 @@ void model_alloc(bb_model* m) {
   m->gc = dalloc<double>(P); m->bc = dalloc<double>(P); m->bz = dalloc<double>(P);
 }
 
-// G = [X y]'[X y] on the FP64 tensor cores.  X, y device pointers.
-void gram_device(const double* X, const double* y, int N, int P, double* G, cudaStream_t st) {
-  const int PA = P + 1;
-  const int nt = (PA + bb::GR_T - 1) / bb::GR_T;
-  const int ntile = nt * (nt + 1) / 2;
-  // split K so that the grid covers the 148 SMs a few times over
-  int nsplit = std::max(1, std::min((N + 4 * bb::GR_K - 1) / (4 * bb::GR_K), (148 * 4 + ntile - 1) / ntile));
-  int rows = (N + nsplit - 1) / nsplit;
-  rows = (rows + bb::GR_K - 1) / bb::GR_K * bb::GR_K;
-  nsplit = (N + rows - 1) / rows;
-  if (nsplit < 1) nsplit = 1;
-  double* part = dalloc<double>((size_t)nsplit * ntile * bb::GR_T * bb::GR_T);
-  bb::gram_kernel<<<dim3(ntile, 1, nsplit), 256, 0, st>>>(X, y, N, P, rows, part);
-  check_launch();
-  bb::gram_reduce_kernel<<<296, 256, 0, st>>>(part, P, nsplit, G);
-  check_launch();
-  launched(2);
-  BB_CUDA_CHECK(cudaStreamSynchronize(st));
-  dfree(part);
-}
-
-// round-robin tournament schedule: n even, n-1 rounds of n/2 pairs
-std::vector<int> tournament(int P, int& rounds, int& npairs) {
-  const int n = P + (P & 1);
-  rounds = n - 1; npairs = n / 2;
-  std::vector<int> out((size_t)rounds * npairs * 2);
-  std::vector<int> ring(n);
-  for (int i = 0; i < n; ++i) ring[i] = i;
-  for (int r = 0; r < rounds; ++r) {
-    for (int k = 0; k < npairs; ++k) {
-      int p = ring[k], q = ring[n - 1 - k];
-      if (p > q) std::swap(p, q);
-      if (q >= P) { p = -1; q = -1; }   // padding column
-      out[((size_t)r * npairs + k) * 2] = p; out[((size_t)r * npairs + k) * 2 + 1] = q;
-    }
-    // rotate all but the first
-    int last = ring[n - 1];
-    for (int i = n - 1; i > 1; --i) ring[i] = ring[i - 1];
-    ring[1] = last;
-  }
-  return out;
-}
-
-// One-sided Jacobi on W (M x P, destroyed): on return W = W0 V, V orthogonal, columns of W orthogonal.
-void jacobi_device(double* W, double* V, int M, int P, cudaStream_t st) {
-  int rounds, npairs;
-  std::vector<int> sched = tournament(P, rounds, npairs);
-  int* d_sched = dalloc<int>(sched.size());
-  BB_CUDA_CHECK(cudaMemcpyAsync(d_sched, sched.data(), sched.size() * sizeof(int), cudaMemcpyHostToDevice, st));
-  unsigned long long* d_conv = dalloc<unsigned long long>(1);
-  bb::set_identity_kernel<<<296, 256, 0, st>>>(V, P); check_launch(); launched();
-  for (int sweep = 0; sweep < 40 && P > 1; ++sweep) {
-    BB_CUDA_CHECK(cudaMemsetAsync(d_conv, 0, sizeof(unsigned long long), st));
-    for (int r = 0; r < rounds; ++r) {
-      bb::jacobi_round_kernel<<<npairs, 256, 0, st>>>(W, V, M, P, d_sched + (size_t)r * npairs * 2, d_conv);
-    }
-    check_launch(); launched(rounds);
-    unsigned long long conv = 0;
-    BB_CUDA_CHECK(cudaMemcpyAsync(&conv, d_conv, sizeof(conv), cudaMemcpyDeviceToHost, st));
-    BB_CUDA_CHECK(cudaStreamSynchronize(st));
-    if (conv == 0) break;   // no pair needed a rotation in this sweep
-  }
-  dfree(d_sched); dfree(d_conv);
-}
-
-double resid_device(const double* X, const double* y, const double* b, int N, int P, cudaStream_t st) {
-  const int nb = std::max(1, std::min(592, (N + 255) / 256));
-  double* part = dalloc<double>(nb);
-  bb::resid_kernel<<<nb, 256, 0, st>>>(X, y, b, N, P, part); check_launch(); launched();
-  std::vector<double> h(nb);
-  BB_CUDA_CHECK(cudaMemcpyAsync(h.data(), part, nb * sizeof(double), cudaMemcpyDeviceToHost, st));
-  BB_CUDA_CHECK(cudaStreamSynchronize(st));
-  dfree(part);
-  double s = 0; for (double v : h) s += v;
-  return s;
-}
-
 // After tV/Vc/Wc/d/a/mean/zc/d2, XX, Xy, bhat are in place: expansion centres and residuals.
 void model_finish(bb_model* m, bool have_rows) {
   const int P = m->P; cudaStream_t st = m->stream;
   // z-space centre zc -> beta-space bz = V zc
-  bb::vz_kernel<<<(P + 127) / 128, 128, 0, st>>>(m->Vc, m->zc, P, m->ldv, m->bz); check_launch(); launched();
+  launched(bb::vz_device(m->Vc, m->zc, P, m->ldv, m->bz, st));
   // beta-space centre for the stable path: bhat (0 if singular)
   BB_CUDA_CHECK(cudaMemcpyAsync(m->bc, m->bhat, P * sizeof(double), cudaMemcpyDeviceToDevice, st));
-  bb::grad_kernel<<<(P + 127) / 128, 128, 0, st>>>(m->XX, m->Xy, m->bc, P, m->gc); check_launch(); launched();
+  launched(bb::grad_device(m->XX, m->Xy, m->bc, P, m->gc, st));
   if (have_rows) {
-    m->r0z = resid_device(m->X, m->y, m->bz, m->N, P, st);
-    m->r0b = resid_device(m->X, m->y, m->bc, m->N, P, st);
+    int nl = 0;
+    m->r0z = bb::resid_device(m->X, m->y, m->bz, m->N, P, st, &nl);
+    m->r0b = bb::resid_device(m->X, m->y, m->bc, m->N, P, st, &nl);
+    launched(nl);
   }
 }
 
@@ -180,9 +94,9 @@ void model_finish(bb_model* m, bool have_rows) {
 void model_factor(bb_model* m, double* W, int M, bool w_is_gram) {
   const int P = m->P; cudaStream_t st = m->stream;
   double* V = dalloc<double>((size_t)P * P);
-  jacobi_device(W, V, M, P, st);
+  launched(bb::jacobi_device(W, V, M, P, st));
   double* nrm = dalloc<double>(P);
-  bb::colnorm_kernel<<<P, 128, 0, st>>>(W, M, P, nrm); check_launch(); launched();
+  launched(bb::colnorm_device(W, M, P, nrm, st));
   std::vector<double> h(P);
   BB_CUDA_CHECK(cudaMemcpyAsync(h.data(), nrm, P * sizeof(double), cudaMemcpyDeviceToHost, st));
   BB_CUDA_CHECK(cudaStreamSynchronize(st));
@@ -201,11 +115,10 @@ void model_factor(bb_model* m, double* W, int M, bool w_is_gram) {
   int* d_perm = dalloc<int>(P);
   BB_CUDA_CHECK(cudaMemcpyAsync(d_perm, perm.data(), P * sizeof(int), cudaMemcpyHostToDevice, st));
   BB_CUDA_CHECK(cudaMemcpyAsync(nrm, h.data(), P * sizeof(double), cudaMemcpyHostToDevice, st));
-  bb::derive_kernel<<<P, 128, 0, st>>>(V, d_perm, nrm, m->Xy, P, m->ldv, m->tV, m->Vc, m->Wc, m->d, m->a, m->mean, m->d2, m->zc);
-  check_launch(); launched();
+  launched(bb::derive_device(V, d_perm, nrm, m->Xy, P, m->ldv, m->tV, m->Vc, m->Wc, m->d, m->a, m->mean, m->d2, m->zc, st));
   // least squares start: V (a / d^2), or 0 when X'X is singular (BridgeRegression.cpp:79-91)
   if (m->singular) BB_CUDA_CHECK(cudaMemsetAsync(m->bhat, 0, P * sizeof(double), st));
-  else { bb::vz_kernel<<<(P + 127) / 128, 128, 0, st>>>(m->Vc, m->zc, P, m->ldv, m->bhat); check_launch(); launched(); }
+  else launched(bb::vz_device(m->Vc, m->zc, P, m->ldv, m->bhat, st));
   BB_CUDA_CHECK(cudaStreamSynchronize(st));
   dfree(V); dfree(nrm); dfree(d_perm);
 }
@@ -234,9 +147,9 @@ void model_take_rows(bb_model* m, const double* X, const double* y, int mem) {
 void model_gram(bb_model* m) {
   const int P = m->P;
   double* G = dalloc<double>((size_t)(P + 1) * (P + 1));
-  gram_device(m->X, m->y, m->N, P, G, m->stream);
+  launched(bb::gram_device(m->X, m->y, m->N, P, G, m->stream));
   double* d_yy = dalloc<double>(1);
-  bb::gram_unpack_kernel<<<296, 256, 0, m->stream>>>(G, P, m->XX, m->Xy, d_yy); check_launch(); launched();
+  launched(bb::gram_unpack(G, P, m->XX, m->Xy, d_yy, m->stream));
   BB_CUDA_CHECK(cudaMemcpyAsync(&m->yy, d_yy, sizeof(double), cudaMemcpyDeviceToHost, m->stream));
   BB_CUDA_CHECK(cudaStreamSynchronize(m->stream));
   dfree(G); dfree(d_yy);
@@ -318,60 +231,6 @@ __global__ void gather_kernel(const double* src, double* dst, int width, long lo
 
 void fill(double* p, size_t n, double v, cudaStream_t st) { fill_kernel<<<296, 256, 0, st>>>(p, n, v); check_launch(); launched(); }
 
-// ---------------- triangle launch: pick J (coordinates per lane) and C (chains per CTA) ----------------
-template <int J, int C>
-void launch_tri_jc(const bb::TriLaunch& L, int W, cudaStream_t st) {
-  const int threads = 32 * (W + C);
-  const size_t smem = ((size_t)2 * C * L.m.P + 2 * C * 32 + 4 * C) * sizeof(double);
-  const int grid = (L.nchains + C - 1) / C;
-  if (threads <= 384) {
-    auto kern = bb::tri_sweep_kernel<J, C, 384>;
-    BB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<grid, threads, smem, st>>>(L);
-  } else {
-    auto kern = bb::tri_sweep_kernel<J, C, 1024>;
-    BB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<grid, threads, smem, st>>>(L);
-  }
-  check_launch(); launched();
-}
-template <int J>
-void launch_tri_j(const bb::TriLaunch& L, int W, int C, cudaStream_t st) {
-  if (C >= 4) launch_tri_jc<J, 4>(L, W, st);
-  else if (C >= 2) launch_tri_jc<J, 2>(L, W, st);
-  else launch_tri_jc<J, 1>(L, W, st);
-}
-void launch_tri(const bb::TriLaunch& L, cudaStream_t st) {
-  const int P = L.m.P;
-  if (P > 8 * 32 * 24) throw std::string("tri: P too large for the on-chip sweep (max 6144)");
-  // compute warps W and coordinates per lane J with 32*W*J >= P
-  int W = std::min(8, (P + 31) / 32);
-  int J = (P + 32 * W - 1) / (32 * W);
-  while (J > 8) { W += 4; J = (P + 32 * W - 1) / (32 * W); }
-  const int Jt = J <= 1 ? 1 : J <= 2 ? 2 : J <= 4 ? 4 : 8;
-  // chains per CTA: fill the 148 SMs first, then stack chains (they share each column of V in registers)
-  int C = 1;
-  if (L.nchains > 148) C = 2;
-  if (L.nchains > 2 * 148) C = 4;
-  if (Jt == 8 && C > 2) C = 2;   // register budget
-  switch (Jt) {
-    case 1: launch_tri_j<1>(L, W, C, st); break;
-    case 2: launch_tri_j<2>(L, W, C, st); break;
-    case 4: launch_tri_j<4>(L, W, C, st); break;
-    default: launch_tri_j<8>(L, W, C, st); break;
-  }
-}
-
-template <int TB>
-void launch_stb_small(const bb::StbLaunch& L, cudaStream_t st) {
-  constexpr int PP = bb::STB_NB * TB;
-  const size_t smem = ((size_t)PP * PP + 2 * (PP + TB) + 4 * PP + 24 + 2) * sizeof(double) + (size_t)(2 * PP + 2 + PP + 2) * sizeof(int) + (size_t)PP * sizeof(bb::RetConst);
-  auto kern = bb::stb_small_kernel<TB>;
-  BB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<L.nchains, bb::STB_THREADS, smem, st>>>(L);
-  check_launch(); launched();
-}
-
 }  // namespace
 
 // ===========================================================================================
@@ -399,22 +258,14 @@ void chains_run(bb_chains* c, const bb_hyper* hh, unsigned iter0, int niter, int
     L.pre_tau = pre_tau; L.pre_sig2 = pre_sig2; L.stages = stages;
     L.beta = c->beta; L.u = c->u; L.aux = c->aux; L.shape = c->shape; L.sig2 = c->sig2; L.tau = c->tau; L.alpha = c->alpha; L.status = c->status;
     L.sink = make_sink(c, thin, slot0);
-    const size_t smem = ((size_t)4 * P + 24 + 4) * sizeof(double) + ((size_t)3 * P + 2) * sizeof(int);
-    if (c->method == BB_TRI) {
-      BB_CUDA_CHECK(cudaFuncSetAttribute(bb::ortho_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      bb::ortho_kernel<false><<<c->nchains, bb::ORT_T, smem, st>>>(L);
-    } else {
-      BB_CUDA_CHECK(cudaFuncSetAttribute(bb::ortho_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      bb::ortho_kernel<true><<<c->nchains, bb::ORT_T, smem, st>>>(L);
-    }
-    check_launch(); launched();
+    launched(bb::launch_ortho(L, c->method != BB_TRI, st));
   } else if (c->method == BB_TRI) {
     bb::TriLaunch L;
     L.m = m->view(); L.h = h; L.key = key; L.nchains = c->nchains; L.chain0 = c->chain0; L.iter0 = iter0; L.niter = niter;
     L.pre_tau = pre_tau; L.init_z = c->z_valid ? 0 : 1; L.stages = stages;
     L.beta = c->beta; L.u = c->u; L.omega = c->aux; L.shape = c->shape; L.z = c->z; L.sig2 = c->sig2; L.tau = c->tau; L.alpha = c->alpha;
     L.status = c->status; L.sink = make_sink(c, thin, slot0);
-    launch_tri(L, st);
+    launched(bb::launch_tri(L, st));
     c->z_valid = (stages & BB_ST_BETA) != 0 || c->z_valid;
   } else if (P <= 128) {
     bb::StbLaunch L;
@@ -422,36 +273,19 @@ void chains_run(bb_chains* c, const bb_hyper* hh, unsigned iter0, int niter, int
     L.pre_tau = pre_tau; L.stages = stages;
     L.beta = c->beta; L.lambda = c->aux; L.sig2 = c->sig2; L.tau = c->tau; L.alpha = c->alpha; L.status = c->status;
     L.sink = make_sink(c, thin, slot0);
-    if (P <= 64) launch_stb_small<4>(L, st); else launch_stb_small<8>(L, st);
+    launched(bb::launch_stb_small(L, st));
   } else {
     if (!c->A) { c->A = dalloc<double>((size_t)c->nchains * P * P); c->sdel = dalloc<double>((size_t)c->nchains * P); }
     bb::StbLargeLaunch L;
     L.m = m->view(); L.h = h; L.key = key; L.nchains = c->nchains; L.chain0 = c->chain0; L.stages = stages;
     L.beta = c->beta; L.lambda = c->aux; L.sig2 = c->sig2; L.tau = c->tau; L.alpha = c->alpha; L.status = c->status;
     L.A = c->A; L.sdel = c->sdel; L.sink = make_sink(c, thin, slot0);
-    const size_t smem_sc = ((size_t)P + 26) * sizeof(double) + ((size_t)3 * P + 2) * sizeof(int);
-    const size_t smem_sv = (size_t)P * sizeof(double);
-    BB_CUDA_CHECK(cudaFuncSetAttribute(bb::stbl_scalar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sc));
-    BB_CUDA_CHECK(cudaFuncSetAttribute(bb::stbl_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));
-    const size_t smem_sy = (size_t)2 * bb::SL_NB * bb::SL_LD * sizeof(double);
-    BB_CUDA_CHECK(cudaFuncSetAttribute(bb::stbl_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
-    const int nblk = (P + bb::SL_NB - 1) / bb::SL_NB;
+    bb::stb_large_prepare(P);
     for (int it = -pre_tau; it < niter; ++it) {
       L.pre = it < 0; L.iter = iter0 + (it < 0 ? 0 : it);
       const bool store = c->nslots > 0 && thin > 0 && it >= 0 && ((it + 1) % thin) == 0;
       L.slot = store ? slot0 + (it + 1) / thin - 1 : -1;
-      bb::stbl_scalar_kernel<<<c->nchains, bb::SL_T, smem_sc, st>>>(L); launched();
-      if (L.pre || !(stages & BB_ST_BETA)) continue;
-      bb::stbl_build_kernel<<<dim3(64, c->nchains), 256, 0, st>>>(L); launched();
-      for (int kb = 0; kb < nblk; ++kb) {
-        bb::stbl_potrf_kernel<<<c->nchains, bb::SL_T, 0, st>>>(c->A, P, kb, c->status); launched();
-        const int rem = nblk - kb - 1;
-        if (rem > 0) {
-          bb::stbl_trsm_kernel<<<dim3(rem, c->nchains), bb::SL_NB, 0, st>>>(c->A, P, kb); launched();
-          bb::stbl_syrk_kernel<<<dim3(rem * (rem + 1) / 2, c->nchains), 256, smem_sy, st>>>(c->A, P, kb); launched();
-        }
-      }
-      bb::stbl_solve_kernel<<<c->nchains, bb::SL_T, smem_sv, st>>>(L); launched();
+      launched(bb::launch_stb_large_iter(L, (stages & BB_ST_BETA) != 0, st));
     }
     check_launch();
   }
@@ -525,9 +359,9 @@ bb_model* bb_model_create_factors(const double* X, const double* y, int N, int P
     BB_CUDA_CHECK(cudaMemcpyAsync(m->tV, tV, (size_t)P * P * sizeof(double), cudaMemcpyHostToDevice, st));
     BB_CUDA_CHECK(cudaMemcpyAsync(m->d, d, P * sizeof(double), cudaMemcpyHostToDevice, st));
     BB_CUDA_CHECK(cudaMemcpyAsync(m->a, a, P * sizeof(double), cudaMemcpyHostToDevice, st));
-    bb::derive_from_tv_kernel<<<P, 128, 0, st>>>(m->tV, m->d, m->a, P, m->ldv, m->Vc, m->Wc, m->mean, m->d2, m->zc); check_launch(); launched();
+    launched(bb::derive_from_tv_device(m->tV, m->d, m->a, P, m->ldv, m->Vc, m->Wc, m->mean, m->d2, m->zc, st));
     if (bhat) BB_CUDA_CHECK(cudaMemcpyAsync(m->bhat, bhat, P * sizeof(double), cudaMemcpyHostToDevice, st));
-    else { bb::vz_kernel<<<(P + 127) / 128, 128, 0, st>>>(m->Vc, m->zc, P, m->ldv, m->bhat); check_launch(); launched(); }
+    else launched(bb::vz_device(m->Vc, m->zc, P, m->ldv, m->bhat, st));
     model_finish(m, true);
     BB_CUDA_CHECK(cudaStreamSynchronize(st));
   });
@@ -538,7 +372,7 @@ bb_model* bb_model_create_factors(const double* X, const double* y, int N, int P
 int bb_gram(const double* X_dev, const double* y_dev, int n_rows, int P, double* G_dev, int device) {
   return guarded([&] {
     BB_CUDA_CHECK(cudaSetDevice(device));
-    gram_device(X_dev, y_dev, n_rows, P, G_dev, nullptr);
+    launched(bb::gram_device(X_dev, y_dev, n_rows, P, G_dev, nullptr));
   });
 }
 
@@ -549,7 +383,7 @@ bb_model* bb_model_create_gram(const double* G_dev, int N, int P, int device) {
     m = model_new(N, P, device);
     if (!m) throw std::string(g_err);
     double* d_yy = dalloc<double>(1);
-    bb::gram_unpack_kernel<<<296, 256, 0, m->stream>>>(G_dev, P, m->XX, m->Xy, d_yy); check_launch(); launched();
+    launched(bb::gram_unpack(G_dev, P, m->XX, m->Xy, d_yy, m->stream));
     BB_CUDA_CHECK(cudaMemcpyAsync(&m->yy, d_yy, sizeof(double), cudaMemcpyDeviceToHost, m->stream));
     double* W = dalloc<double>((size_t)P * P);
     BB_CUDA_CHECK(cudaMemcpyAsync(W, m->XX, (size_t)P * P * sizeof(double), cudaMemcpyDeviceToDevice, m->stream));
@@ -568,7 +402,9 @@ bb_model* bb_model_create_gram(const double* G_dev, int N, int P, int device) {
 int bb_model_resid_partial(const bb_model* m, const double* X_dev, const double* y_dev, int n_rows, double* out_dev) {
   return guarded([&] {
     BB_CUDA_CHECK(cudaSetDevice(m->device));
-    const double r[2] = {resid_device(X_dev, y_dev, m->bz, n_rows, m->P, m->stream), resid_device(X_dev, y_dev, m->bc, n_rows, m->P, m->stream)};
+    int nl = 0;
+    const double r[2] = {bb::resid_device(X_dev, y_dev, m->bz, n_rows, m->P, m->stream, &nl), bb::resid_device(X_dev, y_dev, m->bc, n_rows, m->P, m->stream, &nl)};
+    launched(nl);
     BB_CUDA_CHECK(cudaMemcpy(out_dev, r, 2 * sizeof(double), cudaMemcpyHostToDevice));
   });
 }

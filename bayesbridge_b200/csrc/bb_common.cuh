@@ -86,4 +86,11 @@ __device__ __forceinline__ double warp_sum(double v) {
   return v;
 }
 
+// FP64 tensor-core MMA (DMMA): D(8x8) += A(8x4, row) B(4x8, col).  Lane l holds A[l/4][l%4], B[l%4][l/4],
+// C[l/4][2(l%4) + {0,1}].
+__device__ __forceinline__ void dmma_m8n8k4(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
 }  // namespace bb

@@ -1,0 +1,103 @@
+// bb_launch.h -- launch descriptors and the host-side launchers of every kernel family.
+// Each family lives in its own translation unit (bb_tri.cu, bb_stb.cu, bb_stb_large.cu,
+// bb_ortho.cu, bb_pre.cu) so that nvcc can build them in parallel; bb_abi.cu holds the C ABI.
+#pragma once
+#include "bb_common.cuh"
+
+namespace bb {
+
+struct TriLaunch {
+  DeviceModel m;
+  Hyper h;
+  RngKey key;
+  int nchains;        // chains in this launch
+  uint32_t chain0;    // global id of local chain 0 (Philox counter word 3)
+  uint32_t iter0;     // Gibbs iteration index of the first iteration of this launch
+  int niter;
+  int pre_tau;        // draw tau once before the first iteration (BridgeWrapper.cpp:142)
+  int init_z;         // 1: z = V'beta is formed from beta (BridgeRegression.cpp:246); 0: read from state
+  int stages;         // BB_ST_* mask: which conditionals run (all = the full sweep)
+  // chain state, in/out: [nchains][P] and [nchains]
+  double *beta, *u, *omega, *shape, *z;
+  double *sig2, *tau, *alpha;
+  uint32_t* status;
+  DrawSink sink;
+};
+
+struct StbLaunch {
+  DeviceModel m;
+  Hyper h;
+  RngKey key;
+  int nchains;
+  uint32_t chain0;
+  uint32_t iter0;
+  int niter;
+  int pre_tau;     // draw tau once before the first iteration (BridgeWrapper.cpp:262)
+  int stages;      // BB_ST_* mask
+  double *beta, *lambda;          // state [nchains][P]
+  double *sig2, *tau, *alpha;     // state [nchains]
+  uint32_t* status;
+  DrawSink sink;
+};
+
+struct OrthoLaunch {
+  DeviceModel m;
+  Hyper h;
+  RngKey key;
+  int nchains;
+  uint32_t chain0, iter0;
+  int niter, pre_tau, pre_sig2, stages;
+  double *beta, *u, *aux, *shape;   // aux = omega (tri) | lambda (stb)
+  double *sig2, *tau, *alpha;
+  uint32_t* status;
+  DrawSink sink;
+};
+
+struct StbLargeLaunch {
+  DeviceModel m;
+  Hyper h;
+  RngKey key;
+  int nchains;
+  uint32_t chain0, iter;   // iteration index of THIS iteration
+  int pre;                 // 1: only the tau pre-draw
+  int stages;
+  double *beta, *lambda, *sig2, *tau, *alpha;
+  uint32_t* status;
+  double* A;               // [nchains][P][P] column-major workspace (lower triangle holds L)
+  double* sdel;            // [nchains][P] scratch: X'X (beta - bc)
+  DrawSink sink;
+  long long slot;          // sink slot for this iteration, -1 = do not store
+};
+
+// ---- host launchers; each returns the number of kernel launches it issued ----
+int launch_tri(const TriLaunch& L, cudaStream_t st);                       // bb_tri.cu
+int launch_stb_small(const StbLaunch& L, cudaStream_t st);                 // bb_stb.cu   (P <= 128)
+int launch_ortho(const OrthoLaunch& L, bool stable, cudaStream_t st);      // bb_ortho.cu
+// one iteration of the large-P stable sweep (P > 128); `store_slot` < 0: no draw is stored
+int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st);   // bb_stb_large.cu
+void stb_large_prepare(int P);                                             // opt-in shared memory sizes, once per P
+
+// ---- one-time precompute (bb_pre.cu) ----
+int gram_device(const double* X, const double* y, int N, int P, double* G, cudaStream_t st);   // G = [X y]'[X y]
+int gram_unpack(const double* G, int P, double* XX, double* Xy, double* yy_dev, cudaStream_t st);
+int jacobi_device(double* W, double* V, int M, int P, cudaStream_t st);
+double resid_device(const double* X, const double* y, const double* b, int N, int P, cudaStream_t st, int* launches);
+int colnorm_device(const double* W, int M, int P, double* nrm, cudaStream_t st);
+int derive_device(const double* V, const int* perm, const double* dsrc, const double* Xy, int P, int ldv, double* tV, double* Vc,
+                  double* Wc, double* d, double* a, double* mean, double* d2, double* zc, cudaStream_t st);
+int derive_from_tv_device(const double* tV, const double* d, const double* a, int P, int ldv, double* Vc, double* Wc, double* mean,
+                          double* d2, double* zc, cudaStream_t st);
+int vz_device(const double* Vc, const double* z, int P, int ldv, double* out, cudaStream_t st);
+int grad_device(const double* XX, const double* Xy, const double* b, int P, double* g, cudaStream_t st);
+
+template <typename T>
+inline T* dalloc(size_t n) {
+  T* p = nullptr;
+  BB_CUDA_CHECK(cudaMalloc(&p, (n > 0 ? n : 1) * sizeof(T)));
+  return p;
+}
+template <typename T>
+inline void dfree(T*& p) { if (p) cudaFree((void*)p); p = nullptr; }
+inline void check_launch() { BB_CUDA_CHECK(cudaGetLastError()); }
+
+}  // namespace bb

@@ -10,23 +10,11 @@
 // XX_sub[j] beta_-j = s_j - XX_jj beta_j (the reference forms it by a gemm at :382) and
 // ||y - X beta||^2 = r0 - 2 d'g + d'(s - XX bc),  d = beta - bc.
 #pragma once
-#include "bb_common.cuh"
+#include "bb_launch.h"
 #include "bb_retstable.cuh"
 
 namespace bb {
 
-struct OrthoLaunch {
-  DeviceModel m;
-  Hyper h;
-  RngKey key;
-  int nchains;
-  uint32_t chain0, iter0;
-  int niter, pre_tau, pre_sig2, stages;
-  double *beta, *u, *aux, *shape;   // aux = omega (tri) | lambda (stb)
-  double *sig2, *tau, *alpha;
-  uint32_t* status;
-  DrawSink sink;
-};
 
 constexpr int ORT_T = 256;
 

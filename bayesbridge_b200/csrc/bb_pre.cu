@@ -1,0 +1,118 @@
+// bb_pre.cu -- host side of the one-time precompute kernels (bb_pre.cuh): Gram build, one-sided
+// Jacobi SVD, derived layouts (the role of the BridgeRegression constructor, BridgeRegression.cpp:13-69).
+#include <algorithm>
+#include <vector>
+#include "bb_pre.cuh"
+
+namespace bb {
+
+// G = [X y]'[X y] on the FP64 tensor cores.  X, y device pointers.
+int gram_device(const double* X, const double* y, int N, int P, double* G, cudaStream_t st) {
+  const int PA = P + 1;
+  const int nt = (PA + GR_T - 1) / GR_T;
+  const int ntile = nt * (nt + 1) / 2;
+  // split K so that the grid covers the 148 SMs a few times over
+  int nsplit = std::max(1, std::min((N + 4 * GR_K - 1) / (4 * GR_K), (148 * 4 + ntile - 1) / ntile));
+  int rows = (N + nsplit - 1) / nsplit;
+  rows = (rows + GR_K - 1) / GR_K * GR_K;
+  nsplit = (N + rows - 1) / rows;
+  if (nsplit < 1) nsplit = 1;
+  double* part = dalloc<double>((size_t)nsplit * ntile * GR_T * GR_T);
+  gram_kernel<<<dim3(ntile, 1, nsplit), 256, 0, st>>>(X, y, N, P, rows, part);
+  check_launch();
+  gram_reduce_kernel<<<296, 256, 0, st>>>(part, P, nsplit, G);
+  check_launch();
+  BB_CUDA_CHECK(cudaStreamSynchronize(st));
+  dfree(part);
+  return 2;
+}
+
+int gram_unpack(const double* G, int P, double* XX, double* Xy, double* yy_dev, cudaStream_t st) {
+  gram_unpack_kernel<<<296, 256, 0, st>>>(G, P, XX, Xy, yy_dev); check_launch();
+  return 1;
+}
+
+namespace {
+// round-robin tournament schedule: n even, n-1 rounds of n/2 pairs
+std::vector<int> tournament(int P, int& rounds, int& npairs) {
+  const int n = P + (P & 1);
+  rounds = n - 1; npairs = n / 2;
+  std::vector<int> out((size_t)rounds * npairs * 2);
+  std::vector<int> ring(n);
+  for (int i = 0; i < n; ++i) ring[i] = i;
+  for (int r = 0; r < rounds; ++r) {
+    for (int k = 0; k < npairs; ++k) {
+      int p = ring[k], q = ring[n - 1 - k];
+      if (p > q) std::swap(p, q);
+      if (q >= P) { p = -1; q = -1; }   // padding column
+      out[((size_t)r * npairs + k) * 2] = p; out[((size_t)r * npairs + k) * 2 + 1] = q;
+    }
+    // rotate all but the first
+    int last = ring[n - 1];
+    for (int i = n - 1; i > 1; --i) ring[i] = ring[i - 1];
+    ring[1] = last;
+  }
+  return out;
+}
+}  // namespace
+
+// One-sided Jacobi on W (M x P, destroyed): on return W = W0 V, V orthogonal, columns of W orthogonal.
+int jacobi_device(double* W, double* V, int M, int P, cudaStream_t st) {
+  int rounds, npairs, n = 0;
+  std::vector<int> sched = tournament(P, rounds, npairs);
+  int* d_sched = dalloc<int>(sched.size());
+  BB_CUDA_CHECK(cudaMemcpyAsync(d_sched, sched.data(), sched.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+  unsigned long long* d_conv = dalloc<unsigned long long>(1);
+  set_identity_kernel<<<296, 256, 0, st>>>(V, P); check_launch(); ++n;
+  for (int sweep = 0; sweep < 40 && P > 1; ++sweep) {
+    BB_CUDA_CHECK(cudaMemsetAsync(d_conv, 0, sizeof(unsigned long long), st));
+    for (int r = 0; r < rounds; ++r) {
+      jacobi_round_kernel<<<npairs, 256, 0, st>>>(W, V, M, P, d_sched + (size_t)r * npairs * 2, d_conv);
+    }
+    check_launch(); n += rounds;
+    unsigned long long conv = 0;
+    BB_CUDA_CHECK(cudaMemcpyAsync(&conv, d_conv, sizeof(conv), cudaMemcpyDeviceToHost, st));
+    BB_CUDA_CHECK(cudaStreamSynchronize(st));
+    if (conv == 0) break;   // no pair needed a rotation in this sweep
+  }
+  dfree(d_sched); dfree(d_conv);
+  return n;
+}
+
+double resid_device(const double* X, const double* y, const double* b, int N, int P, cudaStream_t st, int* launches) {
+  const int nb = std::max(1, std::min(592, (N + 255) / 256));
+  double* part = dalloc<double>(nb);
+  resid_kernel<<<nb, 256, 0, st>>>(X, y, b, N, P, part); check_launch();
+  if (launches) *launches += 1;
+  std::vector<double> h(nb);
+  BB_CUDA_CHECK(cudaMemcpyAsync(h.data(), part, nb * sizeof(double), cudaMemcpyDeviceToHost, st));
+  BB_CUDA_CHECK(cudaStreamSynchronize(st));
+  dfree(part);
+  double s = 0; for (double v : h) s += v;
+  return s;
+}
+
+int colnorm_device(const double* W, int M, int P, double* nrm, cudaStream_t st) {
+  colnorm_kernel<<<P, 128, 0, st>>>(W, M, P, nrm); check_launch();
+  return 1;
+}
+int derive_device(const double* V, const int* perm, const double* dsrc, const double* Xy, int P, int ldv, double* tV, double* Vc,
+                  double* Wc, double* d, double* a, double* mean, double* d2, double* zc, cudaStream_t st) {
+  derive_kernel<<<P, 128, 0, st>>>(V, perm, dsrc, Xy, P, ldv, tV, Vc, Wc, d, a, mean, d2, zc); check_launch();
+  return 1;
+}
+int derive_from_tv_device(const double* tV, const double* d, const double* a, int P, int ldv, double* Vc, double* Wc, double* mean,
+                          double* d2, double* zc, cudaStream_t st) {
+  derive_from_tv_kernel<<<P, 128, 0, st>>>(tV, d, a, P, ldv, Vc, Wc, mean, d2, zc); check_launch();
+  return 1;
+}
+int vz_device(const double* Vc, const double* z, int P, int ldv, double* out, cudaStream_t st) {
+  vz_kernel<<<(P + 127) / 128, 128, 0, st>>>(Vc, z, P, ldv, out); check_launch();
+  return 1;
+}
+int grad_device(const double* XX, const double* Xy, const double* b, int P, double* g, cudaStream_t st) {
+  grad_kernel<<<(P + 127) / 128, 128, 0, st>>>(XX, Xy, b, P, g); check_launch();
+  return 1;
+}
+
+}  // namespace bb

@@ -7,7 +7,7 @@
 //   derive_kernel    tV / Vc / Wc layouts, mean = a/d^2 (:268), d^2, zc
 //   resid_kernel     || y - X b ||^2 for the rss expansions
 #pragma once
-#include "bb_common.cuh"
+#include "bb_launch.h"
 
 namespace bb {
 
@@ -20,11 +20,6 @@ namespace bb {
 constexpr int GR_T = 64;    // tile edge
 constexpr int GR_K = 32;    // k chunk
 constexpr int GR_LD = 36;   // smem leading dimension (doubles): 2-way = minimal bank pattern for 8-byte lanes
-
-__device__ __forceinline__ void dmma_m8n8k4(double& c0, double& c1, double a, double b) {
-  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
-               : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
-}
 
 __global__ void __launch_bounds__(256) gram_kernel(const double* __restrict__ X, const double* __restrict__ y,
                                                    int N, int P, int rows_per_split, double* __restrict__ part) {

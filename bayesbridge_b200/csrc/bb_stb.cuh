@@ -16,26 +16,11 @@
 // lambda: round-based tilted-stable draws; unfinished coordinates are compacted into a smem retry
 // queue between rounds so that finished lanes do not idle the warp (bb_retstable.cuh).
 #pragma once
-#include "bb_common.cuh"
+#include "bb_launch.h"
 #include "bb_retstable.cuh"
 
 namespace bb {
 
-struct StbLaunch {
-  DeviceModel m;
-  Hyper h;
-  RngKey key;
-  int nchains;
-  uint32_t chain0;
-  uint32_t iter0;
-  int niter;
-  int pre_tau;     // draw tau once before the first iteration (BridgeWrapper.cpp:262)
-  int stages;      // BB_ST_* mask
-  double *beta, *lambda;          // state [nchains][P]
-  double *sig2, *tau, *alpha;     // state [nchains]
-  uint32_t* status;
-  DrawSink sink;
-};
 
 constexpr int STB_NB = 16;                                   // tiles per dimension
 constexpr int STB_TILES = STB_NB * (STB_NB + 1) / 2;         // 136 lower-triangular tiles

@@ -1,0 +1,38 @@
+// bb_stb_large.cu -- host side of the large-P stable sweep (bb_stb_large.cuh): one Gibbs iteration =
+// scalar stage, build, blocked Cholesky (potrf / trsm / DMMA syrk per block column), solve.
+#include "bb_stb_large.cuh"
+
+namespace bb {
+
+void stb_large_prepare(int P) {
+  const size_t smem_sc = ((size_t)P + 26) * sizeof(double) + ((size_t)3 * P + 2) * sizeof(int);
+  const size_t smem_sv = (size_t)P * sizeof(double);
+  const size_t smem_sy = (size_t)2 * SL_NB * SL_LD * sizeof(double);
+  BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_scalar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sc));
+  BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));
+  BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
+}
+
+int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
+  const int P = L.m.P, nch = L.nchains;
+  const size_t smem_sc = ((size_t)P + 26) * sizeof(double) + ((size_t)3 * P + 2) * sizeof(int);
+  const size_t smem_sv = (size_t)P * sizeof(double);
+  const size_t smem_sy = (size_t)2 * SL_NB * SL_LD * sizeof(double);
+  const int nblk = (P + SL_NB - 1) / SL_NB;
+  int n = 0;
+  stbl_scalar_kernel<<<nch, SL_T, smem_sc, st>>>(L); ++n;
+  if (L.pre || !beta_stage) return n;
+  stbl_build_kernel<<<dim3(64, nch), 256, 0, st>>>(L); ++n;
+  for (int kb = 0; kb < nblk; ++kb) {
+    stbl_potrf_kernel<<<nch, SL_T, 0, st>>>(L.A, P, kb, L.status); ++n;
+    const int rem = nblk - kb - 1;
+    if (rem > 0) {
+      stbl_trsm_kernel<<<dim3(rem, nch), SL_NB, 0, st>>>(L.A, P, kb); ++n;
+      stbl_syrk_kernel<<<dim3(rem * (rem + 1) / 2, nch), 256, smem_sy, st>>>(L.A, P, kb); ++n;
+    }
+  }
+  stbl_solve_kernel<<<nch, SL_T, smem_sv, st>>>(L); ++n;
+  return n;
+}
+
+}  // namespace bb

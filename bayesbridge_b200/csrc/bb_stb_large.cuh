@@ -7,27 +7,11 @@
 //   stbl_potrf_kernel / stbl_trsm_kernel / stbl_syrk_kernel : chol(A_c)   (:559-560)
 //   stbl_solve_kernel  : beta = L^-T (L^-1 Xy + sig eps)              (:563-574)
 #pragma once
-#include "bb_common.cuh"
-#include "bb_pre.cuh"
+#include "bb_launch.h"
 #include "bb_retstable.cuh"
 
 namespace bb {
 
-struct StbLargeLaunch {
-  DeviceModel m;
-  Hyper h;
-  RngKey key;
-  int nchains;
-  uint32_t chain0, iter;   // iteration index of THIS iteration
-  int pre;                 // 1: only the tau pre-draw
-  int stages;
-  double *beta, *lambda, *sig2, *tau, *alpha;
-  uint32_t* status;
-  double* A;               // [nchains][P][P] column-major workspace (lower triangle holds L)
-  double* sdel;            // [nchains][P] scratch: X'X (beta - bc)
-  DrawSink sink;
-  long long slot;          // sink slot for this iteration, -1 = do not store
-};
 
 constexpr int SL_NB = 64;
 constexpr int SL_T = 256;

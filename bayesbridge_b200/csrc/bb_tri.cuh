@@ -24,27 +24,10 @@
 #pragma once
 #include <cfloat>
 #include <math_constants.h>
-#include "bb_common.cuh"
+#include "bb_launch.h"
 
 namespace bb {
 
-struct TriLaunch {
-  DeviceModel m;
-  Hyper h;
-  RngKey key;
-  int nchains;        // chains in this launch
-  uint32_t chain0;    // global id of local chain 0 (Philox counter word 3)
-  uint32_t iter0;     // Gibbs iteration index of the first iteration of this launch
-  int niter;
-  int pre_tau;        // draw tau once before the first iteration (BridgeWrapper.cpp:142)
-  int init_z;         // 1: z = V'beta is formed from beta (BridgeRegression.cpp:246); 0: read from state
-  int stages;         // BB_ST_* mask: which conditionals run (all = the full sweep)
-  // chain state, in/out: [nchains][P] and [nchains]
-  double *beta, *u, *omega, *shape, *z;
-  double *sig2, *tau, *alpha;
-  uint32_t* status;
-  DrawSink sink;
-};
 
 template <int J, int C, int MAXT>
 __global__ void __launch_bounds__(MAXT, 1) tri_sweep_kernel(const TriLaunch L) {
