@@ -41,7 +41,7 @@ struct bb_model {
   int device = 0, N = 0, P = 0, ldv = 0;
   bool own_X = false;
   double *X = nullptr, *y = nullptr;   // may be null (Gram-only construction)
-  double *XX = nullptr, *Xy = nullptr, *bhat = nullptr, *tV = nullptr, *Vc = nullptr, *Wc = nullptr;
+  double *XX = nullptr, *Xy = nullptr, *bhat = nullptr, *tV = nullptr, *Vc = nullptr, *VQ = nullptr;
   double *d = nullptr, *a = nullptr, *mean = nullptr, *zc = nullptr, *d2 = nullptr, *gc = nullptr, *bc = nullptr, *bz = nullptr;
   double r0z = 0, r0b = 0, yy = 0;
   bool singular = false;
@@ -50,14 +50,14 @@ struct bb_model {
 
   bb::DeviceModel view() const {
     bb::DeviceModel m;
-    m.N = N; m.P = P; m.ldv = ldv; m.X = X; m.y = y; m.XX = XX; m.Xy = Xy; m.bhat = bhat; m.tV = tV; m.Vc = Vc; m.Wc = Wc;
+    m.N = N; m.P = P; m.ldv = ldv; m.X = X; m.y = y; m.XX = XX; m.Xy = Xy; m.bhat = bhat; m.tV = tV; m.Vc = Vc; m.VQ = VQ;
     m.d = d; m.mean = mean; m.zc = zc; m.d2 = d2; m.gc = gc; m.bc = bc; m.r0z = r0z; m.r0b = r0b; m.yy = yy;
     return m;
   }
   ~bb_model() {
     cudaSetDevice(device);
     if (own_X) { dfree(X); dfree(y); }
-    dfree(XX); dfree(Xy); dfree(bhat); dfree(tV); dfree(Vc); dfree(Wc); dfree(d); dfree(a); dfree(mean); dfree(zc); dfree(d2);
+    dfree(XX); dfree(Xy); dfree(bhat); dfree(tV); dfree(Vc); dfree(VQ); dfree(d); dfree(a); dfree(mean); dfree(zc); dfree(d2);
     dfree(gc); dfree(bc); dfree(bz);
     if (stream) cudaStreamDestroy(stream);
   }
@@ -69,12 +69,12 @@ void model_alloc(bb_model* m) {
   const size_t P = m->P;
   m->ldv = (int)((P + 31) / 32 * 32);
   m->XX = dalloc<double>(P * P); m->Xy = dalloc<double>(P); m->bhat = dalloc<double>(P);
-  m->tV = dalloc<double>(P * P); m->Vc = dalloc<double>(P * m->ldv); m->Wc = dalloc<double>(P * m->ldv);
+  m->tV = dalloc<double>(P * P); m->Vc = dalloc<double>(P * m->ldv); m->VQ = dalloc<double>(2 * P * m->ldv);
   m->d = dalloc<double>(P); m->a = dalloc<double>(P); m->mean = dalloc<double>(P); m->zc = dalloc<double>(P); m->d2 = dalloc<double>(P);
   m->gc = dalloc<double>(P); m->bc = dalloc<double>(P); m->bz = dalloc<double>(P);
 }
 
-// After tV/Vc/Wc/d/a/mean/zc/d2, XX, Xy, bhat are in place: expansion centres and residuals.
+// After tV/Vc/VQ/d/a/mean/zc/d2, XX, Xy, bhat are in place: expansion centres and residuals.
 void model_finish(bb_model* m, bool have_rows) {
   const int P = m->P; cudaStream_t st = m->stream;
   // z-space centre zc -> beta-space bz = V zc
@@ -115,7 +115,7 @@ void model_factor(bb_model* m, double* W, int M, bool w_is_gram) {
   int* d_perm = dalloc<int>(P);
   BB_CUDA_CHECK(cudaMemcpyAsync(d_perm, perm.data(), P * sizeof(int), cudaMemcpyHostToDevice, st));
   BB_CUDA_CHECK(cudaMemcpyAsync(nrm, h.data(), P * sizeof(double), cudaMemcpyHostToDevice, st));
-  launched(bb::derive_device(V, d_perm, nrm, m->Xy, P, m->ldv, m->tV, m->Vc, m->Wc, m->d, m->a, m->mean, m->d2, m->zc, st));
+  launched(bb::derive_device(V, d_perm, nrm, m->Xy, P, m->ldv, m->tV, m->Vc, m->VQ, m->d, m->a, m->mean, m->d2, m->zc, st));
   // least squares start: V (a / d^2), or 0 when X'X is singular (BridgeRegression.cpp:79-91)
   if (m->singular) BB_CUDA_CHECK(cudaMemsetAsync(m->bhat, 0, P * sizeof(double), st));
   else launched(bb::vz_device(m->Vc, m->zc, P, m->ldv, m->bhat, st));
@@ -359,7 +359,7 @@ bb_model* bb_model_create_factors(const double* X, const double* y, int N, int P
     BB_CUDA_CHECK(cudaMemcpyAsync(m->tV, tV, (size_t)P * P * sizeof(double), cudaMemcpyHostToDevice, st));
     BB_CUDA_CHECK(cudaMemcpyAsync(m->d, d, P * sizeof(double), cudaMemcpyHostToDevice, st));
     BB_CUDA_CHECK(cudaMemcpyAsync(m->a, a, P * sizeof(double), cudaMemcpyHostToDevice, st));
-    launched(bb::derive_from_tv_device(m->tV, m->d, m->a, P, m->ldv, m->Vc, m->Wc, m->mean, m->d2, m->zc, st));
+    launched(bb::derive_from_tv_device(m->tV, m->d, m->a, P, m->ldv, m->Vc, m->VQ, m->mean, m->d2, m->zc, st));
     if (bhat) BB_CUDA_CHECK(cudaMemcpyAsync(m->bhat, bhat, P * sizeof(double), cudaMemcpyHostToDevice, st));
     else launched(bb::vz_device(m->Vc, m->zc, P, m->ldv, m->bhat, st));
     model_finish(m, true);

@@ -23,7 +23,7 @@ struct CudaError { cudaError_t code; explicit CudaError(cudaError_t c) : code(c)
 // /root/reference/Code/C/BridgeRegression.cpp:13-69).  All column-major doubles.
 struct DeviceModel {
   int N, P;
-  int ldv;             // leading dimension of Vc / Wc (P rounded up to a multiple of 32)
+  int ldv;             // leading dimension of Vc / VQ (P rounded up to a multiple of 32)
   const double* X;     // N x P   (may be null when built from a Gram matrix only)
   const double* y;     // N
   const double* XX;    // P x P   X'X                         (:24)
@@ -31,7 +31,7 @@ struct DeviceModel {
   const double* bhat;  // P       least squares, 0 if singular (:41-42,:79-91)
   const double* tV;    // P x P   tV[i + j*P] = V(j,i)        (:47-51)  (used for z = V'beta)
   const double* Vc;    // P x ldv Vc[i*ldv + j] = V(j,i), zero padded  (sweep column i is contiguous)
-  const double* Wc;    // P x ldv 1/|V(j,i)|, +inf where V is 0 or padded
+  const double* VQ;    // P x ldv x 2: VQ[(i*ldv + j)*2 + {0,1}] = {V(j,i), 1/V(j,i)}; 1/V = +-inf where V is 0 or padded
   const double* d;     // P       singular values (0 beyond the rank)
   const double* mean;  // P       a_i / d_i^2                  (:268)
   const double* zc;    // P       centre of the rss expansion in z-space (a_i/d_i^2 where d_i>0, else 0)

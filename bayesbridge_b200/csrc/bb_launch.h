@@ -84,8 +84,8 @@ int jacobi_device(double* W, double* V, int M, int P, cudaStream_t st);
 double resid_device(const double* X, const double* y, const double* b, int N, int P, cudaStream_t st, int* launches);
 int colnorm_device(const double* W, int M, int P, double* nrm, cudaStream_t st);
 int derive_device(const double* V, const int* perm, const double* dsrc, const double* Xy, int P, int ldv, double* tV, double* Vc,
-                  double* Wc, double* d, double* a, double* mean, double* d2, double* zc, cudaStream_t st);
-int derive_from_tv_device(const double* tV, const double* d, const double* a, int P, int ldv, double* Vc, double* Wc, double* mean,
+                  double* VQ, double* d, double* a, double* mean, double* d2, double* zc, cudaStream_t st);
+int derive_from_tv_device(const double* tV, const double* d, const double* a, int P, int ldv, double* Vc, double* VQ, double* mean,
                           double* d2, double* zc, cudaStream_t st);
 int vz_device(const double* Vc, const double* z, int P, int ldv, double* out, cudaStream_t st);
 int grad_device(const double* XX, const double* Xy, const double* b, int P, double* g, cudaStream_t st);

@@ -97,13 +97,13 @@ int colnorm_device(const double* W, int M, int P, double* nrm, cudaStream_t st) 
   return 1;
 }
 int derive_device(const double* V, const int* perm, const double* dsrc, const double* Xy, int P, int ldv, double* tV, double* Vc,
-                  double* Wc, double* d, double* a, double* mean, double* d2, double* zc, cudaStream_t st) {
-  derive_kernel<<<P, 128, 0, st>>>(V, perm, dsrc, Xy, P, ldv, tV, Vc, Wc, d, a, mean, d2, zc); check_launch();
+                  double* VQ, double* d, double* a, double* mean, double* d2, double* zc, cudaStream_t st) {
+  derive_kernel<<<P, 128, 0, st>>>(V, perm, dsrc, Xy, P, ldv, tV, Vc, VQ, d, a, mean, d2, zc); check_launch();
   return 1;
 }
-int derive_from_tv_device(const double* tV, const double* d, const double* a, int P, int ldv, double* Vc, double* Wc, double* mean,
+int derive_from_tv_device(const double* tV, const double* d, const double* a, int P, int ldv, double* Vc, double* VQ, double* mean,
                           double* d2, double* zc, cudaStream_t st) {
-  derive_from_tv_kernel<<<P, 128, 0, st>>>(tV, d, a, P, ldv, Vc, Wc, mean, d2, zc); check_launch();
+  derive_from_tv_kernel<<<P, 128, 0, st>>>(tV, d, a, P, ldv, Vc, VQ, mean, d2, zc); check_launch();
   return 1;
 }
 int vz_device(const double* Vc, const double* z, int P, int ldv, double* out, cudaStream_t st) {

@@ -4,7 +4,7 @@
 //   gram_kernel      G = [X y]'[X y]  ->  X'X (:24), X'y (:25), y'y        FP64 tensor cores (DMMA m8n8k4)
 //   jacobi_*         one-sided (Hestenes) Jacobi: W <- W V with orthogonal columns, V accumulated
 //                    (the SVD of :47-51: V, d;  a = (U D)'y = V'X'y of :53-54)
-//   derive_kernel    tV / Vc / Wc layouts, mean = a/d^2 (:268), d^2, zc
+//   derive_kernel    tV / Vc / VQ (interleaved {V, 1/V} columns for the sweep's TMA ring) layouts, mean = a/d^2 (:268), d^2, zc
 //   resid_kernel     || y - X b ||^2 for the rss expansions
 #pragma once
 #include "bb_launch.h"
@@ -166,7 +166,7 @@ __global__ void colnorm_kernel(const double* __restrict__ W, int M, int P, doubl
 // ------------------------------------------------------------------------------------------
 __global__ void derive_kernel(const double* __restrict__ Vsrc, const int* __restrict__ perm, const double* __restrict__ dsrc,
                               const double* __restrict__ Xy, int P, int ldv,
-                              double* tV, double* Vc, double* Wc, double* d, double* a, double* mean, double* d2, double* zc) {
+                              double* tV, double* Vc, double* VQ, double* d, double* a, double* mean, double* d2, double* zc) {
   const int i = blockIdx.x; if (i >= P) return;
   const double* v = Vsrc + (size_t)perm[i] * P;
   __shared__ double red[8];
@@ -175,7 +175,8 @@ __global__ void derive_kernel(const double* __restrict__ Vsrc, const int* __rest
     const double x = j < P ? v[j] : 0.0;
     if (j < P) { tV[i + (size_t)j * P] = x; s = fma(x, Xy[j], s); }
     Vc[(size_t)i * ldv + j] = x;
-    Wc[(size_t)i * ldv + j] = 1.0 / fabs(x);   // +inf where x == 0 (reference: division by |v_ji| = 0, :261-262)
+    VQ[((size_t)i * ldv + j) * 2] = x;
+    VQ[((size_t)i * ldv + j) * 2 + 1] = 1.0 / x;   // +-inf where x == 0 or padded (reference: division by |v_ji| = 0, :261-262)
   }
   s = warp_sum(s); if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
   __syncthreads();
@@ -191,12 +192,13 @@ __global__ void derive_kernel(const double* __restrict__ Vsrc, const int* __rest
 
 // same, from user-supplied tV (col-major, tV[i + j*P] = V(j,i)), d, a  (parity tests inject the oracle's factors)
 __global__ void derive_from_tv_kernel(const double* __restrict__ tV, const double* __restrict__ d, const double* __restrict__ a,
-                                      int P, int ldv, double* Vc, double* Wc, double* mean, double* d2, double* zc) {
+                                      int P, int ldv, double* Vc, double* VQ, double* mean, double* d2, double* zc) {
   const int i = blockIdx.x; if (i >= P) return;
   for (int j = threadIdx.x; j < ldv; j += blockDim.x) {
     const double x = j < P ? tV[i + (size_t)j * P] : 0.0;
     Vc[(size_t)i * ldv + j] = x;
-    Wc[(size_t)i * ldv + j] = 1.0 / fabs(x);
+    VQ[((size_t)i * ldv + j) * 2] = x;
+    VQ[((size_t)i * ldv + j) * 2 + 1] = 1.0 / x;
   }
   if (threadIdx.x == 0) {
     const double di = d[i];

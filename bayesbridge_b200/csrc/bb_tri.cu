@@ -6,50 +6,65 @@
 namespace bb {
 namespace {
 
-template <int J, int C>
-void launch_tri_jc(const TriLaunch& L, int W, cudaStream_t st) {
-  const int threads = 32 * (W + C);
-  const size_t smem = ((size_t)2 * C * L.m.P + 2 * C * 32 + 4 * C) * sizeof(double);
-  const int grid = (L.nchains + C - 1) / C;
-  if (threads <= 384) {
-    auto kern = tri_sweep_kernel<J, C, 384>;
-    BB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<grid, threads, smem, st>>>(L);
-  } else {
-    auto kern = tri_sweep_kernel<J, C, 1024>;
-    BB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<grid, threads, smem, st>>>(L);
+constexpr size_t SMEM_BUDGET = 220 * 1024;   // of the 227 KB a CTA may opt into on sm_100
+
+template <int J, int W, int C, int NGMAX>
+void launch_cfg(const TriLaunch& L, int NG, cudaStream_t st) {
+  const int P = L.m.P, LD = L.m.ldv;
+  NG = std::max(1, std::min(NG, NGMAX));
+  // ring depth: everything resident when {V,1/V} fits, else as deep as the budget allows (2..8 stages)
+  int S;
+  while (true) {
+    const size_t fixed = tri_smem_bytes(P, LD, 0, NG, W, C);
+    const size_t per_stage = (size_t)LD * 16 + 16;
+    if (fixed + (size_t)P * per_stage <= SMEM_BUDGET) { S = P; break; }
+    S = (int)std::min<size_t>(8, fixed < SMEM_BUDGET ? (SMEM_BUDGET - fixed) / per_stage : 0);
+    if (S >= 2) break;
+    if (NG == 1) throw std::string("tri: P too large for the on-chip sweep");
+    NG = NG / 2;
   }
-  check_launch();
+  const size_t smem = tri_smem_bytes(P, LD, S, NG, W, C);
+  const int CH = NG * C;
+  const int grid = (L.nchains + CH - 1) / CH;
+  auto kern = tri_sweep_kernel<J, W, C, NGMAX>;
+  BB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<grid, 32 * NG * W, smem, st>>>(L, S);
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    cudaFuncAttributes fa{};
+    cudaFuncGetAttributes(&fa, kern);
+    throw std::string("tri_sweep_kernel<J=") + std::to_string(J) + ",W=" + std::to_string(W) + ",C=" + std::to_string(C) + "> launch failed: " +
+        cudaGetErrorString(e) + " (threads " + std::to_string(32 * NG * W) + ", dyn smem " + std::to_string(smem) + ", regs " +
+        std::to_string(fa.numRegs) + ", maxThreadsPerBlock " + std::to_string(fa.maxThreadsPerBlock) + ", static smem " +
+        std::to_string(fa.sharedSizeBytes) + ", local " + std::to_string(fa.localSizeBytes) + ")";
+  }
 }
-template <int J>
-void launch_tri_j(const TriLaunch& L, int W, int C, cudaStream_t st) {
-  if (C >= 4) launch_tri_jc<J, 4>(L, W, st);
-  else if (C >= 2) launch_tri_jc<J, 2>(L, W, st);
-  else launch_tri_jc<J, 1>(L, W, st);
+
+// NGMAX (groups per CTA) bounds the thread count and with it the registers a thread may use
+template <int J, int W>
+void launch_jw(const TriLaunch& L, int C, int NG, cudaStream_t st) {
+  constexpr int NGMAX = J >= 16 ? 1 : (W >= 4 ? 2 : 4);
+  if (C >= 2 && !(J >= 16 && W >= 8)) launch_cfg<J, W, 2, NGMAX>(L, NG, st);
+  else launch_cfg<J, W, 1, NGMAX>(L, NG, st);
 }
 
 }  // namespace
 
 int launch_tri(const TriLaunch& L, cudaStream_t st) {
-  const int P = L.m.P;
-  if (P > 8 * 32 * 24) throw std::string("tri: P too large for the on-chip sweep (max 6144)");
-  // compute warps W and coordinates per lane J with 32*W*J >= P
-  int W = std::min(8, (P + 31) / 32);
-  int J = (P + 32 * W - 1) / (32 * W);
-  while (J > 8) { W += 4; J = (P + 32 * W - 1) / (32 * W); }
-  const int Jt = J <= 1 ? 1 : J <= 2 ? 2 : J <= 4 ? 4 : 8;
-  // chains per CTA: fill the 148 SMs first, then stack chains (they share each column of V in registers)
-  int C = 1;
-  if (L.nchains > 148) C = 2;
-  if (L.nchains > 2 * 148) C = 4;
-  if (Jt == 8 && C > 2) C = 2;   // register budget
-  switch (Jt) {
-    case 1: launch_tri_j<1>(L, W, C, st); break;
-    case 2: launch_tri_j<2>(L, W, C, st); break;
-    case 4: launch_tri_j<4>(L, W, C, st); break;
-    default: launch_tri_j<8>(L, W, C, st); break;
-  }
+  if (L.m.ldv > 4096) throw std::string("tri: P too large for the on-chip sweep (max 4096)");
+  // chains per SM needed to make every chain resident at once; C of them share a warp group
+  const int per_sm = (L.nchains + 147) / 148;
+  const int C = per_sm >= 2 ? 2 : 1;
+  const int NG = (per_sm + C - 1) / C;
+  const int LD = L.m.ldv;
+  if (LD <= 32) launch_jw<1, 1>(L, C, NG, st);
+  else if (LD <= 64) launch_jw<2, 1>(L, C, NG, st);
+  else if (LD <= 128) launch_jw<4, 1>(L, C, NG, st);
+  else if (LD <= 256) launch_jw<8, 1>(L, C, NG, st);
+  else if (LD <= 512) launch_jw<8, 2>(L, C, NG, st);
+  else if (LD <= 1024) launch_jw<8, 4>(L, C, NG, st);
+  else if (LD <= 2048) launch_jw<16, 4>(L, C, NG, st);
+  else launch_jw<16, 8>(L, C, NG, st);
   return 1;
 }
 

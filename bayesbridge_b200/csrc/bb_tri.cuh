@@ -6,21 +6,27 @@
 //        sample_omega     :130-147     sample_u  :97-110     sample_beta  :405-433
 //        rtnorm_gibbs (SVD form, the innermost loop)  :235-286.
 //
-// Layout of one CTA: C chains, W "compute" warps that own the coordinates j (J per lane, all C
-// chains in registers) and C "draw" warps, one per chain.  Step i of the rotated sweep is
-//   compute warps: bounds over j for chain c -> warp max/min -> partials in smem -> bar.arrive PART(c)
-//   draw warp c  : (Philox block for trial=lane already computed) bar.sync PART(c) -> final max/min ->
-//                  truncated-normal draw, 32 trials in parallel -> delta in smem -> bar.arrive DELTA(c)
-//   compute warps: bar.sync DELTA(c) -> beta_j += V(j,i) delta  (and the fresh accumulation of V z)
-// The C chains are staggered through the compute warps, so while draw warp c works the compute
-// warps are busy with chains c+1.. ; column i of V (and of 1/|V|) is loaded once per step and
-// shared by the C chains in registers; the next column is prefetched.
+// The rotated sweep, restated.  Step i of :250-283 needs, over all j,
+//     left_j  = (v>0 ? -(b_j + r_j) : -(b_j - r_j)) / |v|,   right_j = (v>0 ? b_j - r_j : b_j + r_j) / |v|,
+//     v = V(j,i),  r_j = beta_j - v z_i   (beta_j = current V z, kept incrementally: Notes/bbnotes.tex:603-612).
+// With q = 1/v both signs of v collapse to
+//     left_j = z_i - (beta_j q + b_j |q|),      right_j = z_i + (b_j |q| - beta_j q),
+// so  lmax = z_i - min_j fma(beta_j, q, b_j|q|),  rmin = z_i + min_j fma(-beta_j, q, b_j|q|):
+// one multiply, two FMAs and two minima per (i,j), plus the FMA beta_j += v (z_i' - z_i) after the
+// draw: 6 FP64 operations per (i,j).  Where v = 0 (or j is padding) q = +-inf and both candidates
+// come out +inf or NaN, which fmin ignores -- the reference's division by zero (:261-262) likewise
+// produces bounds that never bind.
 //
-// Differences from the reference that are algebraic identities (documented in DESIGN.md):
-//   * beta_j at the current z is kept incrementally instead of the O(P) dot at :258 (the author's
-//     own note, Notes/bbnotes.tex:603-612); beta = V z is re-accumulated every sweep like :285;
-//   * divisions by |v_ji| (:261-262) are multiplications by a precomputed 1/|v_ji|;
-//   * ||y - X beta||^2 (:440-443) is r0 + sum_i d_i^2 (z_i - zc_i)^2, which never touches X.
+// Layout.  A CTA holds NG groups; a group is W warps that own C chains: lane l of warp w keeps
+// coordinates j = jj*32W + 32w + l (jj < J) of all C chains in registers (beta, b), so each column
+// of {V, 1/V} is read once per group-step and the C independent chains interleave in one
+// instruction stream (latency hiding).  Columns are streamed from L2 into a shared-memory ring by
+// one producer thread with TMA bulk copies (cp.async.bulk + mbarrier complete_tx); a column is
+// released as soon as every warp has copied its slice into registers.  Per step: local minima ->
+// 5 shuffle levels -> (W > 1: partials through smem, one named barrier) -> ONE warp of the group
+// draws all C truncated normals at once (32/C lanes = parallel rejection trials per chain; the
+// lowest accepting trial wins, which is what the sequential sampler would have returned) ->
+// delta_c through smem -> axpy.  When the whole {V,1/V} fits (P <= 64) the ring is filled once.
 #pragma once
 #include <cfloat>
 #include <math_constants.h>
@@ -28,128 +34,237 @@
 
 namespace bb {
 
+// ---- mbarrier / TMA bulk-copy wrappers (PTX) ----
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// global -> shared bulk copy (TMA, 1-D); bytes % 16 == 0, both addresses 16-byte aligned
+__device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
 
-template <int J, int C, int MAXT>
-__global__ void __launch_bounds__(MAXT, 1) tri_sweep_kernel(const TriLaunch L) {
-  extern __shared__ double smem[];
-  const int P = L.m.P, ldv = L.m.ldv;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int nct = blockDim.x - 32 * C;  // compute threads
-  const int W = nct >> 5;
-  const bool is_draw = tid >= nct;
-  const int dc = is_draw ? (tid - nct) >> 5 : 0;
-  const int nbar = nct + 32;
+// shared-memory footprint of one CTA (bytes); mirrored by the host launcher
+__host__ __device__ inline size_t tri_smem_bytes(int P, int LD, int S, int NG, int W, int C) {
+  const size_t CH = (size_t)NG * C;
+  return (size_t)S * LD * 16 + 2 * CH * P * 8 + (size_t)(2 * NG * W * C * 2 + NG * C + NG * C * 2) * 8 + (size_t)2 * S * 8;
+}
 
-  double* z_s = smem;                 // [C][P]
-  double* scr_s = z_s + C * P;        // [C][P] scratch (beta for the z initialisation)
-  double* red_l = scr_s + C * P;      // [C][32]
-  double* red_r = red_l + C * 32;     // [C][32]
-  double* bc_s = red_r + C * 32;      // [C][4]: delta, znew | tau, sig2
+// registers live per SM sub-partition (16384 each, warps dealt round-robin over the 4 of them)
+constexpr int tri_maxnreg(int threads) {
+  const int wps = (threads + 127) / 128;
+  return 16384 / (wps * 32) >= 255 ? 255 : (16384 / (wps * 32) / 8) * 8;
+}
 
-  const int cbase = blockIdx.x * C;
-  int lch[C]; bool valid[C];
-#pragma unroll
-  for (int c = 0; c < C; ++c) { valid[c] = cbase + c < L.nchains; lch[c] = valid[c] ? cbase + c : cbase; }
+template <int J, int W, int C, int NGMAX>
+__global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const TriLaunch L, const int S) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int P = L.m.P, LD = L.m.ldv;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int nwarp = blockDim.x >> 5;
+  const int NG = nwarp / W;
+  const int g = wid / W, w = wid - g * W;
+  const int CH = NG * C;
+
+  double2* ring = reinterpret_cast<double2*>(smem_raw);        // [S][LD]  {V(j,i), 1/V(j,i)}
+  double* z_s = reinterpret_cast<double*>(ring + (size_t)S * LD);   // [CH][P]
+  double* u_s = z_s + (size_t)CH * P;                          // [CH][P]
+  double* red = u_s + (size_t)CH * P;                          // [2][NG][W][C][2]
+  double* bc = red + 2 * NG * W * C * 2;                       // [NG][C]    delta of the current step
+  double* sc = bc + NG * C;                                    // [NG][C][2] tau, sig2
+  uint64_t* full = reinterpret_cast<uint64_t*>(sc + NG * C * 2);    // [S]
+  uint64_t* empty = full + S;                                  // [S]
 
   const double alpha = L.h.true_alpha;  // fixed alpha (unknown alpha is handled by the host driver per iteration)
   const bool know_tau = L.h.true_tau > 0, know_sig2 = L.h.true_sig2 > 0;
   const bool do_tau = (L.stages & 1) && !know_tau, do_sig2 = (L.stages & 2) && !know_sig2;
   const bool do_omega = L.stages & 4, do_u = L.stages & 8, do_beta = L.stages & 16;
+  const int nsweep = (L.h.betaburn > 0 ? L.h.betaburn : 0) + 1;
+  const bool resident = S >= P;
+  const long long sweep_steps = do_beta ? (long long)L.niter * nsweep * P : 0;
+  const long long total_steps = (L.init_z ? P : 0) + sweep_steps;
+
+  if (tid == 0) {
+    for (int s = 0; s < S; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], (uint32_t)(NG * W)); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  // ======================= column stream: thread 0 issues the TMA copies =======================
+  // Step m reuses the stage of step m - S.  Thread 0 issues step n + S - D when it enters step n, after
+  // every warp has released step n - D: S - D columns of prefetch, D steps of slack between the groups.
+  const bool issuer = tid == 0;
+  const uint32_t col_bytes = (uint32_t)LD * 16u;
+  const long long nload = resident ? (total_steps < P ? total_steps : (long long)P) : total_steps;
+  const int D = S > 1 ? S / 2 : 1;
+  int is_ = 0, icol = 0; uint32_t iuse = 0; long long inext = 0;   // issuer cursor: stage, column, use count, step
+  auto issue_one = [&]() {
+    if (iuse > 0) mbar_wait(&empty[is_], (iuse - 1) & 1);
+    mbar_arrive_expect_tx(&full[is_], col_bytes);
+    tma_load_1d(ring + (size_t)is_ * LD, L.m.VQ + (size_t)icol * LD * 2, col_bytes, &full[is_]);
+    if (++is_ == S) { is_ = 0; ++iuse; }
+    if (++icol == P) icol = 0;
+    ++inext;
+  };
+  if (issuer) while (inext < nload && inext < S) issue_one();
+
+  // ======================= consumers =======================
+  const int bar_id = 1 + g, bar_n = 32 * W;
+  auto group_sync = [&]() { if (W > 1) bar_sync(bar_id, bar_n); else __syncwarp(); };
+  constexpr int SL = 32 / C;                 // lanes (= parallel rejection trials) per chain in the draw
+  const int dc = lane / SL, sl = lane - dc * SL;
+  const uint32_t slmask = (SL == 32) ? 0xffffffffu : (((1u << SL) - 1u) << (dc * SL));
+
+  const int cbase = blockIdx.x * CH + g * C;
+  int lch[C]; bool valid[C];
+#pragma unroll
+  for (int c = 0; c < C; ++c) { valid[c] = cbase + c < L.nchains; lch[c] = valid[c] ? cbase + c : (L.nchains - 1); }
+  const int lch_d = (cbase + dc < L.nchains) ? cbase + dc : (L.nchains - 1);
+  const uint32_t gch_d = L.chain0 + (uint32_t)lch_d;
+  double* zg = z_s + (size_t)(g * C) * P;    // this group's z rows
+  double* ug = u_s + (size_t)(g * C) * P;
+  double* redg0 = red + (size_t)(g * W) * C * 2;                       // buffer 0, [W][C][2]
+  double* redg1 = red + (size_t)(NG * W + g * W) * C * 2;              // buffer 1
 
   // ---------------- load state ----------------
-  double cur[C][J], uu[C][J], bb_[C][J], acc[C][J];
+  double cur[C][J], bb_[C][J];
 #pragma unroll
   for (int c = 0; c < C; ++c)
 #pragma unroll
     for (int jj = 0; jj < J; ++jj) {
-      const int j = tid + jj * nct;
-      const bool in = !is_draw && j < P;
-      cur[c][jj] = in ? L.beta[(size_t)lch[c] * P + j] : 0.0;
-      uu[c][jj] = in ? L.u[(size_t)lch[c] * P + j] : 0.5;
-      bb_[c][jj] = 1.0; acc[c][jj] = 0.0;
+      const int j = jj * 32 * W + 32 * w + lane;
+      cur[c][jj] = j < P ? L.beta[(size_t)lch[c] * P + j] : 0.0;
+      bb_[c][jj] = 1.0;
+      if (j < P) ug[c * P + j] = L.u[(size_t)lch[c] * P + j];
     }
-  if (L.init_z) {
-    for (int c = 0; c < C; ++c)
-      for (int j = tid; j < P; j += blockDim.x) scr_s[c * P + j] = L.beta[(size_t)lch[c] * P + j];
-    __syncthreads();
-    for (int i = tid; i < P; i += blockDim.x) {
-      double s[C];
-#pragma unroll
-      for (int c = 0; c < C; ++c) s[c] = 0.0;
-      for (int j = 0; j < P; ++j) {
-        const double t = __ldg(L.m.tV + i + (size_t)j * P);
-#pragma unroll
-        for (int c = 0; c < C; ++c) s[c] = fma(t, scr_s[c * P + j], s[c]);
-      }
-#pragma unroll
-      for (int c = 0; c < C; ++c) z_s[c * P + i] = s[c];
-    }
-  } else {
-    for (int c = 0; c < C; ++c)
-      for (int i = tid; i < P; i += blockDim.x) z_s[c * P + i] = L.z[(size_t)lch[c] * P + i];
-  }
   double tau_c[C], sig2_c[C];
 #pragma unroll
   for (int c = 0; c < C; ++c) {
     tau_c[c] = know_tau ? L.h.true_tau : L.tau[lch[c]];
     sig2_c[c] = know_sig2 ? L.h.true_sig2 : L.sig2[lch[c]];
   }
-  uint32_t status = 0;
-  __syncthreads();
+  uint32_t status = 0;        // bits for chain dc (the chain this lane serves in the draw)
 
-  const int nsweep = (L.h.betaburn > 0 ? L.h.betaburn : 0) + 1;
+  // ring cursor
+  int rs = 0; uint32_t ruse = 0; long long nstep = 0;
+  double2 vq[J];
+  auto next_column = [&]() {   // wait for the column, copy this lane's slice into registers, release the stage
+    if (issuer && inext < nload && inext <= nstep + S - D) issue_one();
+    if (!resident || nstep < P) mbar_wait(&full[rs], ruse & 1);
+    const double2* col = ring + (size_t)rs * LD;
+#pragma unroll
+    for (int jj = 0; jj < J; ++jj) {
+      const int j = jj * 32 * W + 32 * w + lane;
+      vq[jj] = j < LD ? col[j] : make_double2(0.0, CUDART_INF);
+    }
+    if (!resident) { __syncwarp(); if (lane == 0) mbar_arrive(&empty[rs]); }
+    if (++rs == S) { rs = 0; ++ruse; }
+    ++nstep;
+  };
+
+  // ---------------- z = V' beta (BridgeRegression.cpp:246) from the registers, or from the state ----------------
+  if (L.init_z) {
+    for (int i = 0; i < P; ++i) {
+      next_column();
+      double pz[C];
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        double s = 0.0;
+#pragma unroll
+        for (int jj = 0; jj < J; ++jj) s = fma(vq[jj].x, cur[c][jj], s);
+        pz[c] = warp_sum(s);
+      }
+      if (W > 1) {
+        double* rb = (i & 1) ? redg1 : redg0;
+        if (lane == 0) {
+#pragma unroll
+          for (int c = 0; c < C; ++c) rb[(w * C + c) * 2] = pz[c];
+        }
+        bar_sync(bar_id, bar_n);
+        if (w == 0 && lane < C) { double s = 0.0; for (int ww = 0; ww < W; ++ww) s += rb[(ww * C + lane) * 2]; zg[lane * P + i] = s; }
+      } else if (lane == 0) {
+#pragma unroll
+        for (int c = 0; c < C; ++c) zg[c * P + i] = pz[c];
+      }
+    }
+  } else {
+    for (int c = 0; c < C; ++c)
+      for (int i = 32 * w + lane; i < P; i += 32 * W) zg[c * P + i] = L.z[(size_t)lch[c] * P + i];
+  }
+  group_sync();
 
   for (int it = -L.pre_tau; it < L.niter; ++it) {
-    const bool pre = it < 0;  // the tau pre-draw before burn-in
+    const bool pre = it < 0;  // the tau pre-draw before burn-in (BridgeWrapper.cpp:142)
     const uint32_t t = L.iter0 + (pre ? 0u : (uint32_t)it);
 
     // ================= tau and sig2 (scalars per chain) =================
-    if (!is_draw) {
+    {
+      double st[C], sr[C];
 #pragma unroll
       for (int c = 0; c < C; ++c) {
-        double st = 0.0, sr = 0.0;
+        double a = 0.0, r = 0.0;
 #pragma unroll
         for (int jj = 0; jj < J; ++jj)
-          if (tid + jj * nct < P) st += exp(alpha * log(fabs(cur[c][jj])));   // BridgeRegression.cpp:459
+          if (jj * 32 * W + 32 * w + lane < P) a += exp(alpha * log(fabs(cur[c][jj])));   // BridgeRegression.cpp:459
         if (!pre && do_sig2)
-          for (int i = tid; i < P; i += nct) {
-            const double dz = z_s[c * P + i] - __ldg(L.m.zc + i);
-            sr = fma(__ldg(L.m.d2 + i) * dz, dz, sr);
+          for (int i = 32 * w + lane; i < P; i += 32 * W) {   // ||y - X beta||^2 = r0 + sum d_i^2 (z_i - zc_i)^2
+            const double dz = zg[c * P + i] - __ldg(L.m.zc + i);
+            r = fma(__ldg(L.m.d2 + i) * dz, dz, r);
           }
-        st = warp_sum(st); sr = warp_sum(sr);
-        if (lane == 0) { red_l[c * 32 + warp] = st; red_r[c * 32 + warp] = sr; }
-        __threadfence_block();
-        bar_arrive(1 + 2 * c, nbar);
+        st[c] = warp_sum(a); sr[c] = warp_sum(r);
       }
+      if (W > 1) {
+        if (lane == 0) {
 #pragma unroll
-      for (int c = 0; c < C; ++c) {
-        bar_sync(2 + 2 * c, nbar);
-        tau_c[c] = bc_s[c * 4 + 2]; sig2_c[c] = bc_s[c * 4 + 3];
+          for (int c = 0; c < C; ++c) { redg0[(w * C + c) * 2] = st[c]; redg0[(w * C + c) * 2 + 1] = sr[c]; }
+        }
+        bar_sync(bar_id, bar_n);
       }
-    } else {
-      const int c = dc;
-      const uint32_t gch = L.chain0 + (uint32_t)lch[c];
-      bar_sync(1 + 2 * c, nbar);
-      double st = lane < W ? red_l[c * 32 + lane] : 0.0, sr = lane < W ? red_r[c * 32 + lane] : 0.0;
-      st = warp_sum(st); sr = warp_sum(sr);
-      double tau = tau_c[c], sig2 = sig2_c[c];
-      if (do_tau || (pre && !know_tau)) {  // BridgeRegression.cpp:453-465
-        const double shape = L.h.nu_shape + ((double)P) / alpha;
-        const double rate = L.h.nu_rate + st;
-        Stream s(L.key, gch, t, pre ? ST_TAU_INIT : ST_TAU, 0);
-        const double nu = gamma_rate<true>(s, shape, rate, status);
-        tau = exp(-1.0 * log(nu) / alpha);
+      if (w == 0) {
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+          double a = st[c], r = sr[c];
+          if (W > 1) { a = 0.0; r = 0.0; for (int ww = 0; ww < W; ++ww) { a += redg0[(ww * C + c) * 2]; r += redg0[(ww * C + c) * 2 + 1]; } }
+          const uint32_t gch = L.chain0 + (uint32_t)lch[c];
+          double tau = tau_c[c], sig2 = sig2_c[c];
+          uint32_t stt = 0;
+          if (do_tau || (pre && !know_tau)) {  // BridgeRegression.cpp:453-465
+            const double shape = L.h.nu_shape + ((double)P) / alpha;
+            const double rate = L.h.nu_rate + a;
+            Stream s(L.key, gch, t, pre ? ST_TAU_INIT : ST_TAU, 0);
+            const double nu = gamma_rate<true>(s, shape, rate, stt);
+            tau = exp(-1.0 * log(nu) / alpha);
+          }
+          if (!pre && do_sig2) {  // BridgeRegression.cpp:436-450
+            const double shape = L.h.sig2_shape + 0.5 * L.m.N;
+            const double scale = L.h.sig2_scale + 0.5 * (L.m.r0z + r);
+            Stream s(L.key, gch, t, ST_SIG2, 0);
+            sig2 = scale / gamma_rate<true>(s, shape, 1.0, stt);
+          }
+          if (lane == 0) { sc[(g * C + c) * 2] = tau; sc[(g * C + c) * 2 + 1] = sig2; if (stt) atomicOr(L.status + lch[c], stt); }
+        }
       }
-      if (!pre && do_sig2) {  // BridgeRegression.cpp:436-450
-        const double shape = L.h.sig2_shape + 0.5 * L.m.N;
-        const double scale = L.h.sig2_scale + 0.5 * (L.m.r0z + sr);
-        Stream s(L.key, gch, t, ST_SIG2, 0);
-        sig2 = scale / gamma_rate<true>(s, shape, 1.0, status);
-      }
-      tau_c[c] = tau; sig2_c[c] = sig2;
-      if (lane == 0) { bc_s[c * 4 + 2] = tau; bc_s[c * 4 + 3] = sig2; }
-      __threadfence_block();
-      bar_arrive(2 + 2 * c, nbar);
+      group_sync();
+#pragma unroll
+      for (int c = 0; c < C; ++c) { tau_c[c] = sc[(g * C + c) * 2]; sig2_c[c] = sc[(g * C + c) * 2 + 1]; }
     }
     if (pre) continue;
 
@@ -157,203 +272,188 @@ __global__ void __launch_bounds__(MAXT, 1) tri_sweep_kernel(const TriLaunch L) {
     const long long slot = L.sink.s0 + (it + 1) / (L.sink.thin > 0 ? L.sink.thin : 1) - 1;
 
     // ================= omega, u, box half-widths (elementwise) =================
-    if (!is_draw) {
 #pragma unroll
-      for (int c = 0; c < C; ++c) {
-        const uint32_t gch = L.chain0 + (uint32_t)lch[c];
-        const double tau = tau_c[c];
+    for (int c = 0; c < C; ++c) {
+      const uint32_t gch = L.chain0 + (uint32_t)lch[c];
+      const double tau = tau_c[c];
 #pragma unroll
-        for (int jj = 0; jj < J; ++jj) {
-          const int j = tid + jj * nct;
-          if (j < P) {
-            const double ab = fabs(cur[c][jj]);
-            // sample_omega, BridgeRegression.cpp:130-147
-            double om; bool one = true;
-            if (do_omega) {
-              const double a_j = exp(alpha * log(ab / ((1 - uu[c][jj]) * tau)));
-              const double prob = alpha / (1 + alpha * a_j);
-              Stream so(L.key, gch, t, ST_OMEGA, (uint32_t)j);
-              double e1, e2; so.block(1, e1, e2);
-              one = so.unif(0) > prob;
-              om = (one ? -log(e1) : -log(e1 * e2)) + a_j;
-            } else om = L.omega[(size_t)lch[c] * P + j];
-            // sample_u, BridgeRegression.cpp:97-110
-            double un = uu[c][jj];
-            if (do_u) {
-              Stream su(L.key, gch, t, ST_U, (uint32_t)j);
-              const double right = 1 - ab / tau * exp(-1.0 * log(om) / alpha);
-              un = right * su.unif(0);
-              uu[c][jj] = un;
+      for (int jj = 0; jj < J; ++jj) {
+        const int j = jj * 32 * W + 32 * w + lane;
+        if (j < P) {
+          const double ab = fabs(cur[c][jj]);
+          const double uo = ug[c * P + j];
+          // sample_omega, BridgeRegression.cpp:130-147
+          double om; bool one = true;
+          if (do_omega) {
+            const double a_j = exp(alpha * log(ab / ((1 - uo) * tau)));
+            const double prob = alpha / (1 + alpha * a_j);
+            Stream so(L.key, gch, t, ST_OMEGA, (uint32_t)j);
+            double e1, e2; so.block(1, e1, e2);
+            one = so.unif(0) > prob;
+            om = (one ? -log(e1) : -log(e1 * e2)) + a_j;
+          } else om = L.omega[(size_t)lch[c] * P + j];
+          // sample_u, BridgeRegression.cpp:97-110
+          double un = uo;
+          if (do_u) {
+            Stream su(L.key, gch, t, ST_U, (uint32_t)j);
+            const double right = 1 - ab / tau * exp(-1.0 * log(om) / alpha);
+            un = right * su.unif(0);
+            ug[c * P + j] = un;
+          }
+          // b_j, BridgeRegression.cpp:409-411
+          bb_[c][jj] = (1.0 - un) * exp(log(om) / alpha) * tau;
+          if (valid[c]) {
+            if (store) {
+              const size_t o = ((size_t)lch[c] * L.sink.chain_stride + slot) * P + j;
+              if (L.sink.omega) L.sink.omega[o] = om;
+              if (L.sink.shape) L.sink.shape[o] = do_omega ? (one ? 1.0 : 2.0) : L.shape[(size_t)lch[c] * P + j];
+              if (L.sink.u) L.sink.u[o] = un;
             }
-            // b_j, BridgeRegression.cpp:409-411
-            bb_[c][jj] = (1.0 - un) * exp(log(om) / alpha) * tau;
-            if (valid[c]) {
-              if (store) {
-                const size_t o = ((size_t)lch[c] * L.sink.chain_stride + slot) * P + j;
-                if (L.sink.omega) L.sink.omega[o] = om;
-                if (L.sink.shape) L.sink.shape[o] = do_omega ? (one ? 1.0 : 2.0) : L.shape[(size_t)lch[c] * P + j];
-                if (L.sink.u) L.sink.u[o] = un;
-              }
-              if (it == L.niter - 1 && do_omega) {
-                L.omega[(size_t)lch[c] * P + j] = om;
-                L.shape[(size_t)lch[c] * P + j] = one ? 1.0 : 2.0;
-              }
+            if (it == L.niter - 1 && do_omega) {
+              L.omega[(size_t)lch[c] * P + j] = om;
+              L.shape[(size_t)lch[c] * P + j] = one ? 1.0 : 2.0;
             }
           }
         }
       }
     }
 
-    // ================= beta: rotated coordinate sweeps =================
+    // ================= beta: rotated coordinate sweeps (BridgeRegression.cpp:235-286) =================
+    double sig_d = sig2_c[0];
+#pragma unroll
+    for (int c = 1; c < C; ++c) if (dc == c) sig_d = sig2_c[c];
+    sig_d = sqrt(sig_d);
     for (int sw = 0; do_beta && sw < nsweep; ++sw) {
-      if (!is_draw) {
-        double v[J], w[J], vn[J], wn[J], vp[J];
+      for (int i = 0; i < P; ++i) {
+        const bool drawer = (W == 1) || (w == i % W);
+        // the Philox block of this lane's first trial and the per-step scalars do not depend on the bounds
+        double ua = 0.5, ub = 0.5, di = 0.0, mean = 0.0;
+        Stream s(L.key, gch_d, t, ST_BETA, (uint32_t)(sw * P + i));
+        if (drawer) { s.block((uint32_t)sl, ua, ub); di = __ldg(L.m.d + i); mean = __ldg(L.m.mean + i); }
+        next_column();
+        // ---- candidates: min_j fma(beta_j, q, b_j|q|) and min_j fma(-beta_j, q, b_j|q|) ----
+        double lmn[C], rmn[C];
+#pragma unroll
+        for (int c = 0; c < C; ++c) { lmn[c] = CUDART_INF; rmn[c] = CUDART_INF; }
 #pragma unroll
         for (int jj = 0; jj < J; ++jj) {
-          const bool in = tid + jj * nct < ldv;   // coordinates beyond the padded row: v = 0, 1/|v| = inf
-          v[jj] = in ? __ldg(L.m.Vc + tid + jj * nct) : 0.0; w[jj] = in ? __ldg(L.m.Wc + tid + jj * nct) : CUDART_INF;
-          vp[jj] = 0.0; vn[jj] = 0.0; wn[jj] = 0.0;
-        }
-#pragma unroll
-        for (int c = 0; c < C; ++c)
-#pragma unroll
-          for (int jj = 0; jj < J; ++jj) acc[c][jj] = 0.0;
-        for (int i = 0; i < P; ++i) {
-          if (i + 1 < P) {
-#pragma unroll
-            for (int jj = 0; jj < J; ++jj) {
-              const bool in = tid + jj * nct < ldv;
-              vn[jj] = in ? __ldg(L.m.Vc + (size_t)(i + 1) * ldv + tid + jj * nct) : 0.0;
-              wn[jj] = in ? __ldg(L.m.Wc + (size_t)(i + 1) * ldv + tid + jj * nct) : CUDART_INF;
-            }
-          }
+          const double q = vq[jj].y, aq = fabs(q);
 #pragma unroll
           for (int c = 0; c < C; ++c) {
-            if (i > 0) {
-              bar_sync(2 + 2 * c, nbar);
-              const double dl = bc_s[c * 4 + 0], zn = bc_s[c * 4 + 1];
-#pragma unroll
-              for (int jj = 0; jj < J; ++jj) { cur[c][jj] = fma(vp[jj], dl, cur[c][jj]); acc[c][jj] = fma(vp[jj], zn, acc[c][jj]); }
-            }
-            const double zi = z_s[c * P + i];
-            double lm = -DBL_MAX, rm = DBL_MAX;
-#pragma unroll
-            for (int jj = 0; jj < J; ++jj) {   // BridgeRegression.cpp:254-265
-              const double r = fma(-v[jj], zi, cur[c][jj]);
-              const double dif = bb_[c][jj] - r, sum = bb_[c][jj] + r;
-              const bool pos = v[jj] > 0;
-              const double left = (pos ? -sum : -dif) * w[jj];
-              const double right = (pos ? dif : sum) * w[jj];
-              lm = fmax(lm, left); rm = fmin(rm, right);
-            }
-            lm = warp_max(lm); rm = warp_min(rm);
-            if (lane == 0) { red_l[c * 32 + warp] = lm; red_r[c * 32 + warp] = rm; }
-            __threadfence_block();
-            bar_arrive(1 + 2 * c, nbar);
+            const double gq = bb_[c][jj] * aq;
+            lmn[c] = fmin(lmn[c], fma(cur[c][jj], q, gq));
+            rmn[c] = fmin(rmn[c], fma(-cur[c][jj], q, gq));
           }
-#pragma unroll
-          for (int jj = 0; jj < J; ++jj) { vp[jj] = v[jj]; v[jj] = vn[jj]; w[jj] = wn[jj]; }
         }
 #pragma unroll
-        for (int c = 0; c < C; ++c) {
-          bar_sync(2 + 2 * c, nbar);
-          const double zn = bc_s[c * 4 + 1];
+        for (int o = 16; o > 0; o >>= 1)
 #pragma unroll
-          for (int jj = 0; jj < J; ++jj) cur[c][jj] = fma(vp[jj], zn, acc[c][jj]);   // beta = V z  (:285)
+          for (int c = 0; c < C; ++c) {
+            lmn[c] = fmin(lmn[c], __shfl_xor_sync(0xffffffffu, lmn[c], o));
+            rmn[c] = fmin(rmn[c], __shfl_xor_sync(0xffffffffu, rmn[c], o));
+          }
+        if (W > 1) {
+          if (lane == 0) {
+#pragma unroll
+            for (int c = 0; c < C; ++c) { redg0[(w * C + c) * 2] = lmn[c]; redg0[(w * C + c) * 2 + 1] = rmn[c]; }
+          }
+          bar_sync(bar_id, bar_n);
         }
-      } else {
-        const int c = dc;
-        const uint32_t gch = L.chain0 + (uint32_t)lch[c];
-        const double sig = sqrt(sig2_c[c]);
-        for (int i = 0; i < P; ++i) {
-          Stream s(L.key, gch, t, ST_BETA, (uint32_t)(sw * P + i));
-          double ua, ub; s.block((uint32_t)lane, ua, ub);
-          const double di = __ldg(L.m.d + i), mean = __ldg(L.m.mean + i);
-          bar_sync(1 + 2 * c, nbar);
-          double lm = lane < W ? red_l[c * 32 + lane] : -DBL_MAX, rm = lane < W ? red_r[c * 32 + lane] : DBL_MAX;
-          lm = warp_max(lm); rm = warp_min(rm);
-          const double zold = z_s[c * P + i];
+        if (drawer) {
+          // this lane serves chain dc: combine the partial minima
+          double lq, rq;
+          if (W > 1) {
+            lq = CUDART_INF; rq = CUDART_INF;
+#pragma unroll
+            for (int ww = 0; ww < W; ++ww) { lq = fmin(lq, redg0[(ww * C + dc) * 2]); rq = fmin(rq, redg0[(ww * C + dc) * 2 + 1]); }
+          } else {
+            lq = lmn[0]; rq = rmn[0];
+#pragma unroll
+            for (int c = 1; c < C; ++c) if (dc == c) { lq = lmn[c]; rq = rmn[c]; }
+          }
+          const double zold = zg[dc * P + i];
+          const double lm = zold - lq, rm = zold + rq;
           double znew;
           if (di > 1e-16) {   // BridgeRegression.cpp:268-273
-            const double sd = sig / di;
+            const double sd = sig_d / di;
             const double a = (lm - mean) / sd, b = (rm - mean) / sd;
             const TnPlan p = tn_setup(a, b);
-            double x;
-            if (p.mode == 5) { status |= ST_NAN; x = a + b; }
-            else if (p.mode == 4) { if (a > b) status |= ST_EMPTY_INTERVAL; x = a; }
-            else {
-              bool acc_ = tn_eval(p, ua, ub, x);
-              uint32_t mk = __ballot_sync(0xffffffffu, acc_);
-              uint32_t base = 32;
-              while (!mk && base < K_CAP - 32) {
-                s.block(base + lane, ua, ub);
-                acc_ = tn_eval(p, ua, ub, x);
-                mk = __ballot_sync(0xffffffffu, acc_);
-                base += 32;
-              }
-              if (mk) x = p.sgn * __shfl_sync(0xffffffffu, x, __ffs(mk) - 1);
-              else { status |= ST_TRIAL_CAP; x = nan(""); }
+            double x = 0.0;
+            bool fin = false;
+            if (p.mode == 5) { status |= ST_NAN; x = a + b; fin = true; }
+            else if (p.mode == 4) { if (a > b) status |= ST_EMPTY_INTERVAL; x = a; fin = true; }
+            uint32_t base = 0;
+            while (true) {
+              double xt = 0.0;
+              const bool acc_ = !fin && tn_eval(p, ua, ub, xt);
+              const uint32_t mine = __ballot_sync(0xffffffffu, acc_) & slmask;
+              const int src = mine ? (__ffs(mine) - 1) : lane;
+              const double xs = __shfl_sync(0xffffffffu, xt, src);
+              if (!fin && mine) { x = p.sgn * xs; fin = true; }
+              if (__ballot_sync(0xffffffffu, !fin) == 0u) break;
+              base += SL;
+              if (base >= K_CAP - 32) { if (!fin) { status |= ST_TRIAL_CAP; x = nan(""); fin = true; } break; }
+              if (!fin) s.block(base + (uint32_t)sl, ua, ub);
             }
             znew = mean + sd * x;
             if (znew < lm) znew = lm;
             if (znew > rm) znew = rm;
           } else {            // flat(lmax, rmin), BridgeRegression.cpp:280
-            const double u0 = __shfl_sync(0xffffffffu, ua, 0);
+            const double u0 = __shfl_sync(0xffffffffu, ua, dc * SL);
             znew = lm + (rm - lm) * u0;
           }
-          if (lane == 0) { z_s[c * P + i] = znew; bc_s[c * 4 + 0] = znew - zold; bc_s[c * 4 + 1] = znew; }
-          __threadfence_block();
-          bar_arrive(2 + 2 * c, nbar);
+          if (sl == 0) { zg[dc * P + i] = znew; bc[g * C + dc] = znew - zold; }
         }
+        group_sync();
+        // ---- beta += V[:,i] (z_i' - z_i) ----
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+          const double dl = bc[g * C + c];
+#pragma unroll
+          for (int jj = 0; jj < J; ++jj) cur[c][jj] = fma(vq[jj].x, dl, cur[c][jj]);
+        }
+        if (W == 1) __syncwarp();   // bc is rewritten by the next step's draw
       }
     }
 
     // ================= store =================
-    if (!is_draw) {
+    if (store) {
 #pragma unroll
       for (int c = 0; c < C; ++c) {
         if (!valid[c]) continue;
 #pragma unroll
         for (int jj = 0; jj < J; ++jj) {
-          const int j = tid + jj * nct;
+          const int j = jj * 32 * W + 32 * w + lane;
           if (j < P) {
-            if (store) {
-              const size_t o = ((size_t)lch[c] * L.sink.chain_stride + slot) * P + j;
-              if (L.sink.beta) L.sink.beta[o] = cur[c][jj];
-              if (L.sink.sum) { L.sink.sum[(size_t)lch[c] * P + j] += cur[c][jj]; L.sink.sumsq[(size_t)lch[c] * P + j] += cur[c][jj] * cur[c][jj]; }
-            }
+            const size_t o = ((size_t)lch[c] * L.sink.chain_stride + slot) * P + j;
+            if (L.sink.beta) L.sink.beta[o] = cur[c][jj];
+            if (L.sink.sum) { L.sink.sum[(size_t)lch[c] * P + j] += cur[c][jj]; L.sink.sumsq[(size_t)lch[c] * P + j] += cur[c][jj] * cur[c][jj]; }
           }
         }
+        if (w == 0 && lane == 0) {
+          const size_t o = (size_t)lch[c] * L.sink.chain_stride + slot;
+          if (L.sink.sig2) L.sink.sig2[o] = sig2_c[c];
+          if (L.sink.tau) L.sink.tau[o] = tau_c[c];
+          if (L.sink.alpha) L.sink.alpha[o] = alpha;
+        }
       }
-    } else if (lane == 0 && valid[dc] && store) {
-      const size_t o = (size_t)lch[dc] * L.sink.chain_stride + slot;
-      if (L.sink.sig2) L.sink.sig2[o] = sig2_c[dc];
-      if (L.sink.tau) L.sink.tau[o] = tau_c[dc];
-      if (L.sink.alpha) L.sink.alpha[o] = alpha;
     }
   }
 
   // ---------------- write state back ----------------
-  __syncthreads();
-  if (!is_draw) {
+  group_sync();
 #pragma unroll
-    for (int c = 0; c < C; ++c) {
-      if (!valid[c]) continue;
+  for (int c = 0; c < C; ++c) {
+    if (!valid[c]) continue;
 #pragma unroll
-      for (int jj = 0; jj < J; ++jj) {
-        const int j = tid + jj * nct;
-        if (j < P) { L.beta[(size_t)lch[c] * P + j] = cur[c][jj]; L.u[(size_t)lch[c] * P + j] = uu[c][jj]; }
-      }
+    for (int jj = 0; jj < J; ++jj) {
+      const int j = jj * 32 * W + 32 * w + lane;
+      if (j < P) { L.beta[(size_t)lch[c] * P + j] = cur[c][jj]; L.u[(size_t)lch[c] * P + j] = ug[c * P + j]; L.z[(size_t)lch[c] * P + j] = zg[c * P + j]; }
     }
-  } else if (valid[dc]) {
-    if (lane == 0) {
-      L.tau[lch[dc]] = tau_c[dc]; L.sig2[lch[dc]] = sig2_c[dc]; L.alpha[lch[dc]] = alpha;
-      if (status) atomicOr(L.status + lch[dc], status);
-    }
+    if (w == 0 && lane == 0) { L.tau[lch[c]] = tau_c[c]; L.sig2[lch[c]] = sig2_c[c]; L.alpha[lch[c]] = alpha; }
   }
-  for (int c = 0; c < C; ++c)
-    if (valid[c])
-      for (int i = tid; i < P; i += blockDim.x) L.z[(size_t)lch[c] * P + i] = z_s[c * P + i];
+  status = __reduce_or_sync(slmask, status);
+  if (sl == 0 && status && cbase + dc < L.nchains) atomicOr(L.status + lch_d, status);
 }
 
 }  // namespace bb

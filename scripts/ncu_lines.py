@@ -2,19 +2,26 @@
 """Aggregate warp-stall samples of an ncu report per source line.
 
     ncu -i rep.ncu-rep --page source --csv --print-source cuda,sass > both.csv
-    python scripts/ncu_lines.py both.csv [top]
+    python scripts/ncu_lines.py both.csv [top] [kernel_file]
 
-Prints, per file, the lines holding the most samples (share of the kernel) and instruction counts."""
+ncu lists an inlined instruction under every source line of its inline chain, so each SASS address
+is counted ONCE per view: the "phase" view attributes it to its line in `kernel_file` (the file
+holding the __global__ function; default: the file covering most addresses), the "leaf" view to
+its line in the last bb_* file that lists it (the innermost of our own code)."""
 import csv
+import gzip
 import sys
 from collections import defaultdict
 
 path = sys.argv[1]
 top = int(sys.argv[2]) if len(sys.argv) > 2 else 40
-cur_file = None
-per = defaultdict(lambda: [0, 0, 0, ""])   # (file, line) -> [samples, inst, thread_inst, text]
-hdr = None
-for row in csv.reader(open(path, newline="")):
+kfile = sys.argv[3] if len(sys.argv) > 3 else None
+op = gzip.open if path.endswith(".gz") else open
+addr = {}                       # address -> (samples, inst, thread_inst)
+where = defaultdict(list)       # address -> [(file, line)]
+text = {}
+cur_file, cur_line, hdr = None, None, None
+for row in csv.reader(op(path, "rt", newline="")):
     if not row:
         continue
     if row[0] in ("File Name", "File Path"):
@@ -28,26 +35,52 @@ for row in csv.reader(open(path, newline="")):
         continue
     if hdr is None or len(row) < len(hdr):
         continue
-    if row[0]:   # a source line row (aggregated over its SASS)
+    if row[0]:
         try:
-            ln = int(row[0])
+            cur_line = int(row[0])
         except ValueError:
             continue
-        key = (cur_file, ln)
-        e = per[key]
-        e[3] = row[1].strip()[:110]
+        text[(cur_file, cur_line)] = row[1].strip()[:100]
+    elif row[2].startswith("0x"):
         try:
-            e[0] += int(row[i_s] or 0); e[1] += int(row[i_i] or 0); e[2] += int(row[i_t] or 0)
+            addr[row[2]] = (int(row[i_s] or 0), int(row[i_i] or 0), int(row[i_t] or 0))
         except ValueError:
-            pass
-tot_s = sum(e[0] for e in per.values()) or 1
-tot_i = sum(e[1] for e in per.values()) or 1
-print(f"total samples {tot_s}, warp instructions {tot_i}")
-byfile = defaultdict(lambda: [0, 0])
-for (f, ln), e in per.items():
-    byfile[f][0] += e[0]; byfile[f][1] += e[1]
-for f, (s, i) in sorted(byfile.items(), key=lambda x: -x[1][0]):
-    print(f"  {f:28s} samples {s / tot_s:6.1%}  inst {i / tot_i:6.1%}")
-for (f, ln), e in sorted(per.items(), key=lambda x: -x[1][0])[:top]:
-    lanes = e[2] / e[1] if e[1] else 0
-    print(f"{e[0] / tot_s:6.1%} {e[1] / tot_i:6.1%} lanes {lanes:4.1f}  {f}:{ln}  {e[3]}")
+            continue
+        where[row[2]].append((cur_file, cur_line))
+tot_s = sum(v[0] for v in addr.values()) or 1
+tot_i = sum(v[1] for v in addr.values()) or 1
+cover = defaultdict(int)
+for a, ws in where.items():
+    for f in {w[0] for w in ws}:
+        cover[f] += 1
+if kfile is None:
+    kfile = max((f for f in cover if f and f.startswith("bb_")), key=lambda f: cover[f], default=None)
+print(f"total samples {tot_s}, warp instructions {tot_i}, kernel file {kfile}")
+
+
+def view(pick, title):
+    per = defaultdict(lambda: [0, 0, 0])
+    for a, v in addr.items():
+        k = pick(where[a])
+        e = per[k]
+        e[0] += v[0]; e[1] += v[1]; e[2] += v[2]
+    print(f"---- {title} ----")
+    for k, e in sorted(per.items(), key=lambda x: -x[1][0])[:top]:
+        lanes = e[2] / e[1] if e[1] else 0
+        print(f"{e[0] / tot_s:6.1%} {e[1] / tot_i:6.1%} lanes {lanes:4.1f}  {k[0]}:{k[1]}  {text.get(k, '')}")
+
+
+def phase(ws):
+    for w in ws:
+        if w[0] == kfile:
+            return w
+    return ws[0]
+
+
+def leaf(ws):
+    ours = [w for w in ws if w[0] and w[0].startswith("bb_")]
+    return ours[-1] if ours else ws[-1]
+
+
+view(phase, "phase view (lines of the kernel file)")
+view(leaf, "leaf view (innermost line of our code)")
