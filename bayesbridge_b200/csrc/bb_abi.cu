@@ -69,7 +69,7 @@ void model_alloc(bb_model* m) {
   const size_t P = m->P;
   m->ldv = (int)((P + 31) / 32 * 32);
   m->XX = dalloc<double>(P * P); m->Xy = dalloc<double>(P); m->bhat = dalloc<double>(P);
-  m->tV = dalloc<double>(P * P); m->Vc = dalloc<double>(P * m->ldv); m->VQ = dalloc<double>(2 * P * m->ldv);
+  m->tV = dalloc<double>(P * P); m->Vc = dalloc<double>(P * m->ldv); m->VQ = dalloc<double>(2 * P * (m->ldv + 2));
   m->d = dalloc<double>(P); m->a = dalloc<double>(P); m->mean = dalloc<double>(P); m->zc = dalloc<double>(P); m->d2 = dalloc<double>(P);
   m->gc = dalloc<double>(P); m->bc = dalloc<double>(P); m->bz = dalloc<double>(P);
 }

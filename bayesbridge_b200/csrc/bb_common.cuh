@@ -31,7 +31,7 @@ struct DeviceModel {
   const double* bhat;  // P       least squares, 0 if singular (:41-42,:79-91)
   const double* tV;    // P x P   tV[i + j*P] = V(j,i)        (:47-51)  (used for z = V'beta)
   const double* Vc;    // P x ldv Vc[i*ldv + j] = V(j,i), zero padded  (sweep column i is contiguous)
-  const double* VQ;    // P x ldv x 2: VQ[(i*ldv + j)*2 + {0,1}] = {V(j,i), 1/V(j,i)}; 1/V = +-inf where V is 0 or padded
+  const double* VQ;    // P x (ldv+2) x 2: column i = {V(j,i), 1/V(j,i)} for j < ldv (1/V = +-inf where V is 0 or padded), then {d_i, mean_i}, {1/d_i, 0}
   const double* d;     // P       singular values (0 beyond the rank)
   const double* mean;  // P       a_i / d_i^2                  (:268)
   const double* zc;    // P       centre of the rss expansion in z-space (a_i/d_i^2 where d_i>0, else 0)

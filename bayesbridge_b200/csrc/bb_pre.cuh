@@ -175,8 +175,8 @@ __global__ void derive_kernel(const double* __restrict__ Vsrc, const int* __rest
     const double x = j < P ? v[j] : 0.0;
     if (j < P) { tV[i + (size_t)j * P] = x; s = fma(x, Xy[j], s); }
     Vc[(size_t)i * ldv + j] = x;
-    VQ[((size_t)i * ldv + j) * 2] = x;
-    VQ[((size_t)i * ldv + j) * 2 + 1] = 1.0 / x;   // +-inf where x == 0 or padded (reference: division by |v_ji| = 0, :261-262)
+    VQ[((size_t)i * (ldv + 2) + j) * 2] = x;
+    VQ[((size_t)i * (ldv + 2) + j) * 2 + 1] = 1.0 / x;   // +-inf where x == 0 or padded (reference: division by |v_ji| = 0, :261-262)
   }
   s = warp_sum(s); if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
   __syncthreads();
@@ -187,6 +187,8 @@ __global__ void derive_kernel(const double* __restrict__ Vsrc, const int* __rest
     const double mu = s / (di * di);               // :268
     mean[i] = mu;
     zc[i] = di > 1e-16 ? mu : 0.0;
+    VQ[((size_t)i * (ldv + 2) + ldv) * 2] = di; VQ[((size_t)i * (ldv + 2) + ldv) * 2 + 1] = mu;   // column trailer {d_i, mean_i, 1/d_i, 0}
+    VQ[((size_t)i * (ldv + 2) + ldv + 1) * 2] = 1.0 / di; VQ[((size_t)i * (ldv + 2) + ldv + 1) * 2 + 1] = 0.0;
   }
 }
 
@@ -197,13 +199,15 @@ __global__ void derive_from_tv_kernel(const double* __restrict__ tV, const doubl
   for (int j = threadIdx.x; j < ldv; j += blockDim.x) {
     const double x = j < P ? tV[i + (size_t)j * P] : 0.0;
     Vc[(size_t)i * ldv + j] = x;
-    VQ[((size_t)i * ldv + j) * 2] = x;
-    VQ[((size_t)i * ldv + j) * 2 + 1] = 1.0 / x;
+    VQ[((size_t)i * (ldv + 2) + j) * 2] = x;
+    VQ[((size_t)i * (ldv + 2) + j) * 2 + 1] = 1.0 / x;
   }
   if (threadIdx.x == 0) {
     const double di = d[i];
     const double mu = a[i] / (di * di);
     mean[i] = mu; d2[i] = di * di; zc[i] = di > 1e-16 ? mu : 0.0;
+    VQ[((size_t)i * (ldv + 2) + ldv) * 2] = di; VQ[((size_t)i * (ldv + 2) + ldv) * 2 + 1] = mu;
+    VQ[((size_t)i * (ldv + 2) + ldv + 1) * 2] = 1.0 / di; VQ[((size_t)i * (ldv + 2) + ldv + 1) * 2 + 1] = 0.0;
   }
 }
 

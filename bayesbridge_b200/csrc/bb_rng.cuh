@@ -113,6 +113,43 @@ __device__ __forceinline__ bool tn_trial(const TnPlan& p, const Stream& s, uint3
   return tn_eval(p, ua, ub, x);
 }
 
+// ---- latency-trimmed forms for the sweep (bb_tri.cuh): same plan, same trial, shorter dependent chain ----
+// tn_setup_fast decides exponential-vs-uniform tail proposals without sqrt/exp/div whenever the interval is
+// clearly on one side of Robert's threshold: thresh - a = exp(E)/lam with E in (0, 1/2] and
+// lam in [max(1,a), a+1], so  w max(1,a) > e^(1/2)  => mode 2  and  w (a+1) < 1  => mode 3  (w = b - a);
+// only in between is the threshold evaluated.  Identical decisions to tn_setup.
+__device__ __forceinline__ TnPlan tn_setup_fast(double a, double b) {
+  TnPlan p; p.sgn = 1.0; p.lam = 0.0; p.a = a; p.b = b;
+  if (a != a || b != b) { p.mode = 5; return p; }
+  if (!(a < b)) { p.mode = 4; return p; }
+  if (a > 0.0 || b < 0.0) {
+    if (b < 0.0) { p.sgn = -1.0; p.a = -b; p.b = -a; }
+    const double aa = p.a, w = p.b - aa;
+    if (w * (aa + 1.0) < 1.0) { p.mode = 3; return p; }
+    const double sq = sqrt(aa * aa + 4.0);
+    p.lam = 0.5 * (aa + sq);
+    if (w * fmax(1.0, aa) > 1.648721271) { p.mode = 2; return p; }
+    const double thresh = aa + exp(0.5 + 0.25 * (aa * aa - aa * sq)) / p.lam;
+    p.mode = (p.b > thresh) ? 2 : 3;
+    return p;
+  }
+  p.mode = (b - a >= SQRT_2PI) ? 0 : 1;
+  return p;
+}
+// one trial from (ua, ub) with nlu = -log(ua) and lub = log(ub) computed ahead of time; the acceptance
+// tests `ub <= exp(t)` of tn_eval are taken in log form, `log(ub) <= t` (same event up to the last ulp).
+__device__ __forceinline__ bool tn_eval_log(const TnPlan& p, double ua, double ub, double nlu, double lub, double& x) {
+  if (p.mode & 1) {   // 1: uniform proposal around 0, 3: uniform proposal in the tail -- log density (c0 - x^2)/2, c0 = 0 | a^2
+    x = p.a + (p.b - p.a) * ua;
+    const double c0 = p.mode == 3 ? p.a * p.a : 0.0;
+    return lub <= 0.5 * (c0 - x * x);
+  }
+  if (p.mode == 0) { x = sqrt(2.0 * nlu) * cos(TWO_PI * ub); return x >= p.a && x <= p.b; }
+  x = p.a + nlu / p.lam;
+  const double t = x - p.lam;
+  return x <= p.b && lub <= -0.5 * t * t;
+}
+
 // scalar form: one thread
 __device__ inline double tnorm_std_scalar(const Stream& s, double a, double b, uint32_t& status) {
   const TnPlan p = tn_setup(a, b);

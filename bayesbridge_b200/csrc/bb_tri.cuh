@@ -62,10 +62,54 @@ __device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t
                ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+// min that keeps `m` when `x` is NaN: one DSETP + two SEL (fmin() carries a NaN fix-up and costs twice that)
+__device__ __forceinline__ double dmin_keep(double m, double x) { return (x < m) ? x : m; }
+__device__ __forceinline__ double shfl_xor_d(double v, int o) { return __shfl_xor_sync(0xffffffffu, v, o); }
+
+// Reduce NV = 2C per-lane minima over the 32 lanes with a TRANSPOSED butterfly: at the first log2(NV)
+// levels a lane keeps one half of its values and hands the other half to its partner, so the number of
+// live values halves together with the distance; plain butterflies finish the last value.  On return
+// lane l holds the complete minimum of value index  (l >> (5 - log2 NV))  -- for C = 2: lanes 0-7 L0,
+// 8-15 R0, 16-23 L1, 24-31 R1 -- i.e. the {L,R} pair of chain c sits in the lanes of draw slice c.
+// 2C = 4: 7 shuffle rounds of one double instead of 20.
+template <int C>
+__device__ __forceinline__ double reduce_minima(const double (&lmn)[C], const double (&rmn)[C], int lane) {
+  if (C == 1) {
+    const bool hi = lane & 16;
+    double keep = hi ? rmn[0] : lmn[0], send = hi ? lmn[0] : rmn[0];
+    keep = dmin_keep(keep, shfl_xor_d(send, 16));
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) keep = dmin_keep(keep, shfl_xor_d(keep, o));
+    return keep;                                   // lanes 0-15: L, lanes 16-31: R
+  } else if (C == 2) {
+    const bool h16 = lane & 16, h8 = lane & 8;
+    double k0 = h16 ? lmn[1] : lmn[0], k1 = h16 ? rmn[1] : rmn[0];
+    const double s0 = h16 ? lmn[0] : lmn[1], s1 = h16 ? rmn[0] : rmn[1];
+    k0 = dmin_keep(k0, shfl_xor_d(s0, 16)); k1 = dmin_keep(k1, shfl_xor_d(s1, 16));
+    double keep = h8 ? k1 : k0;
+    const double send = h8 ? k0 : k1;
+    keep = dmin_keep(keep, shfl_xor_d(send, 8));
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) keep = dmin_keep(keep, shfl_xor_d(keep, o));
+    return keep;                                   // lanes 0-7 L0, 8-15 R0, 16-23 L1, 24-31 R1
+  } else {
+    // generic fallback (C = 4): full butterflies, then pick
+    double out = 0.0;
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      double a = lmn[c], b = rmn[c];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) { a = dmin_keep(a, shfl_xor_d(a, o)); b = dmin_keep(b, shfl_xor_d(b, o)); }
+      if ((lane >> 3) == c) out = (lane & 4) ? b : a;
+    }
+    return out;                                    // lanes 8c..8c+3: L_c, 8c+4..8c+7: R_c
+  }
+}
+
 // shared-memory footprint of one CTA (bytes); mirrored by the host launcher
 __host__ __device__ inline size_t tri_smem_bytes(int P, int LD, int S, int NG, int W, int C) {
   const size_t CH = (size_t)NG * C;
-  return (size_t)S * LD * 16 + 2 * CH * P * 8 + (size_t)(2 * NG * W * C * 2 + NG * C + NG * C * 2) * 8 + (size_t)2 * S * 8;
+  return (size_t)S * (LD + 2) * 16 + 2 * CH * P * 8 + (size_t)(2 * NG * W * C * 2 + NG * C + NG * C * 2) * 8 + (size_t)2 * S * 8;
 }
 
 // registers live per SM sub-partition (16384 each, warps dealt round-robin over the 4 of them)
@@ -84,8 +128,9 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
   const int g = wid / W, w = wid - g * W;
   const int CH = NG * C;
 
-  double2* ring = reinterpret_cast<double2*>(smem_raw);        // [S][LD]  {V(j,i), 1/V(j,i)}
-  double* z_s = reinterpret_cast<double*>(ring + (size_t)S * LD);   // [CH][P]
+  const int LQ = LD + 2;                                        // column record: LD pairs {V(j,i), 1/V(j,i)} + {d_i, mean_i} + {1/d_i, 0}
+  double2* ring = reinterpret_cast<double2*>(smem_raw);        // [S][LQ]
+  double* z_s = reinterpret_cast<double*>(ring + (size_t)S * LQ);   // [CH][P]
   double* u_s = z_s + (size_t)CH * P;                          // [CH][P]
   double* red = u_s + (size_t)CH * P;                          // [2][NG][W][C][2]
   double* bc = red + 2 * NG * W * C * 2;                       // [NG][C]    delta of the current step
@@ -112,14 +157,14 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
   // Step m reuses the stage of step m - S.  Thread 0 issues step n + S - D when it enters step n, after
   // every warp has released step n - D: S - D columns of prefetch, D steps of slack between the groups.
   const bool issuer = tid == 0;
-  const uint32_t col_bytes = (uint32_t)LD * 16u;
+  const uint32_t col_bytes = (uint32_t)LQ * 16u;
   const long long nload = resident ? (total_steps < P ? total_steps : (long long)P) : total_steps;
   const int D = S > 1 ? S / 2 : 1;
   int is_ = 0, icol = 0; uint32_t iuse = 0; long long inext = 0;   // issuer cursor: stage, column, use count, step
   auto issue_one = [&]() {
     if (iuse > 0) mbar_wait(&empty[is_], (iuse - 1) & 1);
     mbar_arrive_expect_tx(&full[is_], col_bytes);
-    tma_load_1d(ring + (size_t)is_ * LD, L.m.VQ + (size_t)icol * LD * 2, col_bytes, &full[is_]);
+    tma_load_1d(ring + (size_t)is_ * LQ, L.m.VQ + (size_t)icol * LQ * 2, col_bytes, &full[is_]);
     if (++is_ == S) { is_ = 0; ++iuse; }
     if (++icol == P) icol = 0;
     ++inext;
@@ -165,11 +210,12 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
 
   // ring cursor
   int rs = 0; uint32_t ruse = 0; long long nstep = 0;
-  double2 vq[J];
+  double2 vq[J], dm, dm2;   // dm = {d_i, mean_i}, dm2 = {1/d_i, -}
   auto next_column = [&]() {   // wait for the column, copy this lane's slice into registers, release the stage
     if (issuer && inext < nload && inext <= nstep + S - D) issue_one();
     if (!resident || nstep < P) mbar_wait(&full[rs], ruse & 1);
-    const double2* col = ring + (size_t)rs * LD;
+    const double2* col = ring + (size_t)rs * LQ;
+    dm = col[LD]; dm2 = col[LD + 1];
 #pragma unroll
     for (int jj = 0; jj < J; ++jj) {
       const int j = jj * 32 * W + 32 * w + lane;
@@ -323,14 +369,20 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
 #pragma unroll
     for (int c = 1; c < C; ++c) if (dc == c) sig_d = sig2_c[c];
     sig_d = sqrt(sig_d);
+    const double isig_d = 1.0 / sig_d;
+    // RNG look-ahead: the Philox block of a lane's first trial and its two logarithms do not depend on the
+    // bounds.  With W > 1 the warp that draws step i+1 prepares them while the drawer of step i is busy.
+    double ua = 0.5, ub = 0.5, nlu = 0.0, lub = 0.0;
+    bool have_rng = false;
     for (int sw = 0; do_beta && sw < nsweep; ++sw) {
       for (int i = 0; i < P; ++i) {
         const bool drawer = (W == 1) || (w == i % W);
-        // the Philox block of this lane's first trial and the per-step scalars do not depend on the bounds
-        double ua = 0.5, ub = 0.5, di = 0.0, mean = 0.0;
         Stream s(L.key, gch_d, t, ST_BETA, (uint32_t)(sw * P + i));
-        if (drawer) { s.block((uint32_t)sl, ua, ub); di = __ldg(L.m.d + i); mean = __ldg(L.m.mean + i); }
+        if (drawer && !have_rng) { s.block((uint32_t)sl, ua, ub); nlu = -log(ua); lub = log(ub); }
+        have_rng = false;
         next_column();
+        double di = 0.0, mean = 0.0, sd = 1.0, isd = 1.0;
+        if (drawer) { di = dm.x; mean = dm.y; sd = sig_d * dm2.x; isd = di * isig_d; }   // sd = sig/d_i (:269) by reciprocals
         // ---- candidates: min_j fma(beta_j, q, b_j|q|) and min_j fma(-beta_j, q, b_j|q|) ----
         double lmn[C], rmn[C];
 #pragma unroll
@@ -341,23 +393,20 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
 #pragma unroll
           for (int c = 0; c < C; ++c) {
             const double gq = bb_[c][jj] * aq;
-            lmn[c] = fmin(lmn[c], fma(cur[c][jj], q, gq));
-            rmn[c] = fmin(rmn[c], fma(-cur[c][jj], q, gq));
+            lmn[c] = dmin_keep(lmn[c], fma(cur[c][jj], q, gq));
+            rmn[c] = dmin_keep(rmn[c], fma(-cur[c][jj], q, gq));
           }
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1)
-#pragma unroll
-          for (int c = 0; c < C; ++c) {
-            lmn[c] = fmin(lmn[c], __shfl_xor_sync(0xffffffffu, lmn[c], o));
-            rmn[c] = fmin(rmn[c], __shfl_xor_sync(0xffffffffu, rmn[c], o));
-          }
+        // after the transposed butterfly the first half of draw slice c holds L_c, the second half R_c
+        double keep = reduce_minima<C>(lmn, rmn, lane);
         if (W > 1) {
-          if (lane == 0) {
-#pragma unroll
-            for (int c = 0; c < C; ++c) { redg0[(w * C + c) * 2] = lmn[c]; redg0[(w * C + c) * 2 + 1] = rmn[c]; }
-          }
+          if ((sl & (SL / 2 - 1)) == 0) redg0[(w * C + dc) * 2 + (sl >= SL / 2 ? 1 : 0)] = keep;
           bar_sync(bar_id, bar_n);
+          if (!drawer && i + 1 < P && w == (i + 1) % W) {   // idle until the draw is done: prepare the next step's trial
+            Stream sn(L.key, gch_d, t, ST_BETA, (uint32_t)(sw * P + i + 1));
+            sn.block((uint32_t)sl, ua, ub); nlu = -log(ua); lub = log(ub);
+            have_rng = true;
+          }
         }
         if (drawer) {
           // this lane serves chain dc: combine the partial minima
@@ -365,19 +414,17 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
           if (W > 1) {
             lq = CUDART_INF; rq = CUDART_INF;
 #pragma unroll
-            for (int ww = 0; ww < W; ++ww) { lq = fmin(lq, redg0[(ww * C + dc) * 2]); rq = fmin(rq, redg0[(ww * C + dc) * 2 + 1]); }
+            for (int ww = 0; ww < W; ++ww) { lq = dmin_keep(lq, redg0[(ww * C + dc) * 2]); rq = dmin_keep(rq, redg0[(ww * C + dc) * 2 + 1]); }
           } else {
-            lq = lmn[0]; rq = rmn[0];
-#pragma unroll
-            for (int c = 1; c < C; ++c) if (dc == c) { lq = lmn[c]; rq = rmn[c]; }
+            const double other = shfl_xor_d(keep, SL / 2);
+            lq = sl < SL / 2 ? keep : other; rq = sl < SL / 2 ? other : keep;
           }
           const double zold = zg[dc * P + i];
           const double lm = zold - lq, rm = zold + rq;
           double znew;
           if (di > 1e-16) {   // BridgeRegression.cpp:268-273
-            const double sd = sig_d / di;
-            const double a = (lm - mean) / sd, b = (rm - mean) / sd;
-            const TnPlan p = tn_setup(a, b);
+            const double a = (lm - mean) * isd, b = (rm - mean) * isd;
+            const TnPlan p = tn_setup_fast(a, b);
             double x = 0.0;
             bool fin = false;
             if (p.mode == 5) { status |= ST_NAN; x = a + b; fin = true; }
@@ -385,7 +432,7 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
             uint32_t base = 0;
             while (true) {
               double xt = 0.0;
-              const bool acc_ = !fin && tn_eval(p, ua, ub, xt);
+              const bool acc_ = !fin && tn_eval_log(p, ua, ub, nlu, lub, xt);
               const uint32_t mine = __ballot_sync(0xffffffffu, acc_) & slmask;
               const int src = mine ? (__ffs(mine) - 1) : lane;
               const double xs = __shfl_sync(0xffffffffu, xt, src);
@@ -393,7 +440,7 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
               if (__ballot_sync(0xffffffffu, !fin) == 0u) break;
               base += SL;
               if (base >= K_CAP - 32) { if (!fin) { status |= ST_TRIAL_CAP; x = nan(""); fin = true; } break; }
-              if (!fin) s.block(base + (uint32_t)sl, ua, ub);
+              if (!fin) { s.block(base + (uint32_t)sl, ua, ub); nlu = -log(ua); lub = log(ub); }
             }
             znew = mean + sd * x;
             if (znew < lm) znew = lm;
