@@ -28,15 +28,31 @@ constexpr double RS_SQRT_PI = 1.7724538509055159;   // sqrt(M_PI)
 constexpr double RS_C1 = 1.2533141373155001;        // sqrt(M_PI_2)
 constexpr double RS_SQRT2 = 1.41421356237309504880;
 
-// per-item constants (retstable.cpp:121-147); h = beta_j^2/tau^2, alpha = alpha_bridge/2
+// Powers are taken in the log domain: pow(x, y) = exp(y log x) costs ~80 instructions against ~250 for
+// pow(), and the round needs the logarithms of sinc(alpha U), sinc((1-alpha) U), sinc(U) only once for BdB0
+// (retstable.cpp:73-77), A_ (:40-47), a, m and m^-b together.  Relative deviation from the reference's
+// pow() calls <= |y log x| 2^-52 (~1e-14 here), far inside the 1e-10 parity tolerance.
+
+// constants of alpha alone (alpha = alpha_bridge/2), shared by every item of a stage
+struct RetAlpha {
+  double alpha, Ialpha, b, inv_alpha, inv_Ialpha, lA, lI, log_b;
+  __device__ __forceinline__ void init(double alpha_) {
+    alpha = alpha_; Ialpha = 1. - alpha_;
+    b = (1. - alpha_) / alpha_;                // retstable.cpp:123
+    inv_alpha = 1. / alpha_; inv_Ialpha = 1. / (1. - alpha_);
+    lA = log(alpha_); lI = log(1. - alpha_); log_b = log(b);
+  }
+};
+
+// per-item constants (retstable.cpp:121-147); h = beta_j^2/tau^2
 struct RetConst {
-  double h, alpha, b, lambda_alpha, gamma, sgamma, xi, psi, w1, w2, w3;
-  __device__ __forceinline__ void init(double h_, double alpha_) {
-    h = h_; alpha = alpha_;
+  double h, lambda_alpha, log_la, gamma, sgamma, xi, psi, w1, w2, w3;
+  __device__ __forceinline__ void init(double h_, const RetAlpha& A) {
+    h = h_;
     const double c2 = 2. + RS_C1;
-    b = (1. - alpha) / alpha;
-    lambda_alpha = pow(h, alpha);
-    gamma = lambda_alpha * alpha * (1. - alpha);
+    log_la = A.alpha * log(h);                 // log(lambda^alpha); -inf when h = 0
+    lambda_alpha = exp(log_la);                // pow(h, alpha)   (:131)
+    gamma = lambda_alpha * A.alpha * A.Ialpha; // :140
     sgamma = sqrt(gamma);
     const double c3 = c2 * sgamma;
     xi = (1. + RS_SQRT2 * c3) / RS_PI;
@@ -49,13 +65,12 @@ struct RetConst {
 
 // One round starting at block k, as straight-line code: the inner trial (3 Philox blocks,
 // retstable.cpp:162-207) and the outer trial (2 more blocks, :212-256) are BOTH evaluated, the
-// outer one speculatively, so that its pow/exp chain overlaps the inner one instead of waiting
-// behind a branch (the kernels that call this are latency-bound, the FP64 pipe has room).
-// Returns 0 = inner trial rejected (3 blocks consumed), 1 = outer trial rejected (5 blocks),
-// 2 = accepted (value in `out`).  The blocks are the ones the sequential reference would consume
-// at that position of its stream, so the accepted value does not depend on scheduling.
-__device__ __forceinline__ int retstable_round_at(const RetConst& c, const Stream& s, uint32_t k, double& out) {
-  const double alpha = c.alpha, Ialpha = 1. - alpha;
+// outer one speculatively, so that its exp/log chain overlaps the inner one instead of waiting
+// behind a branch.  Returns 0 = inner trial rejected (3 blocks consumed), 1 = outer trial rejected
+// (5 blocks), 2 = accepted (value in `out`).  The blocks are the ones the sequential reference would
+// consume at that position of its stream, so the accepted value does not depend on scheduling.
+__device__ __forceinline__ int retstable_round_at(const RetAlpha& A, const RetConst& c, const Stream& s, uint32_t k, double& out) {
+  const double alpha = A.alpha, Ialpha = A.Ialpha;
   double u0, u0b, u1a, u1b, u2, u2b, u3, u3b, u4a, u4b;
   s.block(k, u0, u0b); s.block(k + 1, u1a, u1b); s.block(k + 2, u2, u2b); s.block(k + 3, u3, u3b); s.block(k + 4, u4a, u4b);
   // ---- inner trial ----
@@ -70,10 +85,13 @@ __device__ __forceinline__ int retstable_round_at(const RetConst& c, const Strea
   }
   const double W = u2;
   const double sA = sinc_mm(alpha * U), sI = sinc_mm(Ialpha * U), sU = sinc_mm(U);
-  const double den = pow(sA, alpha) * pow(sI, Ialpha);      // BdB0 (retstable.cpp:73-77)
-  const double zeta = sqrt(sU / den);
-  const double z = 1 / (1 - pow(1 + alpha * zeta / c.sgamma, -1 / alpha));
-  double rho = RS_PI * exp(-c.lambda_alpha * (1. - 1. / (zeta * zeta))) / ((1. + RS_C1) * c.sgamma / zeta + z);
+  const double lsA = log(sA), lsI = log(sI), lsU = log(sU);
+  const double lden = alpha * lsA + Ialpha * lsI;            // log BdB0 denominator (retstable.cpp:73-77)
+  const double izeta2 = exp(lden) / sU;                      // 1 / zeta^2
+  const double zeta = sqrt(1. / izeta2);
+  // z = 1 / (1 - (1 + alpha zeta / sqrt(gamma))^(-1/alpha))
+  const double z = -1. / expm1(-log1p(alpha * zeta / c.sgamma) * A.inv_alpha);
+  double rho = RS_PI * exp(-c.lambda_alpha * (1. - izeta2)) / ((1. + RS_C1) * c.sgamma / zeta + z);
   double d = 0.;
   if (U >= 0 && c.gamma >= 1) d += c.xi * exp(-c.gamma * U * U / 2.);
   if (U > 0 && U < RS_PI) d += c.psi / sqrt(RS_PI - U);
@@ -82,9 +100,12 @@ __device__ __forceinline__ int retstable_round_at(const RetConst& c, const Strea
   const double Z = W * rho;
   const bool inner_ok = (U < RS_PI && Z <= 1.);
   // ---- outer trial (speculative) ----
-  const double Aval = pow(Ialpha * sI, Ialpha) * pow(alpha * sA, alpha) / sU;   // A_ (retstable.cpp:40-47)
-  const double a = pow(Aval, 1. / (1. - alpha));
-  const double m = pow(c.b / a, alpha) * c.lambda_alpha;
+  // A_ = ((1-alpha) sI)^(1-alpha) (alpha sA)^alpha / sU (:40-47);  a = A_^(1/(1-alpha));  m = (b/a)^alpha lambda^alpha
+  const double lAval = Ialpha * (A.lI + lsI) + alpha * (A.lA + lsA) - lsU;
+  const double la = lAval * A.inv_Ialpha;
+  const double a = exp(la);
+  const double lm = alpha * (A.log_b - la) + c.log_la;
+  const double m = exp(lm);
   const double delta = sqrt(m * alpha / a);
   const double a1 = delta * RS_C1, a2 = delta, a3 = z / a;
   const double ssum = a1 + a2 + a3;
@@ -94,11 +115,11 @@ __device__ __forceinline__ int retstable_round_at(const RetConst& c, const Strea
   else if (V_ < (a1 + a2) / ssum) X = m + delta * u4a;
   else { E_ = -log(u4a); X = m + delta + E_ * a3; }
   const double E = -log(Z);
+  out = exp(-A.b * log(X));   // X^-b = exp(1/alpha*log(V0) - b*log(X)) with V0 = 1 (retstable.cpp:270)
   double cc = a * (X - m);
-  cc += (m != 0) ? c.h * (pow(X, -1. * c.b) - pow(m, -1. * c.b)) : 0.0;
+  cc += (m != 0) ? c.h * (out - exp(-A.b * lm)) : 0.0;       // h (X^-b - m^-b)  (:248)
   if (X < m) cc -= N_ * N_ / 2.;
   else if (X > m + delta) cc -= E_;
-  out = exp(-c.b * log(X));   // exp(1/alpha*log(V0) - b*log(X)) with V0 = 1 (retstable.cpp:270)
   if (!inner_ok) return 0;
   return (X >= 0 && cc <= E) ? 2 : 1;
 }
@@ -106,10 +127,11 @@ __device__ __forceinline__ int retstable_round_at(const RetConst& c, const Strea
 // sequential form, one thread per item
 __device__ inline double retstable_scalar(const Stream& s, double h, double alpha, uint32_t& status) {
   if (alpha == 1.) return 1.0;  // point mass at V0 (retstable.cpp:104-110)
-  RetConst c; c.init(h, alpha);
+  RetAlpha A; A.init(alpha);
+  RetConst c; c.init(h, A);
   uint32_t k = 0; double out = 0.;
   while (k < K_CAP - 8) {
-    const int r = retstable_round_at(c, s, k, out);
+    const int r = retstable_round_at(A, c, s, k, out);
     if (r == 2) return out;
     k += r == 0 ? 3u : 5u;
   }
@@ -148,6 +170,7 @@ __device__ inline void lambda_stage_cta(int P, const double* beta, double* lam_o
     __syncthreads();
     return;
   }
+  RetAlpha A; A.init(alpha_half);
   while (n_act > 0) {
     int G = 1;
     while (G < 32 && n_act * (G * 2) <= NT) G *= 2;
@@ -165,11 +188,11 @@ __device__ inline void lambda_stage_cta(int P, const double* beta, double* lam_o
         if (rc_s && !first) rc = rc_s[j];
         else {
           const double b = beta[j];
-          rc.init(b * b / (tau * tau), alpha_half);   // h = beta_j^2 / tau^2 (BridgeRegression.cpp:509)
+          rc.init(b * b / (tau * tau), A);   // h = beta_j^2 / tau^2 (BridgeRegression.cpp:509)
           if (rc_s && sub == 0) rc_s[j] = rc;
         }
         Stream s(key, gch, t, ST_LAMBDA, (uint32_t)j);
-        code = retstable_round_at(rc, s, k0 + (uint32_t)rs_reach(sub), out);
+        code = retstable_round_at(A, rc, s, k0 + (uint32_t)rs_reach(sub), out);
       }
       // walk the sequential path through the G evaluated offsets (uniform trip count: shuffles)
       int pos = 0, res = -1;

@@ -1,5 +1,6 @@
 // bb_stb.cu -- host launcher of the on-chip stable-mixture sweep kernel (bb_stb.cuh, P <= 128).
 #include "bb_stb.cuh"
+#include "bb_stb64.cuh"
 
 namespace bb {
 namespace {
@@ -18,7 +19,12 @@ void launch_tb(const StbLaunch& L, cudaStream_t st) {
 }  // namespace
 
 int launch_stb_small(const StbLaunch& L, cudaStream_t st) {
-  if (L.m.P <= 64) launch_tb<4>(L, st); else launch_tb<8>(L, st);
+  if (L.m.P <= 64) {
+    const size_t smem = stb64_smem_bytes();
+    BB_CUDA_CHECK(cudaFuncSetAttribute(stb64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    stb64_kernel<<<L.nchains, S64_T, smem, st>>>(L);
+    check_launch();
+  } else launch_tb<8>(L, st);
   return 1;
 }
 

@@ -1,0 +1,217 @@
+// bb_stb64.cuh -- the stable (normal scale mixture) Gibbs sweep for P <= 64: one chain per CTA of
+// 128 threads, everything on chip.
+//
+// One launch advances `nchains` chains by `niter` iterations of
+//   tau -> sig2 -> lambda -> beta                 (/root/reference/Code/C/BridgeWrapper.cpp:287-298)
+// with   sample_tau_marg  BridgeRegression.cpp:453-465     sample_sig2  :436-450
+//        sample_lambda    :506-510 -> retstable_LD retstable.cpp:94-271   (bb_retstable.cuh)
+//        sample_beta_stable :552-575  (Cholesky of X'X + diag(lambda sig2/tau^2), triangular solves).
+//
+// The kernel is bound by instruction issue and by the length of its dependent chains, not by
+// arithmetic (P^3/3 = 87k flops per chain-iteration), so the Cholesky is organised for FEW
+// instructions and ONE barrier per column:
+//   * the 64 x 64 system sits in shared memory with row stride 65 (conflict-free by rows and by columns);
+//   * thread (t, h) = (tid & 63, tid >> 6) owns row t and the columns j = h (mod 2) of it: at step k it
+//     applies  S(t,j) -= S(t,k)/S(k,k) * S(j,k)  for k < j <= t  -- S(j,k) is one broadcast LDS;
+//   * columns are left UNSCALED during the factorisation (L(t,k) = S(t,k) rs_k with rs_k = S(k,k)^-1/2
+//     published per step), so a step never rewrites what other threads still read and one
+//     __syncthreads per column suffices; the thread that completes the next pivot publishes its
+//     reciprocal and rsqrt before the barrier, off everyone else's critical path;
+//   * w = L^-1 Xy (the reference's first trsm, :564) rides along as one extra FMA per row and step, and
+//     since both of the reference's back-substitutions use the same factor, beta = U^-1 (w + sig eps) is
+//     ONE back-substitution (:565,:570-574), done by one warp with the row of L broadcast from smem.
+#pragma once
+#include "bb_launch.h"
+#include "bb_retstable.cuh"
+
+namespace bb {
+
+constexpr int S64_T = 128;     // threads per CTA
+constexpr int S64_P = 64;      // padded dimension
+constexpr int S64_LD = 65;     // row stride of the system in shared memory
+
+__host__ __device__ inline size_t stb64_smem_bytes() {
+  return (size_t)(S64_P * S64_LD + 7 * S64_P + 32) * sizeof(double) + (size_t)(3 * S64_P + 4) * sizeof(int) + (size_t)S64_P * sizeof(RetConst);
+}
+
+__global__ void __launch_bounds__(S64_T, 4) stb64_kernel(const StbLaunch L) {
+  extern __shared__ double smem[];
+  const int P = L.m.P;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr int NW = S64_T / 32;
+  constexpr int PP = S64_P, LD = S64_LD;
+
+  double* S = smem;                        // [PP][LD]  lower triangle: unscaled columns of the factor
+  double* beta_s = S + PP * LD;            // [PP]
+  double* lam_s = beta_s + PP;             // [PP]
+  double* dl_s = lam_s + PP;               // [PP]   beta - bc
+  double* rhs_s = dl_s + PP;               // [PP]   w + sig*eps
+  double* rs_s = rhs_s + PP;               // [PP]   1 / sqrt(pivot_k) = 1 / L(k,k)
+  double* ip_s = rs_s + PP;                // [PP]   1 / pivot_k
+  double* rb_s = ip_s + PP;                // [PP]   forward-substitution residual r_k when row k becomes the pivot row
+  double* red_s = rb_s + PP;               // [3][8]
+  double* sc_s = red_s + 24;               // tau, sig2 (+ pad to 32)
+  int* q_s = reinterpret_cast<int*>(red_s + 32);            // [2][PP] retry queues
+  int* qn_s = q_s + 2 * PP;                                 // [2] counts
+  uint32_t* kk_s = reinterpret_cast<uint32_t*>(qn_s + 2);   // [PP] next Philox block per coordinate
+  RetConst* rc_s = reinterpret_cast<RetConst*>(kk_s + PP + 2);   // [PP]
+
+  const int ch = blockIdx.x;
+  if (ch >= L.nchains) return;
+  const uint32_t gch = L.chain0 + (uint32_t)ch;
+  const int t = tid & 63, h = tid >> 6;    // row, column parity
+
+  const double alpha = L.h.true_alpha;
+  const bool know_tau = L.h.true_tau > 0, know_sig2 = L.h.true_sig2 > 0;
+  const bool do_tau = (L.stages & 1) && !know_tau, do_sig2 = (L.stages & 2) && !know_sig2;
+  const bool do_lambda = L.stages & 32, do_beta = L.stages & 16;
+  uint32_t status = 0;
+
+  for (int j = tid; j < PP; j += S64_T) {
+    beta_s[j] = j < P ? L.beta[(size_t)ch * P + j] : 0.0;
+    lam_s[j] = j < P ? L.lambda[(size_t)ch * P + j] : 1.0;
+  }
+  if (tid == 0) { sc_s[0] = know_tau ? L.h.true_tau : L.tau[ch]; sc_s[1] = know_sig2 ? L.h.true_sig2 : L.sig2[ch]; qn_s[0] = 0; qn_s[1] = 0; }
+  __syncthreads();
+
+  for (int it = -L.pre_tau; it < L.niter; ++it) {
+    const bool pre = it < 0;
+    const uint32_t tt = L.iter0 + (pre ? 0u : (uint32_t)it);
+
+    // ---- partial sums for tau and the residual sum of squares ----
+    if (tid < PP) dl_s[tid] = tid < P ? beta_s[tid] - __ldg(L.m.bc + tid) : 0.0;
+    __syncthreads();
+    double p_tau = 0.0, p_q = 0.0, p_g = 0.0;
+    if (tid < P) {
+      const double b = beta_s[tid];
+      p_tau = exp(alpha * log(fabs(b)));                       // BridgeRegression.cpp:459
+      if (!pre && do_sig2) {                                   // rss = r0 - 2 d'g + d'XXd, d = beta - bc
+        double s = 0.0;
+        for (int j = 0; j < P; ++j) s = fma(__ldg(L.m.XX + tid + (size_t)j * P), dl_s[j], s);
+        p_q = dl_s[tid] * s;
+        p_g = dl_s[tid] * __ldg(L.m.gc + tid);
+      }
+    }
+    p_tau = warp_sum(p_tau); p_q = warp_sum(p_q); p_g = warp_sum(p_g);
+    if (lane == 0) { red_s[warp] = p_tau; red_s[8 + warp] = p_q; red_s[16 + warp] = p_g; }
+    __syncthreads();
+    if (warp == 0 && (do_tau || (pre && !know_tau))) {          // BridgeRegression.cpp:453-465
+      double st = lane < NW ? red_s[lane] : 0.0;
+      st = warp_sum(st);
+      const double shape = L.h.nu_shape + ((double)P) / alpha;
+      const double rate = L.h.nu_rate + st;
+      Stream s(L.key, gch, tt, pre ? ST_TAU_INIT : ST_TAU, 0);
+      const double nu = gamma_rate<true>(s, shape, rate, status);
+      if (lane == 0) sc_s[0] = exp(-1.0 * log(nu) / alpha);
+    }
+    if (warp == 1 && !pre && do_sig2) {                         // BridgeRegression.cpp:436-450
+      double sq = lane < NW ? red_s[8 + lane] : 0.0, sg = lane < NW ? red_s[16 + lane] : 0.0;
+      sq = warp_sum(sq); sg = warp_sum(sg);
+      const double rss = L.m.r0b - 2.0 * sg + sq;
+      const double shape = L.h.sig2_shape + 0.5 * L.m.N;
+      const double scale = L.h.sig2_scale + 0.5 * rss;
+      Stream s(L.key, gch, tt, ST_SIG2, 0);
+      const double g = gamma_rate<true>(s, shape, 1.0, status);
+      if (lane == 0) sc_s[1] = scale / g;
+    }
+    __syncthreads();
+    if (pre) continue;
+    const double tau = sc_s[0], sig2 = sc_s[1];
+
+    // ---- lambda_j = 2 * retstable(beta_j^2 / tau^2, alpha/2): retry queue + speculative look-ahead ----
+    if (do_lambda) lambda_stage_cta<S64_T>(P, beta_s, lam_s, tau, 0.5 * alpha, L.key, gch, tt, rc_s, q_s, PP, qn_s, kk_s, status);
+    else __syncthreads();
+
+    if (do_beta) {
+      // ---- S = X'X + diag(lambda sig2 / tau^2)   (BridgeRegression.cpp:554-556), lower triangle ----
+      const double f = sig2 / (tau * tau);
+      for (int j = h; j <= t; j += 2) {
+        double v = (t < P && j < P) ? __ldg(L.m.XX + t + (size_t)j * P) : (t == j ? 1.0 : 0.0);
+        if (t == j && t < P) v += lam_s[t] * f;
+        S[t * LD + j] = v;
+        if (t == 0) {   // first pivot (thread (0,0))
+          if (!(v > 0.0)) status |= ST_CHOL_FAIL;
+          ip_s[0] = 1.0 / v; rs_s[0] = rsqrt(v);
+        }
+      }
+      double r = (h == 0 && t < P) ? __ldg(L.m.Xy + t) : 0.0;   // forward-substitution residual of row t
+      if (tid == 0) rb_s[0] = r;
+      // normals for the noise term (BridgeRegression.cpp:567-568), one item per coordinate
+      double eps = 0.0;
+      if (tid < P) { Stream s(L.key, gch, tt, ST_BETA_STB, (uint32_t)tid); eps = s.norm(0); }
+      __syncthreads();
+
+      // ---- right-looking Cholesky with unscaled columns, one barrier per column ----
+      for (int k = 0; k < PP - 1; ++k) {
+        if (t > k) {
+          const double lip = S[t * LD + k] * ip_s[k];          // S(t,k) / pivot_k  =  L(t,k) rs_k
+          int j = k + 1 + ((k + 1 + h) & 1);                   // first column > k of my parity
+          double* row = S + t * LD;
+          const double* colk = S + k;
+#pragma unroll 4
+          for (; j <= t; j += 2) row[j] = fma(-lip, colk[j * LD], row[j]);
+          if (h == 0) r = fma(-lip, rb_s[k], r);               // r_t -= L(t,k) w_k
+          if (t == k + 1) {                                    // row k+1 is the next pivot row
+            if (h == ((k + 1) & 1)) {
+              const double piv = row[t];
+              if (!(piv > 0.0)) status |= ST_CHOL_FAIL;
+              ip_s[k + 1] = 1.0 / piv; rs_s[k + 1] = rsqrt(piv);
+            }
+            if (h == 0) rb_s[k + 1] = r;
+          }
+        }
+        __syncthreads();
+      }
+      // w = L^-1 Xy is rb_s[k] rs_k;  rhs = w + sig eps
+      const double sig = sqrt(sig2);
+      if (tid < PP) rhs_s[tid] = tid < P ? fma(sig, eps, rb_s[tid] * rs_s[tid]) : 0.0;
+      __syncthreads();
+
+      // ---- back-substitution  L' x = rhs  with L(k,i) = S(k,i) rs_i :  x_i = (rhs_i - rs_i acc_i) rs_i,
+      //      acc_i = sum_{k>i} S(k,i) x_k   (the reference's trsm(U, ., 'U','L'), :565,570) ----
+      if (warp == 0) {
+        const double rs0 = rs_s[lane], rs1 = rs_s[lane + 32];
+        const double rh0 = rhs_s[lane], rh1 = rhs_s[lane + 32];
+        double acc0 = 0.0, acc1 = 0.0;
+        for (int k = PP - 1; k >= 0; --k) {
+          const double sk0 = S[k * LD + lane], sk1 = S[k * LD + lane + 32];   // row k (independent of x_k: issued early)
+          const double cand = (k >= 32) ? (rh1 - rs1 * acc1) * rs1 : (rh0 - rs0 * acc0) * rs0;
+          const double xk = __shfl_sync(0xffffffffu, cand, k & 31);
+          if (lane == 0) beta_s[k] = xk;
+          if (lane < k) acc0 = fma(sk0, xk, acc0);
+          if (lane + 32 < k) acc1 = fma(sk1, xk, acc1);
+        }
+      }
+      __syncthreads();
+    }  // do_beta
+
+    // ---- store ----
+    const bool store = L.sink.thin > 0 && ((it + 1) % L.sink.thin) == 0;
+    if (store) {
+      const long long slot = L.sink.s0 + (it + 1) / L.sink.thin - 1;
+      for (int j = tid; j < P; j += S64_T) {
+        const size_t o = ((size_t)ch * L.sink.chain_stride + slot) * P + j;
+        if (L.sink.beta) L.sink.beta[o] = beta_s[j];
+        if (L.sink.lambda) L.sink.lambda[o] = lam_s[j];
+        if (L.sink.sum) { L.sink.sum[(size_t)ch * P + j] += beta_s[j]; L.sink.sumsq[(size_t)ch * P + j] += beta_s[j] * beta_s[j]; }
+      }
+      if (tid == 0) {
+        const size_t o = (size_t)ch * L.sink.chain_stride + slot;
+        if (L.sink.sig2) L.sink.sig2[o] = sig2;
+        if (L.sink.tau) L.sink.tau[o] = tau;
+        if (L.sink.alpha) L.sink.alpha[o] = alpha;
+      }
+    }
+  }
+
+  __syncthreads();
+  for (int j = tid; j < P; j += S64_T) {
+    L.beta[(size_t)ch * P + j] = beta_s[j];
+    L.lambda[(size_t)ch * P + j] = lam_s[j];
+  }
+  if (tid == 0) { L.tau[ch] = sc_s[0]; L.sig2[ch] = sc_s[1]; L.alpha[ch] = alpha; }
+  status = __reduce_or_sync(0xffffffffu, status);
+  if (lane == 0 && status) atomicOr(L.status + ch, status);
+}
+
+}  // namespace bb
