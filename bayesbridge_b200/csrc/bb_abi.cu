@@ -557,13 +557,19 @@ void run_driver(int method, int ortho, const double* X, const double* y, int N, 
   if (nsamp < 1 || burn < 0 || nchains < 1) throw std::string("bridge driver: need nsamp >= 1, burn >= 0, nchains >= 1");
   if (thin < 1) thin = 1;
   struct Guard { bb_model* m = nullptr; bb_chains* c = nullptr; ~Guard() { delete c; delete m; } } g;
+  auto tp0 = std::chrono::steady_clock::now();
+  auto lap = [&](const char* what) {
+    if (g_verbose >= 2) { auto n = std::chrono::steady_clock::now(); std::printf("  [driver] %-22s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(n - tp0).count()); tp0 = n; }
+  };
   g.m = bb_model_create(X, y, N, P, device, BB_MEM_HOST);
   if (!g.m) throw std::string(g_err);
+  lap("model (upload+factors)");
   g.c = bb_chains_create(g.m, method, ortho, nchains, seed, chain0);
   if (!g.c) throw std::string(g_err);
   int mask = BB_OUT_BETA | BB_OUT_SIG2 | BB_OUT_TAU | BB_OUT_ALPHA;
   mask |= (method == BB_TRI) ? (BB_OUT_U | BB_OUT_OMEGA | BB_OUT_SHAPE) : BB_OUT_LAMBDA;
   if (bb_chains_reserve(g.c, nsamp, mask)) throw std::string(g_err);
+  lap("chains + draw buffer");
   if (g_verbose) {
     std::printf("Bridge Regression (%s): known alpha=%g", method == BB_TRI ? "mix. of triangles" : "mix. of normals", h->true_alpha);
     if (h->true_sig2 > 0) std::printf(", sig2=%g", h->true_sig2);
@@ -577,6 +583,7 @@ void run_driver(int method, int ortho, const double* X, const double* y, int N, 
   else pre = ortho ? 0 : 1;                           // :262 / none (:490)
   chains_run(g.c, h, 0u, nburn, BB_ST_ALL, pre & 1, (pre >> 1) & 1, 0, 0, nullptr);
   if (bb_chains_store_state(g.c, 0)) throw std::string(g_err);     // sample 0 = state after burn-in
+  lap("burn-in");
   auto t0 = std::chrono::steady_clock::now();
   const long long total = (long long)(nsamp - 1) * thin;
   long long done = 0;
@@ -588,12 +595,14 @@ void run_driver(int method, int ortho, const double* X, const double* y, int N, 
   }
   const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   if (runtime) *runtime = secs;
+  lap("sampling loop");
   auto fetch = [&](int which, double* out) { if (out && bb_chains_fetch(g.c, which, 0, nsamp, out)) throw std::string(g_err); };
   fetch(BB_OUT_BETA, beta);
   if (method == BB_TRI) { fetch(BB_OUT_U, aux1); fetch(BB_OUT_OMEGA, aux2); fetch(BB_OUT_SHAPE, aux3); }
   else fetch(BB_OUT_LAMBDA, aux1);
   fetch(BB_OUT_SIG2, sig2); fetch(BB_OUT_TAU, tau); fetch(BB_OUT_ALPHA, alpha);
   if (status && bb_chains_get(g.c, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, status)) throw std::string(g_err);
+  lap("download");
   if (g_verbose) std::printf("Sampling complete: %g sec. for %i iterations.\n", secs, nsamp);
 }
 

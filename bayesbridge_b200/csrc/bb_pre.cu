@@ -64,7 +64,26 @@ int jacobi_device(double* W, double* V, int M, int P, cudaStream_t st) {
   BB_CUDA_CHECK(cudaMemcpyAsync(d_sched, sched.data(), sched.size() * sizeof(int), cudaMemcpyHostToDevice, st));
   unsigned long long* d_conv = dalloc<unsigned long long>(1);
   set_identity_kernel<<<296, 256, 0, st>>>(V, P); check_launch(); ++n;
-  for (int sweep = 0; sweep < 40 && P > 1; ++sweep) {
+  // one cooperative launch when every pair's CTA can be resident at once (always, up to P ~ 2000)
+  constexpr int MAX_SWEEPS = 40;
+  int dev = 0, nsm = 0, per_sm = 0, coop = 0;
+  BB_CUDA_CHECK(cudaGetDevice(&dev));
+  BB_CUDA_CHECK(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));
+  BB_CUDA_CHECK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+  BB_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, jacobi_persistent_kernel, 256, 0));
+  if (coop && P > 1 && npairs <= nsm * per_sm) {
+    unsigned long long* d_convs = dalloc<unsigned long long>(MAX_SWEEPS);
+    unsigned int* d_counter = dalloc<unsigned int>(1);
+    BB_CUDA_CHECK(cudaMemsetAsync(d_convs, 0, MAX_SWEEPS * sizeof(unsigned long long), st));
+    BB_CUDA_CHECK(cudaMemsetAsync(d_counter, 0, sizeof(unsigned int), st));
+    int max_sweeps = MAX_SWEEPS;
+    void* args[] = {&W, &V, &M, &P, &d_sched, &rounds, &npairs, &d_convs, &d_counter, &max_sweeps};
+    BB_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)jacobi_persistent_kernel, dim3(npairs), dim3(256), args, 0, st));
+    ++n;
+    BB_CUDA_CHECK(cudaStreamSynchronize(st));
+    dfree(d_convs); dfree(d_counter);
+  } else
+  for (int sweep = 0; sweep < MAX_SWEEPS && P > 1; ++sweep) {
     BB_CUDA_CHECK(cudaMemsetAsync(d_conv, 0, sizeof(unsigned long long), st));
     for (int r = 0; r < rounds; ++r) {
       jacobi_round_kernel<<<npairs, 256, 0, st>>>(W, V, M, P, d_sched + (size_t)r * npairs * 2, d_conv);

@@ -145,6 +145,74 @@ __global__ void __launch_bounds__(256) jacobi_round_kernel(double* __restrict__ 
   for (int k = tid; k < P; k += 256) { const double a = vp[k], b = vq[k]; vp[k] = c * a - s * b; vq[k] = s * a + c * b; }
 }
 
+// The same rotation as a device function (one CTA, one column pair), shared by the per-round kernel above
+// in spirit and used by the persistent form below.
+__device__ __forceinline__ void jacobi_rotate_pair(double* __restrict__ W, double* __restrict__ V, int M, int P, int p, int q,
+                                                   unsigned long long* conv, double (*red)[8], double* cs) {
+  double* wp = W + (size_t)p * M; double* wq = W + (size_t)q * M;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double al = 0, be = 0, ga = 0;
+  for (int k = tid; k < M; k += 256) { const double a = __ldcg(wp + k), b = __ldcg(wq + k); al = fma(a, a, al); be = fma(b, b, be); ga = fma(a, b, ga); }
+  al = warp_sum(al); be = warp_sum(be); ga = warp_sum(ga);
+  if (lane == 0) { red[0][warp] = al; red[1][warp] = be; red[2][warp] = ga; }
+  __syncthreads();
+  if (tid == 0) {
+    al = be = ga = 0;
+    for (int w = 0; w < 8; ++w) { al += red[0][w]; be += red[1][w]; ga += red[2][w]; }
+    double c = 1.0, s = 0.0;
+    const double denom = sqrt(al * be);
+    const double rel = denom > 0 ? fabs(ga) / denom : 0.0;
+    if (rel > 1e-15 && ga != 0.0) {
+      const double zeta = (be - al) / (2.0 * ga);
+      const double t = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+      c = 1.0 / sqrt(1.0 + t * t); s = c * t;
+      atomicMax(conv, (unsigned long long)__double_as_longlong(rel));
+    }
+    cs[0] = c; cs[1] = s;
+  }
+  __syncthreads();
+  const double c = cs[0], s = cs[1];
+  if (s != 0.0) {
+    for (int k = tid; k < M; k += 256) { const double a = __ldcg(wp + k), b = __ldcg(wq + k); wp[k] = c * a - s * b; wq[k] = s * a + c * b; }
+    double* vp = V + (size_t)p * P; double* vq = V + (size_t)q * P;
+    for (int k = tid; k < P; k += 256) { const double a = __ldcg(vp + k), b = __ldcg(vq + k); vp[k] = c * a - s * b; vq[k] = s * a + c * b; }
+  }
+  __syncthreads();
+}
+
+// Grid-wide barrier for a cooperative launch (all CTAs co-resident): monotone ticket counter.
+__device__ __forceinline__ void grid_barrier(unsigned int* counter, unsigned int& epoch) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    epoch += gridDim.x;
+    __threadfence();
+    atomicAdd(counter, 1u);
+    while (*((volatile unsigned int*)counter) < epoch) { }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+// Persistent one-sided Jacobi: the whole tournament (all rounds of up to `max_sweeps` sweeps) in ONE cooperative
+// launch, CTA b = pair b of the round, a grid barrier between rounds -- replaces rounds x sweeps tiny launches
+// (567 for P = 64), which dominated the end-to-end time of short runs.  conv[s] collects the largest rotation
+// of sweep s; every CTA reads it after the sweep's last barrier and stops when it is zero.
+__global__ void __launch_bounds__(256) jacobi_persistent_kernel(double* __restrict__ W, double* __restrict__ V, int M, int P,
+                                                                const int* __restrict__ sched, int rounds, int npairs,
+                                                                unsigned long long* conv, unsigned int* counter, int max_sweeps) {
+  __shared__ double red[3][8];
+  __shared__ double cs[2];
+  unsigned int epoch = 0;
+  for (int sweep = 0; sweep < max_sweeps; ++sweep) {
+    for (int r = 0; r < rounds; ++r) {
+      const int p = sched[((size_t)r * npairs + blockIdx.x) * 2], q = sched[((size_t)r * npairs + blockIdx.x) * 2 + 1];
+      if (p >= 0 && q >= 0 && p < P && q < P) jacobi_rotate_pair(W, V, M, P, p, q, conv + sweep, red, cs);
+      grid_barrier(counter, epoch);
+    }
+    if (*((volatile unsigned long long*)(conv + sweep)) == 0ull) break;
+  }
+}
+
 __global__ void set_identity_kernel(double* V, int P) {
   for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < (size_t)P * P; e += (size_t)gridDim.x * blockDim.x)
     V[e] = (e % P == e / P) ? 1.0 : 0.0;

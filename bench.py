@@ -46,8 +46,9 @@ WORKLOADS = {
 
 
 def algorithmic_flops_per_chain_iter(method, P):
-    """triangle 10 P^2 FP64 ops; stable P^3/3 + 5 P^2 flops."""
-    return 10.0 * P * P if method == "triangle" else P ** 3 / 3.0 + 5.0 * P * P
+    """triangle 6 P^2 FP64 operations (1 mul, 2 FMA, 2 min, 1 axpy FMA per (i,j); SURVEY.md
+    section 8(d) counted 10 for the as-written form); stable P^3/3 + 5 P^2 flops (Cholesky + solves + rss form)."""
+    return 6.0 * P * P if method == "triangle" else P ** 3 / 3.0 + 5.0 * P * P
 
 
 class ClockSampler:
@@ -220,6 +221,8 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device; the sampler has no CPU fallback (use --impl reference for the CPU arm)")
     dev = torch.device("cuda", local)
     L = bb._lib.load()
+    if os.environ.get("BB_VERBOSE"):
+        L.bb_set_verbose(int(os.environ["BB_VERBOSE"]))   # 2: per-phase timings of the batched driver on stdout
     wl = WORKLOADS[args.workload]
     cfg, (X, y, _) = make_data(args.workload)
     method, alpha = cfg["method"], cfg["alpha"]
@@ -282,13 +285,15 @@ def run_ours(args):
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
     if os.path.exists(tpath):
-        traffic = json.load(open(tpath)).get(args.workload)
+        traffic = (json.load(open(tpath)).get(args.workload) or {}).get("bytes_per_launch")
     store_bytes = 8.0 * P * nch * ips
     roofline = {"bound": "tensor", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak,
                 "traffic": traffic, "kernel": kernel_name(method, P),
                 "peak_source": "cuBLAS DGEMM 8192^3 measured in this run (FP64; MEASURED_PEAKS.json carries no FP64 figure)",
                 "algorithmic_flops_per_chain_iter": algorithmic_flops_per_chain_iter(method, P),
-                "hbm_store_GBs": store_bytes * args.steps / T_local / 1e9, "hbm_peak_GBs": measured_hbm()}
+                "hbm_store_GBs": store_bytes * args.steps / T_local / 1e9, "hbm_peak_GBs": measured_hbm(),
+                "note": "FP64 path: no bf16/HBM roofline applies; the sweep kernels are issue/latency-bound (sequential Gibbs steps, "
+                        "3.5 chains per SM), see profiles/*.md for fp64-pipe utilisation and stall breakdowns"}
 
     # ---- ESS/sec from the draws of the timed region (coda definition, bayesbridge_b200/ess.py) ----
     ess_info = None
@@ -325,6 +330,8 @@ def run_ours(args):
 def kernel_name(method, P):
     if method == "triangle":
         return "tri_sweep_kernel"
+    if P <= 64:
+        return "stb64_kernel"
     return "stb_small_kernel" if P <= 128 else "stbl_syrk_kernel (+potrf/trsm/solve)"
 
 
