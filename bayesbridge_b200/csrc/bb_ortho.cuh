@@ -157,7 +157,7 @@ __global__ void __launch_bounds__(ORT_T) ortho_kernel(const OrthoLaunch L) {
       }
     } else {
       // lambda (BridgeRegression.cpp:506-510): retry queue + speculative look-ahead (bb_retstable.cuh)
-      if (do_lambda) lambda_stage_cta<ORT_T>(P, beta_s, b_s, tau, 0.5 * alpha, L.key, gch, t, nullptr, q_s, P, qn_s, kk_s, status);
+      if (do_lambda) lambda_stage_cta<ORT_T>(tid, P, beta_s, b_s, tau, 0.5 * alpha, L.key, gch, t, nullptr, q_s, P, qn_s, kk_s, status);
       if (do_sig2) draw_sig2(t);
       const double sig2 = sc[1];
       if (do_beta) {

@@ -154,15 +154,16 @@ __device__ inline double retstable_scalar(const Stream& s, double h, double alph
 __device__ __forceinline__ int rs_reach(int i) { return i < 4 ? ((0x6530 >> (4 * i)) & 0xF) : i + 4; }     // 0,3,5,6,8,9,10,...
 __device__ __forceinline__ int rs_slot_of(int pos) { return pos >= 8 ? pos - 4 : (pos == 0 ? 0 : pos == 3 ? 1 : pos == 5 ? 2 : pos == 6 ? 3 : 64); }
 
-// NT: threads of the CTA (multiple of 32); every thread of the CTA must call.  beta: per-item
+// NT: threads serving one chain (multiple of 32); every thread of the CTA must call.  beta: per-item
 // coordinate values (shared or global), lam_out: where 2*draw goes (shared or global).
 // q_s: [2][qld] ints, qn_s: [2] ints (both zero on entry and on exit), kk_s: [P] block positions.
 // rc_s: optional [P] cache of the per-item constants (nullptr: recompute every pass).
 template <int NT>
-__device__ inline void lambda_stage_cta(int P, const double* beta, double* lam_out, double tau, double alpha_half,
+__device__ inline void lambda_stage_cta(const int tid, int P, const double* beta, double* lam_out, double tau, double alpha_half,
                                         const RngKey key, uint32_t gch, uint32_t t, RetConst* rc_s,
                                         int* q_s, int qld, int* qn_s, uint32_t* kk_s, uint32_t& status) {
-  const int tid = threadIdx.x;
+  // `tid` = index of the thread among the NT threads that serve THIS chain (a CTA may hold several chains,
+  // each with its own queues; the barriers are CTA-wide and the loop runs until every chain is done)
   int cur_q = 0, n_act = P;
   bool first = true;
   if (alpha_half == 1.) {   // point mass at V0 = 1 (retstable.cpp:104-110)
@@ -171,13 +172,14 @@ __device__ inline void lambda_stage_cta(int P, const double* beta, double* lam_o
     return;
   }
   RetAlpha A; A.init(alpha_half);
-  while (n_act > 0) {
+  bool any = true;
+  while (any) {
     int G = 1;
     while (G < 32 && n_act * (G * 2) <= NT) G *= 2;
     const int per_pass = NT / G;
     const int sub = tid & (G - 1);
     int nlvl = rs_reach(G - 1) / 3 + 1;
-    for (int base = 0; base < n_act; base += per_pass) {
+    for (int base = 0; base < n_act; base += per_pass) {   // (no pass for a chain that is already done: n_act = 0)
       const int slot = base + tid / G;
       const bool valid = slot < n_act;
       int j = 0; uint32_t k0 = 0; int code = 2; double out = 0.0;
@@ -221,7 +223,7 @@ __device__ inline void lambda_stage_cta(int P, const double* beta, double* lam_o
     n_act = qn_s[cur_q];
     first = false;
     if (tid == 0) qn_s[cur_q ^ 1] = 0;   // the queue the next pass fills
-    __syncthreads();
+    any = __syncthreads_or(n_act > 0);
   }
 }
 

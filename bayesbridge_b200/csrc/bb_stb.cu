@@ -1,4 +1,5 @@
 // bb_stb.cu -- host launcher of the on-chip stable-mixture sweep kernel (bb_stb.cuh, P <= 128).
+#include <cstdlib>
 #include "bb_stb.cuh"
 #include "bb_stb64.cuh"
 
@@ -16,14 +17,26 @@ void launch_tb(const StbLaunch& L, cudaStream_t st) {
   check_launch();
 }
 
+template <bool TC, int NCH>
+void launch64(const StbLaunch& L, cudaStream_t st) {
+  const size_t smem = stb64_smem_bytes() * NCH;
+  auto kern = stb64_kernel<TC, NCH>;
+  BB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<(L.nchains + NCH - 1) / NCH, S64_T * NCH, smem, st>>>(L);
+  check_launch();
+}
+
 }  // namespace
 
 int launch_stb_small(const StbLaunch& L, cudaStream_t st) {
   if (L.m.P <= 64) {
-    const size_t smem = stb64_smem_bytes();
-    BB_CUDA_CHECK(cudaFuncSetAttribute(stb64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    stb64_kernel<<<L.nchains, S64_T, smem, st>>>(L);
-    check_launch();
+    static const bool scalar_path = std::getenv("BB_STB64_SCALAR") != nullptr;   // development: the pre-DMMA Cholesky
+    static const int nch_env = std::getenv("BB_STB64_NCH") ? std::atoi(std::getenv("BB_STB64_NCH")) : 0;
+    const int nch = nch_env > 0 ? nch_env : (L.nchains >= 4 * 148 / 2 ? 4 : L.nchains >= 148 ? 2 : 1);
+    if (scalar_path) launch64<false, 4>(L, st);
+    else if (nch >= 4) launch64<true, 4>(L, st);
+    else if (nch >= 2) launch64<true, 2>(L, st);
+    else launch64<true, 1>(L, st);
   } else launch_tb<8>(L, st);
   return 1;
 }

@@ -154,7 +154,7 @@ __global__ void __launch_bounds__(STB_THREADS, (TB == 4 ? 4 : 1)) stb_small_kern
     const double tau = sc_s[0], sig2 = sc_s[1];
 
     // ---- lambda_j = 2 * retstable(beta_j^2 / tau^2, alpha/2): retry queue + speculative look-ahead ----
-    if (do_lambda) lambda_stage_cta<STB_THREADS>(P, beta_s, lam_s, tau, 0.5 * alpha, L.key, gch, t, rc_s, q_s, PP, qn_s, kk_s, status);
+    if (do_lambda) lambda_stage_cta<STB_THREADS>(tid, P, beta_s, lam_s, tau, 0.5 * alpha, L.key, gch, t, rc_s, q_s, PP, qn_s, kk_s, status);
 
     if (do_beta) {
     // ---- A = X'X + diag(lambda sig2 / tau^2)   (BridgeRegression.cpp:554-556) ----

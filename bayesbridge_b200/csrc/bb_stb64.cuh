@@ -28,18 +28,64 @@ namespace bb {
 
 constexpr int S64_T = 128;     // threads per CTA
 constexpr int S64_P = 64;      // padded dimension
-constexpr int S64_LD = 65;     // row stride of the system in shared memory
+constexpr int S64_LD = 68;     // row stride of the system in shared memory (68 = 4 mod 16: DMMA fragment loads are 2-way at worst)
+constexpr int S64_PB = 12;     // row stride of a published 8 x 8 tile / inverse diagonal block
 
-__host__ __device__ inline size_t stb64_smem_bytes() {
-  return (size_t)(S64_P * S64_LD + 7 * S64_P + 32) * sizeof(double) + (size_t)(3 * S64_P + 4) * sizeof(int) + (size_t)S64_P * sizeof(RetConst);
+__host__ __device__ inline size_t stb64_smem_bytes() {   // per chain; a multiple of 16
+  return 15 + (size_t)(S64_P * S64_LD + 7 * S64_P + 2 * 8 * 8 * S64_PB + 32) * sizeof(double) + (size_t)(3 * S64_P + 4) * sizeof(int) + (size_t)S64_P * sizeof(RetConst) & ~(size_t)15;
 }
 
-__global__ void __launch_bounds__(S64_T, 4) stb64_kernel(const StbLaunch L) {
-  extern __shared__ double smem[];
+
+// Cholesky factor and inverse factor of one 8 x 8 diagonal block, in registers, every lane redundantly
+// (all indices static; no shuffles on the 8-pivot dependent chain).  W = L^-1 (lower) goes to Wout[8][S64_PB].
+__device__ __forceinline__ void chol8_inverse(const double* __restrict__ tile, double* __restrict__ Wout, uint32_t& status) {
+  double a[8][8], rs[8];
+#pragma unroll
+  for (int r = 0; r < 8; ++r)
+#pragma unroll
+    for (int c = 0; c <= r; ++c) a[r][c] = tile[r * S64_PB + c];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const double piv = a[k][k];
+    if (!(piv > 0.0)) status |= ST_CHOL_FAIL;
+    rs[k] = rsqrt(piv);
+#pragma unroll
+    for (int r = k + 1; r < 8; ++r) a[r][k] *= rs[k];
+#pragma unroll
+    for (int r = k + 1; r < 8; ++r)
+#pragma unroll
+      for (int c = k + 1; c <= r; ++c) a[r][c] = fma(-a[r][k], a[c][k], a[r][c]);
+  }
+  // W = L^-1 column by column: W(c,c) = 1/L(c,c), W(r,c) = -1/L(r,r) sum_{m=c}^{r-1} L(r,m) W(m,c)
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    double w[8];
+    w[c] = rs[c];
+#pragma unroll
+    for (int r = c + 1; r < 8; ++r) {
+      double sum = 0.0;
+#pragma unroll
+      for (int m = c; m < r; ++m) sum = fma(a[r][m], w[m], sum);
+      w[r] = -rs[r] * sum;
+    }
+#pragma unroll
+    for (int r = c; r < 8; ++r) Wout[r * S64_PB + c] = w[r];
+  }
+}
+
+// NCH chains share one CTA (128 threads each).  All barriers are CTA-wide, so the chains of an SM walk
+// through the kernel's phases together and the instruction cache holds ONE phase at a time; with four
+// independent CTAs per SM the same code ran at four different places and `stall_no_instruction` was the
+// largest stall reason after the barriers (profiles/r1_c2_*.md).
+template <bool TC, int NCH>
+__global__ void __launch_bounds__(S64_T * NCH, 4 / NCH) stb64_kernel(const StbLaunch L) {
+  extern __shared__ double smem_all[];
   const int P = L.m.P;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int cslot = threadIdx.x / S64_T;
+  double* smem = smem_all + (size_t)cslot * (stb64_smem_bytes() / sizeof(double));
+  const int tid = threadIdx.x - cslot * S64_T, lane = tid & 31, warp = tid >> 5;
   constexpr int NW = S64_T / 32;
-  constexpr int PP = S64_P, LD = S64_LD;
+  constexpr int PP = S64_P, LD = TC ? S64_LD : 65;   // the scalar path reads columns: stride 65 is conflict-free there
 
   double* S = smem;                        // [PP][LD]  lower triangle: unscaled columns of the factor
   double* beta_s = S + PP * LD;            // [PP]
@@ -49,15 +95,17 @@ __global__ void __launch_bounds__(S64_T, 4) stb64_kernel(const StbLaunch L) {
   double* rs_s = rhs_s + PP;               // [PP]   1 / sqrt(pivot_k) = 1 / L(k,k)
   double* ip_s = rs_s + PP;                // [PP]   1 / pivot_k
   double* rb_s = ip_s + PP;                // [PP]   forward-substitution residual r_k when row k becomes the pivot row
-  double* red_s = rb_s + PP;               // [3][8]
+  double* pb_s = rb_s + PP;                // [8][8][PB] published tiles of the current block column (TC path)
+  double* wi_s = pb_s + 8 * 8 * S64_PB;    // [8][8][PB] inverses of the diagonal blocks of the factor (TC path)
+  double* red_s = wi_s + 8 * 8 * S64_PB;   // [3][8]
   double* sc_s = red_s + 24;               // tau, sig2 (+ pad to 32)
   int* q_s = reinterpret_cast<int*>(red_s + 32);            // [2][PP] retry queues
   int* qn_s = q_s + 2 * PP;                                 // [2] counts
   uint32_t* kk_s = reinterpret_cast<uint32_t*>(qn_s + 2);   // [PP] next Philox block per coordinate
   RetConst* rc_s = reinterpret_cast<RetConst*>(kk_s + PP + 2);   // [PP]
 
-  const int ch = blockIdx.x;
-  if (ch >= L.nchains) return;
+  const bool valid = blockIdx.x * NCH + cslot < L.nchains;       // a padding slot repeats the last chain, stores nothing
+  const int ch = valid ? blockIdx.x * NCH + cslot : L.nchains - 1;
   const uint32_t gch = L.chain0 + (uint32_t)ch;
   const int t = tid & 63, h = tid >> 6;    // row, column parity
 
@@ -72,6 +120,7 @@ __global__ void __launch_bounds__(S64_T, 4) stb64_kernel(const StbLaunch L) {
     lam_s[j] = j < P ? L.lambda[(size_t)ch * P + j] : 1.0;
   }
   if (tid == 0) { sc_s[0] = know_tau ? L.h.true_tau : L.tau[ch]; sc_s[1] = know_sig2 ? L.h.true_sig2 : L.sig2[ch]; qn_s[0] = 0; qn_s[1] = 0; }
+  for (int e = tid; e < 8 * 8 * S64_PB; e += S64_T) wi_s[e] = 0.0;   // the upper triangles stay zero
   __syncthreads();
 
   for (int it = -L.pre_tau; it < L.niter; ++it) {
@@ -119,10 +168,10 @@ __global__ void __launch_bounds__(S64_T, 4) stb64_kernel(const StbLaunch L) {
     const double tau = sc_s[0], sig2 = sc_s[1];
 
     // ---- lambda_j = 2 * retstable(beta_j^2 / tau^2, alpha/2): retry queue + speculative look-ahead ----
-    if (do_lambda) lambda_stage_cta<S64_T>(P, beta_s, lam_s, tau, 0.5 * alpha, L.key, gch, tt, rc_s, q_s, PP, qn_s, kk_s, status);
+    if (do_lambda) lambda_stage_cta<S64_T>(tid, P, beta_s, lam_s, tau, 0.5 * alpha, L.key, gch, tt, rc_s, q_s, PP, qn_s, kk_s, status);
     else __syncthreads();
 
-    if (do_beta) {
+    if (do_beta && !TC) {
       // ---- S = X'X + diag(lambda sig2 / tau^2)   (BridgeRegression.cpp:554-556), lower triangle ----
       const double f = sig2 / (tau * tau);
       for (int j = h; j <= t; j += 2) {
@@ -183,10 +232,122 @@ __global__ void __launch_bounds__(S64_T, 4) stb64_kernel(const StbLaunch L) {
         }
       }
       __syncthreads();
-    }  // do_beta
+    }  // do_beta, scalar path
+
+    if (do_beta && TC) {
+      // ================= blocked Cholesky on the FP64 tensor cores (DMMA m8n8k4) =================
+      // The 36 lower 8 x 8 tiles of  X'X + diag(lambda sig2 / tau^2)  (BridgeRegression.cpp:554-556) live in
+      // registers as DMMA accumulator fragments: tile n = i(i+1)/2 + j belongs to warp n & 3, slot n >> 2.
+      // Block column s:  publish tiles (i,s) -> warp 0 factors the diagonal block and inverts its factor
+      // (registers, static indices) -> panel L(i,s) = T(i,s) W_s' by DMMA -> trailing T(i,j) -= L(i,s) L(j,s)'
+      // by DMMA.  3 barriers per block column, 24 in all (the scalar path needs 64).
+      const double f = sig2 / (tau * tau);
+      const int fr = lane >> 2, fc = 2 * (lane & 3);      // accumulator fragment: row fr, columns fc, fc+1
+      const int ar = lane >> 2, ak = lane & 3;            // A/B fragment: row ar, k = ak
+      double c0[9], c1[9];
+      int ti[9], tj[9];
+#pragma unroll
+      for (int sl = 0; sl < 9; ++sl) {
+        const int n = sl * 4 + warp;
+        int i = 0;
+        while ((i + 1) * (i + 2) / 2 <= n) ++i;
+        ti[sl] = i; tj[sl] = n - i * (i + 1) / 2;
+        const int row = 8 * i + fr, col = 8 * tj[sl] + fc;
+        double v0 = (row < P && col < P) ? __ldg(L.m.XX + row + (size_t)col * P) : (row == col ? 1.0 : 0.0);
+        double v1 = (row < P && col + 1 < P) ? __ldg(L.m.XX + row + (size_t)(col + 1) * P) : (row == col + 1 ? 1.0 : 0.0);
+        if (row == col && row < P) v0 += lam_s[row] * f;
+        if (row == col + 1 && row < P) v1 += lam_s[row] * f;
+        c0[sl] = v0; c1[sl] = v1;
+      }
+      // normals for the noise term (BridgeRegression.cpp:567-568), one item per coordinate
+      double eps = 0.0;
+      if (tid < P) { Stream s(L.key, gch, tt, ST_BETA_STB, (uint32_t)tid); eps = s.norm(0); }
+      if (tid < PP) rhs_s[tid] = tid < P ? __ldg(L.m.Xy + tid) : 0.0;
+
+      for (int s = 0; s < 8; ++s) {
+        // (1) publish the tiles of block column s
+#pragma unroll
+        for (int sl = 0; sl < 9; ++sl)
+          if (tj[sl] == s) *reinterpret_cast<double2*>(pb_s + (ti[sl] * 8 + fr) * S64_PB + fc) = make_double2(c0[sl], c1[sl]);
+        __syncthreads();
+        // (2) diagonal block: factor and inverse factor (warp 0)
+        if (warp == 0) chol8_inverse(pb_s + s * 8 * S64_PB, wi_s + s * 8 * S64_PB, status);
+        __syncthreads();
+        // (3) panel: L(i,s) = T(i,s) W_s'  for i > s, tile i by warp i & 3
+        for (int i = s + 1 + ((warp - (s + 1)) & 3); i < 8; i += 4) {
+          double d0 = 0.0, d1 = 0.0;
+#pragma unroll
+          for (int k0 = 0; k0 < 8; k0 += 4)
+            dmma_m8n8k4(d0, d1, pb_s[(i * 8 + ar) * S64_PB + k0 + ak], wi_s[(s * 8 + ar) * S64_PB + k0 + ak]);
+          *reinterpret_cast<double2*>(S + (8 * i + fr) * LD + 8 * s + fc) = make_double2(d0, d1);
+        }
+        __syncthreads();
+        // (4) trailing update of my tiles (i,j), i >= j > s
+#pragma unroll
+        for (int sl = 0; sl < 9; ++sl)
+          if (tj[sl] > s) {
+#pragma unroll
+            for (int k0 = 0; k0 < 8; k0 += 4)
+              dmma_m8n8k4(c0[sl], c1[sl], -S[(8 * ti[sl] + ar) * LD + 8 * s + k0 + ak], S[(8 * tj[sl] + ar) * LD + 8 * s + k0 + ak]);
+          }
+      }
+      __syncthreads();
+      // ---- w = L^-1 Xy (the reference's first trsm, :564), blocked with the inverse diagonal blocks ----
+      const double sig = sqrt(sig2);
+      if (warp == 0) {
+        for (int s = 0; s < 8; ++s) {
+          if (lane < 8) {
+            double w = 0.0;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) w = fma(wi_s[(s * 8 + lane) * S64_PB + c], rhs_s[8 * s + c], w);   // W is lower: zeros above
+            rb_s[8 * s + lane] = w;
+          }
+          __syncwarp();
+#pragma unroll
+          for (int q = 0; q < 2; ++q) {
+            const int row = lane + 32 * q;
+            if (row >= 8 * (s + 1)) {
+              double r = rhs_s[row];
+#pragma unroll
+              for (int c = 0; c < 8; ++c) r = fma(-S[row * LD + 8 * s + c], rb_s[8 * s + c], r);
+              rhs_s[row] = r;
+            }
+          }
+          __syncwarp();
+        }
+        // rhs = w + sig eps;  then  L' x = rhs  backwards (:565, :570-574)
+        rhs_s[lane] = lane < P ? fma(sig, eps, rb_s[lane]) : 0.0;
+      }
+      __syncthreads();
+      if (warp == 1) rhs_s[32 + lane] = (32 + lane) < P ? fma(sig, eps, rb_s[32 + lane]) : 0.0;
+      __syncthreads();
+      if (warp == 0) {
+        for (int s = 7; s >= 0; --s) {
+          if (lane < 8) {
+            double x = 0.0;
+#pragma unroll
+            for (int r = 0; r < 8; ++r) x = fma(wi_s[(s * 8 + r) * S64_PB + lane], rhs_s[8 * s + r], x);   // W' y
+            beta_s[8 * s + lane] = x;
+          }
+          __syncwarp();
+#pragma unroll
+          for (int q = 0; q < 2; ++q) {
+            const int col = lane + 32 * q;
+            if (col < 8 * s) {
+              double y = rhs_s[col];
+#pragma unroll
+              for (int r = 0; r < 8; ++r) y = fma(-S[(8 * s + r) * LD + col], beta_s[8 * s + r], y);
+              rhs_s[col] = y;
+            }
+          }
+          __syncwarp();
+        }
+      }
+      __syncthreads();
+    }  // do_beta, tensor-core path
 
     // ---- store ----
-    const bool store = L.sink.thin > 0 && ((it + 1) % L.sink.thin) == 0;
+    const bool store = valid && L.sink.thin > 0 && ((it + 1) % L.sink.thin) == 0;
     if (store) {
       const long long slot = L.sink.s0 + (it + 1) / L.sink.thin - 1;
       for (int j = tid; j < P; j += S64_T) {
@@ -205,6 +366,7 @@ __global__ void __launch_bounds__(S64_T, 4) stb64_kernel(const StbLaunch L) {
   }
 
   __syncthreads();
+  if (!valid) return;
   for (int j = tid; j < P; j += S64_T) {
     L.beta[(size_t)ch * P + j] = beta_s[j];
     L.lambda[(size_t)ch * P + j] = lam_s[j];

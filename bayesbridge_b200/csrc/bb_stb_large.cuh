@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(SL_T) stbl_scalar_kernel(const StbLargeLaunch 
   const double tau = sc[0];
   if (tid == 0) { L.tau[ch] = sc[0]; L.sig2[ch] = sc[1]; L.alpha[ch] = alpha; }
   double* lam = L.lambda + (size_t)ch * P;
-  if (do_lambda) lambda_stage_cta<SL_T>(P, beta, lam, tau, 0.5 * alpha, L.key, gch, t, nullptr, q_s, P, qn_s, kk_s, status);
+  if (do_lambda) lambda_stage_cta<SL_T>(tid, P, beta, lam, tau, 0.5 * alpha, L.key, gch, t, nullptr, q_s, P, qn_s, kk_s, status);
   status = __reduce_or_sync(0xffffffffu, status);
   if (lane == 0 && status) atomicOr(L.status + ch, status);
 }

@@ -103,3 +103,10 @@ def max_over_ranks(x, device=None):
 def barrier():
     if dist.is_initialized() and dist.get_world_size() > 1:
         dist.barrier()
+
+
+def shutdown():
+    """tear the process group down (no-op for a single process)"""
+    import torch.distributed as td
+    if td.is_available() and td.is_initialized():
+        td.destroy_process_group()

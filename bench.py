@@ -325,6 +325,7 @@ def run_ours(args):
             line["cpu_baseline"] = cpu_baseline(method, X, y, alpha, args.cpu_seconds)
         print(json.dumps(line), flush=True)
     bdist.barrier()
+    bdist.shutdown()
 
 
 def kernel_name(method, P):
