@@ -1,0 +1,155 @@
+"""-m gpu: the CUDA sampler at BASELINE.json's FULL sizes.
+
+Same-stream parity against the C port where the oracle finishes in seconds (one or two chains of the
+c3 / c4 shapes, conditional by conditional), plus size-independent properties of whole runs:
+  * draws do not depend on batching (a chain computed alone == the same global chain inside a batch),
+  * the box constraint |beta_j| <= b_j of the triangle sampler holds for every stored draw,
+  * V z == beta after many incremental sweeps (the z / beta book-keeping does not drift),
+  * posterior means of the two samplers agree (the reference's own acceptance test, Code/R/Trial.R:1).
+"""
+import numpy as np
+import pytest
+
+from helpers import rel_err, teacher_forced_sweep_error
+
+pytestmark = pytest.mark.gpu
+
+SEED = 0xBADC0FFEE
+
+
+def test_c3_shape_tri_conditionals(port):
+    """n=10000, p=1000 (config c3): device factors (Jacobi SVD on the GPU) feed the oracle, then every
+    conditional of one iteration is compared for two chains; the sweep is checked draw by draw."""
+    import bayesbridge_b200 as bb
+    from bayesbridge_b200 import synth
+    from bayesbridge_b200._lib import ST_BETA, ST_OMEGA, ST_SIG2, ST_TAU, ST_U
+    X, y, _ = synth.make("c3")
+    N, P = X.shape
+    model = bb.Model(X, y)
+    f = model.factors()
+    sv = np.linalg.svd(X, compute_uv=False)
+    assert rel_err(f["d"], sv) < 1e-10
+    pm = port.model(X, y, (f["tV"], f["d"], f["a"], f["bhat"]))
+    nch, alpha, it = 2, 0.5, 7
+    rng = np.random.default_rng(3)
+    beta0 = f["bhat"][None, :] * (1 + 0.05 * rng.standard_normal((nch, P))) + 0.01 * rng.standard_normal((nch, P))
+    u0 = rng.uniform(0.05, 0.9, (nch, P))
+    ch = model.chains("triangle", nch, seed=SEED, chain0=11)
+    hyp = bb.make_hyper(alpha=alpha)
+    ch.set(beta=beta0, u=u0)
+    ch.run(hyp, 1, it, ST_TAU); tau = ch.get()["tau"]
+    ch.run(hyp, 1, it, ST_SIG2); sig2 = ch.get()["sig2"]
+    ch.run(hyp, 1, it, ST_OMEGA); st = ch.get(); om, sh = st["aux"], st["shape"]
+    ch.run(hyp, 1, it, ST_U); u1 = ch.get()["u"]
+    ch.run(hyp, 1, it, ST_BETA); b1 = ch.get()["beta"]
+    for c in range(nch):
+        assert rel_err(tau[c], pm.sample_tau_marg(beta0[c], alpha, 2.0, 2.0, SEED, 11 + c, it)) < 1e-10
+        assert rel_err(sig2[c], pm.sample_sig2(beta0[c], 0.0, 0.0, SEED, 11 + c, it)) < 1e-8
+        o, s = pm.sample_omega(beta0[c], u0[c], tau[c], alpha, SEED, 11 + c, it)
+        assert rel_err(om[c], o) < 1e-10 and np.array_equal(sh[c], s)
+        assert np.abs(u1[c] - pm.sample_u(beta0[c], om[c], tau[c], alpha, SEED, 11 + c, it)).max() < 1e-10
+        bbox = (1.0 - u1[c]) * np.exp(np.log(om[c]) / alpha) * tau[c]
+        assert teacher_forced_sweep_error(f, beta0[c], bbox, sig2[c], SEED, 11 + c, it, b1[c]) < 1e-10
+    assert not ch.get()["status"].any()
+
+
+def test_c4_shape_stb_conditionals(port):
+    """n=500, p=2000, alpha=0.25 (config c4, p > n): tau, sig2, lambda and the 2000 x 2000 Cholesky draw of
+    beta (blocked DMMA factorisation in HBM) against the oracle for one chain."""
+    import bayesbridge_b200 as bb
+    from bayesbridge_b200 import synth
+    from bayesbridge_b200._lib import ST_BETA, ST_LAMBDA, ST_SIG2, ST_TAU
+    X, y, _ = synth.make("c4")
+    N, P = X.shape
+    model = bb.Model(X, y)
+    f = model.factors()
+    assert not np.abs(f["bhat"]).any()          # singular X'X: least squares start is 0 (BridgeRegression.cpp:79-91)
+    pm = port.model(X, y, (f["tV"], f["d"], f["a"], f["bhat"]))
+    alpha, it = 0.25, 4
+    rng = np.random.default_rng(4)
+    beta0 = 0.05 * rng.standard_normal((1, P))
+    ch = model.chains("stable", 1, seed=SEED, chain0=5)
+    hyp = bb.make_hyper(alpha=alpha)
+    ch.set(beta=beta0)
+    ch.run(hyp, 1, it, ST_TAU); tau = ch.get()["tau"]
+    ch.run(hyp, 1, it, ST_SIG2); sig2 = ch.get()["sig2"]
+    ch.run(hyp, 1, it, ST_LAMBDA); lam = ch.get()["aux"]
+    ch.run(hyp, 1, it, ST_BETA); st = ch.get()
+    assert not st["status"].any()
+    assert rel_err(tau[0], pm.sample_tau_marg(beta0[0], alpha, 2.0, 2.0, SEED, 5, it)) < 1e-10
+    assert rel_err(sig2[0], pm.sample_sig2(beta0[0], 0.0, 0.0, SEED, 5, it)) < 1e-8
+    want = pm.sample_lambda(beta0[0], alpha, tau[0], SEED, 5, it)
+    assert np.abs(lam[0] / want - 1).max() < 1e-9
+    assert rel_err(st["beta"][0], pm.sample_beta_stable(lam[0], sig2[0], tau[0], SEED, 5, it)) < 1e-7
+
+
+@pytest.mark.parametrize("method,cfg", [("stable", "c2"), ("triangle", "c1")])
+def test_batching_invariance_full_chain_count(method, cfg):
+    """512 chains in one launch (the bench's c2 batch) reproduce, bit for bit, chains run on their own."""
+    import bayesbridge_b200 as bb
+    from bayesbridge_b200 import synth
+    from bayesbridge_b200._lib import ST_ALL
+    X, y, _ = synth.make(cfg)
+    model = bb.Model(X, y)
+    hyp = bb.make_hyper(alpha=0.5)
+    big = model.chains(method, 512, seed=SEED, chain0=0)
+    big.run(hyp, 30, 0, ST_ALL, pre_tau=1)
+    B = big.get()
+    for g in (0, 3, 257, 511):
+        one = model.chains(method, 1, seed=SEED, chain0=g)
+        one.run(hyp, 30, 0, ST_ALL, pre_tau=1)
+        O = one.get()
+        assert np.array_equal(O["beta"][0], B["beta"][g])
+        assert O["tau"][0] == B["tau"][g] and O["sig2"][0] == B["sig2"][g]
+
+
+def test_tri_invariants_after_many_sweeps():
+    """p=256 (c5 shape, fewer rows): after 300 iterations every stored draw respects |beta_j| <= b_j and the
+    incrementally updated z = V' beta has not drifted from beta (next sweep reproduced from beta alone)."""
+    import bayesbridge_b200 as bb
+    from bayesbridge_b200 import synth
+    from bayesbridge_b200._lib import ST_ALL, ST_BETA
+    X, y, _ = synth.gaussian_design(3000, 256, 30, 0.3, 0.8, synth.BASE_SEED + 5)
+    model = bb.Model(X, y)
+    f = model.factors()
+    hyp = bb.make_hyper(alpha=0.5)
+    nch = 8
+    ch = model.chains("triangle", nch, seed=SEED)
+    ch.reserve(300, ("beta", "u", "omega", "tau"))
+    ch.run(hyp, 300, 0, ST_ALL, pre_tau=1, thin=1, slot0=0)
+    st = ch.get()
+    assert not st["status"].any()
+    beta, u, om, tau = (ch.fetch(k) for k in ("beta", "u", "omega", "tau"))
+    b = (1.0 - u) * om ** 2.0 * tau[:, :, None]                  # b_j = (1-u_j) omega_j^(1/alpha) tau, alpha = 0.5
+    assert (np.abs(beta) <= b * (1 + 1e-9)).all()
+    # one more sweep from the device state, checked draw by draw from z = V' beta recomputed on the host: a
+    # device z that had drifted away from V' beta over 300 incremental updates would show up here
+    beta0, u0, om0 = st["beta"], st["u"], st["aux"]
+    ch.run(hyp, 1, 300, ST_BETA)
+    b1 = ch.get()["beta"]
+    for c in range(nch):
+        bbox = (1.0 - u0[c]) * om0[c] ** 2.0 * st["tau"][c]
+        assert teacher_forced_sweep_error(f, beta0[c], bbox, st["sig2"][c], SEED, c, 300, b1[c]) < 1e-8
+
+
+def test_tri_vs_stb_posterior_means_agree():
+    """the reference's own acceptance criterion (Code/R/Trial.R:1,98-99): both samplers target the same
+    posterior; means of beta over 256 chains x 400 draws agree within 5 Monte-Carlo standard errors."""
+    import bayesbridge_b200 as bb
+    from bayesbridge_b200 import synth
+    from bayesbridge_b200._lib import ST_ALL
+    X, y, _ = synth.make("c2")
+    model = bb.Model(X, y)
+    hyp = bb.make_hyper(alpha=0.5)
+    means, ses = [], []
+    for method in ("triangle", "stable"):
+        burn = 3000 if method == "triangle" else 300
+        ch = model.chains(method, 256, seed=SEED + 1)
+        ch.run(hyp, burn, 0, ST_ALL, pre_tau=1)
+        ch.reserve(400, ("beta",))
+        ch.run(hyp, 400 * 5, burn, ST_ALL, thin=5, slot0=0)
+        d = ch.fetch("beta")                                       # [chain, slot, P]
+        cm = d.mean(axis=1)                                        # per-chain means: independent replicates
+        means.append(cm.mean(axis=0)); ses.append(cm.std(axis=0, ddof=1) / np.sqrt(cm.shape[0]))
+    zscore = np.abs(means[0] - means[1]) / np.sqrt(ses[0] ** 2 + ses[1] ** 2)
+    assert zscore.max() < 5.0, zscore.max()
