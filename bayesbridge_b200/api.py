@@ -237,9 +237,11 @@ class Chains:
         if rc:
             raise RuntimeError(_lib.last_error())
 
-    def set(self, beta=None, u=None, aux=None, sig2=None, tau=None):
+    def set(self, beta=None, u=None, aux=None, sig2=None, tau=None, alpha=None):
         arrs = [None if a is None else _f(a) for a in (beta, u, aux, sig2, tau)]
         self._ck(self.L.bb_chains_set(self.h, *[_p(a) for a in arrs]))
+        if alpha is not None:
+            self._ck(self.L.bb_chains_alpha(self.h, _p(_f(np.broadcast_to(alpha, (self.nchains,)))), None))
 
     def get(self):
         n, P = self.nchains, self.P
@@ -247,7 +249,9 @@ class Chains:
         sig2, tau = np.zeros(n), np.zeros(n)
         status = np.zeros(n, dtype=np.uint32)
         self._ck(self.L.bb_chains_get(self.h, _p(beta), _p(u), _p(aux), _p(shape), _p(sig2), _p(tau), status.ctypes.data_as(up)))
-        return dict(beta=beta, u=u, aux=aux, shape=shape, sig2=sig2, tau=tau, status=status)
+        alpha = np.zeros(n)
+        self._ck(self.L.bb_chains_alpha(self.h, None, _p(alpha)))
+        return dict(beta=beta, u=u, aux=aux, shape=shape, sig2=sig2, tau=tau, alpha=alpha, status=status)
 
     def reserve(self, nslots, outputs=("beta",)):
         mask = 0

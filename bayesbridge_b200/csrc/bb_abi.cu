@@ -242,7 +242,6 @@ void chains_run(bb_chains* c, const bb_hyper* hh, unsigned iter0, int niter, int
                 int thin, long long slot0, double* kernel_ms) {
   const bb_model* m = c->m;
   BB_CUDA_CHECK(cudaSetDevice(m->device));
-  if (!(hh->true_alpha > 0)) throw std::string("alpha must be fixed (> 0); the alpha Metropolis step is not on the device path yet");
   const bb::Hyper h = to_hyper(hh);
   const bb::RngKey key{(uint32_t)c->seed, (uint32_t)(c->seed >> 32)};
   cudaStream_t st = c->stream;
@@ -476,6 +475,15 @@ int bb_chains_get(const bb_chains* c, double* beta, double* u, double* aux, doub
   });
 }
 
+int bb_chains_alpha(bb_chains* c, const double* set, double* get) {
+  return guarded([&] {
+    BB_CUDA_CHECK(cudaSetDevice(c->m->device));
+    const size_t ns = (size_t)c->nchains * sizeof(double);
+    if (set) BB_CUDA_CHECK(cudaMemcpy(c->alpha, set, ns, cudaMemcpyHostToDevice));
+    if (get) BB_CUDA_CHECK(cudaMemcpy(get, c->alpha, ns, cudaMemcpyDeviceToHost));
+  });
+}
+
 int bb_chains_reserve(bb_chains* c, long long nslots, int out_mask) {
   return guarded([&] {
     BB_CUDA_CHECK(cudaSetDevice(c->m->device));
@@ -571,7 +579,8 @@ void run_driver(int method, int ortho, const double* X, const double* y, int N, 
   if (bb_chains_reserve(g.c, nsamp, mask)) throw std::string(g_err);
   lap("chains + draw buffer");
   if (g_verbose) {
-    std::printf("Bridge Regression (%s): known alpha=%g", method == BB_TRI ? "mix. of triangles" : "mix. of normals", h->true_alpha);
+    std::printf("Bridge Regression (%s):", method == BB_TRI ? "mix. of triangles" : "mix. of normals");
+    if (h->true_alpha > 0) std::printf(" known alpha=%g", h->true_alpha);
     if (h->true_sig2 > 0) std::printf(", sig2=%g", h->true_sig2);
     if (h->true_tau > 0) std::printf(", tau=%g", h->true_tau);
     std::printf("\nBurn-in: %i, Num. Samples: %i, Chains: %i\n", burn, nsamp, nchains);
@@ -588,9 +597,13 @@ void run_driver(int method, int ortho, const double* X, const double* y, int N, 
   const long long total = (long long)(nsamp - 1) * thin;
   long long done = 0;
   const long long chunk = 8192LL * thin;
+  // the sampling loop of the non-orthogonal stable driver hands (alpha_b, alpha_b) to the alpha step
+  // (BridgeWrapper.cpp:294; its burn-in :272 and the other three drivers pass (alpha_a, alpha_b)): kept as written
+  bb_hyper hs = *h;
+  if (method != BB_TRI && !ortho) hs.alpha_a = hs.alpha_b;
   while (done < total) {
     const long long n = std::min(chunk, total - done);
-    chains_run(g.c, h, (unsigned)(nburn + done), (int)n, BB_ST_ALL, 0, 0, thin, 1 + done / thin, nullptr);
+    chains_run(g.c, &hs, (unsigned)(nburn + done), (int)n, BB_ST_ALL, 0, 0, thin, 1 + done / thin, nullptr);
     done += n;
   }
   const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();

@@ -12,6 +12,7 @@
 #pragma once
 #include "bb_launch.h"
 #include "bb_retstable.cuh"
+#include "bb_alpha.cuh"
 
 namespace bb {
 
@@ -47,9 +48,9 @@ __global__ void __launch_bounds__(ORT_T) ortho_kernel(const OrthoLaunch L) {
   const int ch = blockIdx.x;
   if (ch >= L.nchains) return;
   const uint32_t gch = L.chain0 + (uint32_t)ch;
-  const double alpha = L.h.true_alpha;
-  const bool know_tau = L.h.true_tau > 0, know_sig2 = L.h.true_sig2 > 0;
-  const bool do_tau = (L.stages & 1) && !know_tau, do_sig2 = (L.stages & 2) && !know_sig2;
+  const bool know_tau = L.h.true_tau > 0, know_sig2 = L.h.true_sig2 > 0, know_alpha = L.h.true_alpha > 0;
+  const bool do_tau = (L.stages & 1) && !know_tau, do_sig2 = (L.stages & 2) && !know_sig2, do_alpha = (L.stages & 64) && !know_alpha;
+  double alpha = know_alpha ? L.h.true_alpha : L.alpha[ch];   // unknown alpha: chain state, moved by the Metropolis step below
   const bool do_omega = L.stages & 4, do_u = L.stages & 8, do_beta = L.stages & 16, do_lambda = L.stages & 32;
   uint32_t status = 0;
 
@@ -177,6 +178,18 @@ __global__ void __launch_bounds__(ORT_T) ortho_kernel(const OrthoLaunch L) {
         }
         __syncthreads();
       }
+    }
+    if (do_alpha) {   // BridgeRegression.cpp:477-503 (BridgeWrapper.cpp:390,412,498)
+      if (warp == 0) {
+        Stream sa(L.key, gch, t, ST_ALPHA, 0);
+        const AlphaProposal pr = alpha_propose(sa, alpha);
+        double sn = 0.0, so = 0.0;
+        for (int j = lane; j < P; j += 32) alpha_terms(beta_s[j], tau, pr, sn, so);
+        sn = warp_sum(sn); so = warp_sum(so);
+        if (lane == 0) sc[3] = alpha_decide(sa, pr, sn, so, P, L.h.alpha_a, L.h.alpha_b);
+      }
+      __syncthreads();
+      alpha = sc[3];
     }
     if (store) {
       for (int j = tid; j < P; j += ORT_T) {

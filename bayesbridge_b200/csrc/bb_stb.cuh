@@ -18,6 +18,7 @@
 #pragma once
 #include "bb_launch.h"
 #include "bb_retstable.cuh"
+#include "bb_alpha.cuh"
 
 namespace bb {
 
@@ -62,10 +63,10 @@ __global__ void __launch_bounds__(STB_THREADS, (TB == 4 ? 4 : 1)) stb_small_kern
   const bool tile_on = tid < STB_TILES + STB_NB;
   const bool xy_row = tile_on && ti == STB_NB;
 
-  const double alpha = L.h.true_alpha;
-  const bool know_tau = L.h.true_tau > 0, know_sig2 = L.h.true_sig2 > 0;
+  const bool know_tau = L.h.true_tau > 0, know_sig2 = L.h.true_sig2 > 0, know_alpha = L.h.true_alpha > 0;
   const bool do_tau = (L.stages & 1) && !know_tau, do_sig2 = (L.stages & 2) && !know_sig2;
-  const bool do_lambda = L.stages & 32, do_beta = L.stages & 16;
+  const bool do_lambda = L.stages & 32, do_beta = L.stages & 16, do_alpha = (L.stages & 64) && !know_alpha;
+  double alpha = know_alpha ? L.h.true_alpha : L.alpha[ch];   // unknown alpha: chain state, moved by the Metropolis step below
   uint32_t status = 0;
 
   for (int j = tid; j < PP; j += STB_THREADS) {
@@ -239,6 +240,21 @@ __global__ void __launch_bounds__(STB_THREADS, (TB == 4 ? 4 : 1)) stb_small_kern
     __syncthreads();
 
     }  // do_beta
+
+    // ---- alpha (only when it is unknown): BridgeRegression.cpp:477-503 ----
+    if (do_alpha) {
+      if (warp == 0) {
+        Stream sa(L.key, gch, t, ST_ALPHA, 0);
+        const AlphaProposal pr = alpha_propose(sa, alpha);
+        double sn = 0.0, so = 0.0;
+        for (int j = lane; j < P; j += 32) alpha_terms(beta_s[j], tau, pr, sn, so);
+        sn = warp_sum(sn); so = warp_sum(so);
+        if (lane == 0) red_s[0] = alpha_decide(sa, pr, sn, so, P, L.h.alpha_a, L.h.alpha_b);
+      }
+      __syncthreads();
+      alpha = red_s[0];
+      __syncthreads();
+    }
 
     // ---- store ----
     const bool store = L.sink.thin > 0 && ((it + 1) % L.sink.thin) == 0;

@@ -23,6 +23,7 @@
 #pragma once
 #include "bb_launch.h"
 #include "bb_retstable.cuh"
+#include "bb_alpha.cuh"
 
 namespace bb {
 
@@ -109,10 +110,10 @@ __global__ void __launch_bounds__(S64_T * NCH, 4 / NCH) stb64_kernel(const StbLa
   const uint32_t gch = L.chain0 + (uint32_t)ch;
   const int t = tid & 63, h = tid >> 6;    // row, column parity
 
-  const double alpha = L.h.true_alpha;
-  const bool know_tau = L.h.true_tau > 0, know_sig2 = L.h.true_sig2 > 0;
+  const bool know_tau = L.h.true_tau > 0, know_sig2 = L.h.true_sig2 > 0, know_alpha = L.h.true_alpha > 0;
   const bool do_tau = (L.stages & 1) && !know_tau, do_sig2 = (L.stages & 2) && !know_sig2;
-  const bool do_lambda = L.stages & 32, do_beta = L.stages & 16;
+  const bool do_lambda = L.stages & 32, do_beta = L.stages & 16, do_alpha = (L.stages & 64) && !know_alpha;
+  double alpha = know_alpha ? L.h.true_alpha : L.alpha[ch];   // unknown alpha: chain state, moved by the Metropolis step below
   uint32_t status = 0;
 
   for (int j = tid; j < PP; j += S64_T) {
@@ -345,6 +346,20 @@ __global__ void __launch_bounds__(S64_T * NCH, 4 / NCH) stb64_kernel(const StbLa
       }
       __syncthreads();
     }  // do_beta, tensor-core path
+
+    // ---- alpha (only when it is unknown): BridgeRegression.cpp:477-503 ----
+    if (do_alpha) {
+      if (warp == 0) {
+        Stream sa(L.key, gch, tt, ST_ALPHA, 0);
+        const AlphaProposal pr = alpha_propose(sa, alpha);
+        double sn = 0.0, so = 0.0;
+        for (int j = lane; j < P; j += 32) alpha_terms(beta_s[j], tau, pr, sn, so);
+        sn = warp_sum(sn); so = warp_sum(so);
+        if (lane == 0) sc_s[2] = alpha_decide(sa, pr, sn, so, P, L.h.alpha_a, L.h.alpha_b);
+      }
+      __syncthreads();
+      alpha = sc_s[2];
+    }
 
     // ---- store ----
     const bool store = valid && L.sink.thin > 0 && ((it + 1) % L.sink.thin) == 0;

@@ -20,8 +20,12 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
   const size_t smem_sy = (size_t)2 * SL_NB * SL_LD * sizeof(double);
   const int nblk = (P + SL_NB - 1) / SL_NB;
   int n = 0;
+  const bool do_alpha = (L.stages & 64) && !(L.h.true_alpha > 0) && !L.pre;
   stbl_scalar_kernel<<<nch, SL_T, smem_sc, st>>>(L); ++n;
-  if (L.pre || !beta_stage) return n;
+  if (L.pre || !beta_stage) {
+    if (do_alpha) { stbl_alpha_kernel<<<(nch + 7) / 8, 256, 0, st>>>(L); ++n; }
+    return n;
+  }
   stbl_build_kernel<<<dim3(64, nch), 256, 0, st>>>(L); ++n;
   for (int kb = 0; kb < nblk; ++kb) {
     stbl_potrf_kernel<<<nch, SL_T, 0, st>>>(L.A, P, kb, L.status); ++n;
@@ -32,6 +36,7 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
     }
   }
   stbl_solve_kernel<<<nch, SL_T, smem_sv, st>>>(L); ++n;
+  if (do_alpha) { stbl_alpha_kernel<<<(nch + 7) / 8, 256, 0, st>>>(L); ++n; }
   return n;
 }
 

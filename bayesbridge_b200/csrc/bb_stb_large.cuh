@@ -9,6 +9,7 @@
 #pragma once
 #include "bb_launch.h"
 #include "bb_retstable.cuh"
+#include "bb_alpha.cuh"
 
 namespace bb {
 
@@ -28,7 +29,7 @@ __global__ void __launch_bounds__(SL_T) stbl_scalar_kernel(const StbLargeLaunch 
   uint32_t* kk_s = reinterpret_cast<uint32_t*>(qn_s + 2);
   const int ch = blockIdx.x; if (ch >= L.nchains) return;
   const uint32_t gch = L.chain0 + (uint32_t)ch, t = L.iter;
-  const double alpha = L.h.true_alpha;
+  const double alpha = L.h.true_alpha > 0 ? L.h.true_alpha : L.alpha[ch];   // unknown alpha: chain state (stbl_alpha_kernel moves it)
   const bool know_tau = L.h.true_tau > 0, know_sig2 = L.h.true_sig2 > 0;
   const bool do_tau = ((L.stages & 1) || L.pre) && !know_tau, do_sig2 = (L.stages & 2) && !know_sig2 && !L.pre;
   const bool do_lambda = (L.stages & 32) && !L.pre;
@@ -253,6 +254,25 @@ __global__ void __launch_bounds__(SL_T) stbl_solve_kernel(const StbLargeLaunch L
     if (L.sink.sig2) L.sink.sig2[o] = L.sig2[ch];
     if (L.sink.tau) L.sink.tau[o] = L.tau[ch];
     if (L.sink.alpha) L.sink.alpha[o] = L.alpha[ch];
+  }
+}
+
+// ---- alpha, only when it is unknown (BridgeRegression.cpp:477-503): one warp per chain, after the beta draw ----
+__global__ void __launch_bounds__(256) stbl_alpha_kernel(const StbLargeLaunch L) {
+  const int P = L.m.P, lane = threadIdx.x & 31;
+  const int ch = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (ch >= L.nchains) return;
+  const double* beta = L.beta + (size_t)ch * P;
+  const double tau = L.h.true_tau > 0 ? L.h.true_tau : L.tau[ch];
+  Stream sa(L.key, L.chain0 + (uint32_t)ch, L.iter, ST_ALPHA, 0);
+  const AlphaProposal pr = alpha_propose(sa, L.alpha[ch]);
+  double sn = 0.0, so = 0.0;
+  for (int j = lane; j < P; j += 32) alpha_terms(beta[j], tau, pr, sn, so);
+  sn = warp_sum(sn); so = warp_sum(so);
+  if (lane == 0) {
+    const double a = alpha_decide(sa, pr, sn, so, P, L.h.alpha_a, L.h.alpha_b);
+    L.alpha[ch] = a;
+    if (L.slot >= 0 && L.sink.alpha) L.sink.alpha[(size_t)ch * L.sink.chain_stride + L.slot] = a;
   }
 }
 

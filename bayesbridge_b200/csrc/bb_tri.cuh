@@ -31,6 +31,7 @@
 #include <cfloat>
 #include <math_constants.h>
 #include "bb_launch.h"
+#include "bb_alpha.cuh"
 
 namespace bb {
 
@@ -109,7 +110,7 @@ __device__ __forceinline__ double reduce_minima(const double (&lmn)[C], const do
 // shared-memory footprint of one CTA (bytes); mirrored by the host launcher
 __host__ __device__ inline size_t tri_smem_bytes(int P, int LD, int S, int NG, int W, int C) {
   const size_t CH = (size_t)NG * C;
-  return (size_t)S * (LD + 2) * 16 + 2 * CH * P * 8 + (size_t)(2 * NG * W * C * 2 + NG * C + NG * C * 2) * 8 + (size_t)2 * S * 8;
+  return (size_t)S * (LD + 2) * 16 + 2 * CH * P * 8 + (size_t)(2 * NG * W * C * 2 + NG * C + NG * C * 3) * 8 + (size_t)2 * S * 8;
 }
 
 // registers live per SM sub-partition (16384 each, warps dealt round-robin over the 4 of them)
@@ -135,11 +136,12 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
   double* red = u_s + (size_t)CH * P;                          // [2][NG][W][C][2]
   double* bc = red + 2 * NG * W * C * 2;                       // [NG][C]    delta of the current step
   double* sc = bc + NG * C;                                    // [NG][C][2] tau, sig2
-  uint64_t* full = reinterpret_cast<uint64_t*>(sc + NG * C * 2);    // [S]
+  double* al_s = sc + NG * C * 2;                              // [NG][C]    alpha of each chain
+  uint64_t* full = reinterpret_cast<uint64_t*>(al_s + NG * C);      // [S]
   uint64_t* empty = full + S;                                  // [S]
 
-  const double alpha = L.h.true_alpha;  // fixed alpha (unknown alpha is handled by the host driver per iteration)
-  const bool know_tau = L.h.true_tau > 0, know_sig2 = L.h.true_sig2 > 0;
+  const bool know_tau = L.h.true_tau > 0, know_sig2 = L.h.true_sig2 > 0, know_alpha = L.h.true_alpha > 0;
+  const bool do_alpha = (L.stages & 64) && !know_alpha;   // unknown alpha: chain state moved by a Metropolis step per iteration
   const bool do_tau = (L.stages & 1) && !know_tau, do_sig2 = (L.stages & 2) && !know_sig2;
   const bool do_omega = L.stages & 4, do_u = L.stages & 8, do_beta = L.stages & 16;
   const int nsweep = (L.h.betaburn > 0 ? L.h.betaburn : 0) + 1;
@@ -150,6 +152,10 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
   if (tid == 0) {
     for (int s = 0; s < S; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], (uint32_t)(NG * W)); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (w == 0 && lane < C) {
+    const int ch = blockIdx.x * CH + g * C + lane;
+    al_s[g * C + lane] = know_alpha ? L.h.true_alpha : L.alpha[ch < L.nchains ? ch : L.nchains - 1];
   }
   __syncthreads();
 
@@ -266,6 +272,7 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
       double st[C], sr[C];
 #pragma unroll
       for (int c = 0; c < C; ++c) {
+        const double alpha = al_s[g * C + c];
         double a = 0.0, r = 0.0;
 #pragma unroll
         for (int jj = 0; jj < J; ++jj)
@@ -290,6 +297,7 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
           double a = st[c], r = sr[c];
           if (W > 1) { a = 0.0; r = 0.0; for (int ww = 0; ww < W; ++ww) { a += redg0[(ww * C + c) * 2]; r += redg0[(ww * C + c) * 2 + 1]; } }
           const uint32_t gch = L.chain0 + (uint32_t)lch[c];
+          const double alpha = al_s[g * C + c];
           double tau = tau_c[c], sig2 = sig2_c[c];
           uint32_t stt = 0;
           if (do_tau || (pre && !know_tau)) {  // BridgeRegression.cpp:453-465
@@ -321,7 +329,7 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
 #pragma unroll
     for (int c = 0; c < C; ++c) {
       const uint32_t gch = L.chain0 + (uint32_t)lch[c];
-      const double tau = tau_c[c];
+      const double tau = tau_c[c], alpha = al_s[g * C + c];
 #pragma unroll
       for (int jj = 0; jj < J; ++jj) {
         const int j = jj * 32 * W + 32 * w + lane;
@@ -463,6 +471,27 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
       }
     }
 
+    // ================= alpha, only when it is unknown (BridgeRegression.cpp:477-503) =================
+    if (do_alpha) {
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        Stream sa(L.key, L.chain0 + (uint32_t)lch[c], t, ST_ALPHA, 0);
+        const AlphaProposal pr = alpha_propose(sa, al_s[g * C + c]);
+        double sn = 0.0, so = 0.0;
+#pragma unroll
+        for (int jj = 0; jj < J; ++jj)
+          if (jj * 32 * W + 32 * w + lane < P) alpha_terms(cur[c][jj], tau_c[c], pr, sn, so);
+        sn = warp_sum(sn); so = warp_sum(so);
+        if (W > 1) {
+          if (lane == 0) { redg0[(w * C + c) * 2] = sn; redg0[(w * C + c) * 2 + 1] = so; }
+          bar_sync(bar_id, bar_n);
+          if (w == 0) { sn = 0.0; so = 0.0; for (int ww = 0; ww < W; ++ww) { sn += redg0[(ww * C + c) * 2]; so += redg0[(ww * C + c) * 2 + 1]; } }
+        }
+        if (w == 0 && lane == 0) al_s[g * C + c] = alpha_decide(sa, pr, sn, so, P, L.h.alpha_a, L.h.alpha_b);
+      }
+      group_sync();
+    }
+
     // ================= store =================
     if (store) {
 #pragma unroll
@@ -481,7 +510,7 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
           const size_t o = (size_t)lch[c] * L.sink.chain_stride + slot;
           if (L.sink.sig2) L.sink.sig2[o] = sig2_c[c];
           if (L.sink.tau) L.sink.tau[o] = tau_c[c];
-          if (L.sink.alpha) L.sink.alpha[o] = alpha;
+          if (L.sink.alpha) L.sink.alpha[o] = al_s[g * C + c];
         }
       }
     }
@@ -497,7 +526,7 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
       const int j = jj * 32 * W + 32 * w + lane;
       if (j < P) { L.beta[(size_t)lch[c] * P + j] = cur[c][jj]; L.u[(size_t)lch[c] * P + j] = ug[c * P + j]; L.z[(size_t)lch[c] * P + j] = zg[c * P + j]; }
     }
-    if (w == 0 && lane == 0) { L.tau[lch[c]] = tau_c[c]; L.sig2[lch[c]] = sig2_c[c]; L.alpha[lch[c]] = alpha; }
+    if (w == 0 && lane == 0) { L.tau[lch[c]] = tau_c[c]; L.sig2[lch[c]] = sig2_c[c]; L.alpha[lch[c]] = al_s[g * C + c]; }
   }
   status = __reduce_or_sync(slmask, status);
   if (sl == 0 && status && cbase + dc < L.nchains) atomicOr(L.status + lch_d, status);

@@ -88,7 +88,8 @@ enum {
   BB_ST_U = 8,       /* sample_u            :97-110    (tri) */
   BB_ST_BETA = 16,   /* sample_beta :405-433 (tri) | sample_beta_stable :552-575 (stb) | the *_ortho forms */
   BB_ST_LAMBDA = 32, /* sample_lambda       :506-510   (stb) */
-  BB_ST_ALL = 63
+  BB_ST_ALPHA = 64,  /* sample_alpha_marg   :477-503   (only acts when true_alpha <= 0: alpha unknown) */
+  BB_ST_ALL = 127
 };
 
 /* which per-iteration draws bb_chains_run keeps (bit mask) and bb_chains_fetch returns */
@@ -132,6 +133,10 @@ int bb_chains_set(bb_chains *c, const double *beta, const double *u, const doubl
                   const double *sig2, const double *tau);
 int bb_chains_get(const bb_chains *c, double *beta, double *u, double *aux, double *shape,
                   double *sig2, double *tau, unsigned int *status);
+/* alpha of every chain, [nchains] host memory: `set` (may be NULL) is installed first, then the current
+ * values are copied to `get` (may be NULL).  Chains start at 0.5 (BridgeWrapper.cpp:125,246,363,474); the
+ * state only moves when alpha is unknown (true_alpha <= 0, BridgeWrapper.cpp:109,152,185). */
+int bb_chains_alpha(bb_chains *c, const double *set, double *get);
 /* reserve a device buffer for `nslots` stored iterations per chain of the outputs in out_mask */
 int bb_chains_reserve(bb_chains *c, long long nslots, int out_mask);
 /* Advance every chain by niter iterations; iteration index of the first = iter0 (RNG counter).
