@@ -21,6 +21,7 @@ namespace {
 thread_local std::string g_err;
 long long g_launches = 0;
 unsigned long long g_seed = 20121027ULL;
+unsigned g_scalar_calls = 0;   // Philox `iter` word of the stand-alone scalar samplers: one per call since bb_set_seed
 int g_device = 0;
 int g_verbose = 0;
 
@@ -314,7 +315,7 @@ extern "C" {
 const char* bb_last_error(void) { return g_err.c_str(); }
 int bb_device_count(void) { int n = 0; if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; } return n; }
 long long bb_launch_count(void) { return g_launches; }
-void bb_set_seed(unsigned long long seed) { g_seed = seed; }
+void bb_set_seed(unsigned long long seed) { g_seed = seed; g_scalar_calls = 0; }
 void bb_set_device(int device) { g_device = device; }
 void bb_set_verbose(int v) { g_verbose = v; }
 
@@ -665,6 +666,62 @@ void bridge_reg_stable(double* betap, double* lambdap, double* sig2p, double* ta
     const size_t n = (size_t)(*P) * (*M);
     nan_fill(betap, n); nan_fill(lambdap, n); nan_fill(sig2p, *M); nan_fill(taup, *M); nan_fill(alphap, *M); nan_fill(runtime, 1);
   }
+}
+
+// ---- the stand-alone scalar samplers (BridgeWrapper.h:230-244; bodies BridgeWrapper.cpp:762-984) ----
+namespace {
+void scalar_call(const char* name, int kind, int n, const double* p0, const double* p1, const double* p2, const double* p3, double* x) {
+  if (n <= 0) return;
+  const int rc = guarded([&] {
+    BB_CUDA_CHECK(cudaSetDevice(g_device));
+    cudaStream_t st = cudaStreamPerThread;
+    const double* src[4] = {p0, p1, p2, p3};
+    struct Bufs { double* d[5] = {nullptr, nullptr, nullptr, nullptr, nullptr}; uint32_t* status = nullptr;
+                  ~Bufs() { for (double* q : d) dfree(q); dfree(status); } } b;
+    for (int k = 0; k < 4; ++k)
+      if (src[k]) {
+        b.d[k] = dalloc<double>((size_t)n);
+        BB_CUDA_CHECK(cudaMemcpyAsync(b.d[k], src[k], (size_t)n * sizeof(double), cudaMemcpyHostToDevice, st));
+      }
+    b.d[4] = dalloc<double>((size_t)n);
+    b.status = dalloc<uint32_t>(1);
+    BB_CUDA_CHECK(cudaMemsetAsync(b.status, 0, sizeof(uint32_t), st));
+    const bb::RngKey key{(uint32_t)g_seed, (uint32_t)(g_seed >> 32)};
+    launched(bb::launch_scalar(kind, n, b.d[0], b.d[1], b.d[2], b.d[3], b.d[4], key, g_scalar_calls++, b.status, st));
+    check_launch();
+    BB_CUDA_CHECK(cudaMemcpyAsync(x, b.d[4], (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, st));
+    BB_CUDA_CHECK(cudaStreamSynchronize(st));
+  });
+  if (rc) {
+    std::fprintf(stderr, "%s (bayesbridge_b200): %s\n", name, g_err.c_str());
+    nan_fill(x, (size_t)n);
+  }
+}
+}  // namespace
+
+void rtexpon_rate_left(double* x, double* left, double* rate, int* num) {
+  scalar_call("rtexpon_rate_left", bb::SC_TEXPON_LEFT, *num, left, rate, nullptr, nullptr, x);
+}
+void rtexpon_rate_both(double* x, double* left, double* right, double* rate, int* num) {
+  scalar_call("rtexpon_rate_both", bb::SC_TEXPON_BOTH, *num, left, right, rate, nullptr, x);
+}
+void rtexpon_rate(double* x, double* left, double* right, double* rate, int* num) {
+  scalar_call("rtexpon_rate", bb::SC_TEXPON, *num, left, right, rate, nullptr, x);
+}
+void rtnorm_left(double* x, double* left, double* mu, double* sig, int* num) {
+  scalar_call("rtnorm_left", bb::SC_TNORM_LEFT, *num, left, mu, sig, nullptr, x);
+}
+void rtnorm_both(double* x, double* left, double* right, double* mu, double* sig, int* num) {
+  scalar_call("rtnorm_both", bb::SC_TNORM_BOTH, *num, left, right, mu, sig, x);
+}
+void rtnorm(double* x, double* left, double* right, double* mu, double* sig, int* num) {
+  scalar_call("rtnorm", bb::SC_TNORM, *num, left, right, mu, sig, x);
+}
+void rrtgamma_rate(double* x, double* scale, double* rate, double* right_t, int* num) {
+  scalar_call("rrtgamma_rate", bb::SC_RTGAMMA, *num, scale, rate, right_t, nullptr, x);
+}
+void retstable_LD(double* x, double* alpha, double* V0, double* h, int* num) {
+  scalar_call("retstable_LD", bb::SC_RETSTABLE, *num, alpha, V0, h, nullptr, x);
 }
 
 }  // extern "C"

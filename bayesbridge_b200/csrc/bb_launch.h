@@ -69,6 +69,11 @@ struct StbLargeLaunch {
   long long slot;          // sink slot for this iteration, -1 = do not store
 };
 
+// the reference's stand-alone scalar samplers (BridgeWrapper.h:230-244), bb_scalar.cu
+enum ScalarKind { SC_TEXPON_LEFT = 0, SC_TEXPON_BOTH, SC_TEXPON, SC_TNORM_LEFT, SC_TNORM_BOTH, SC_TNORM, SC_RTGAMMA, SC_RETSTABLE };
+int launch_scalar(int kind, int n, const double* p0, const double* p1, const double* p2, const double* p3, double* out,
+                  RngKey key, uint32_t iter, uint32_t* status, cudaStream_t st);
+
 // ---- host launchers; each returns the number of kernel launches it issued ----
 int launch_tri(const TriLaunch& L, cudaStream_t st);                       // bb_tri.cu
 int launch_stb_small(const StbLaunch& L, cudaStream_t st);                 // bb_stb.cu   (P <= 128)

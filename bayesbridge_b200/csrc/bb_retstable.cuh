@@ -47,11 +47,12 @@ struct RetAlpha {
 // per-item constants (retstable.cpp:121-147); h = beta_j^2/tau^2
 struct RetConst {
   double h, lambda_alpha, log_la, gamma, sgamma, xi, psi, w1, w2, w3;
-  __device__ __forceinline__ void init(double h_, const RetAlpha& A) {
+  // log_v0 = log(V0): 0 for the sweep (V0 = 1, BridgeRegression.cpp:509); general V0 only for the exported scalar sampler
+  __device__ __forceinline__ void init(double h_, const RetAlpha& A, double log_v0 = 0.0) {
     h = h_;
     const double c2 = 2. + RS_C1;
-    log_la = A.alpha * log(h);                 // log(lambda^alpha); -inf when h = 0
-    lambda_alpha = exp(log_la);                // pow(h, alpha)   (:131)
+    log_la = A.alpha * log(h) + log_v0;        // log(lambda^alpha V0); -inf when h = 0
+    lambda_alpha = exp(log_la);                // pow(h, alpha) * V0   (:131)
     gamma = lambda_alpha * A.alpha * A.Ialpha; // :140
     sgamma = sqrt(gamma);
     const double c3 = c2 * sgamma;
@@ -125,14 +126,15 @@ __device__ __forceinline__ int retstable_round_at(const RetAlpha& A, const RetCo
 }
 
 // sequential form, one thread per item
-__device__ inline double retstable_scalar(const Stream& s, double h, double alpha, uint32_t& status) {
-  if (alpha == 1.) return 1.0;  // point mass at V0 (retstable.cpp:104-110)
+__device__ inline double retstable_scalar(const Stream& s, double h, double alpha, uint32_t& status, double V0 = 1.0) {
+  if (alpha == 1.) return V0;  // point mass at V0 (retstable.cpp:104-110)
   RetAlpha A; A.init(alpha);
-  RetConst c; c.init(h, A);
+  const double log_v0 = V0 == 1.0 ? 0.0 : log(V0);
+  RetConst c; c.init(h, A, log_v0);
   uint32_t k = 0; double out = 0.;
   while (k < K_CAP - 8) {
     const int r = retstable_round_at(A, c, s, k, out);
-    if (r == 2) return out;
+    if (r == 2) return V0 == 1.0 ? out : exp(log_v0 * A.inv_alpha) * out;   // V0^(1/alpha) X^-b (retstable.cpp:270)
     k += r == 0 ? 3u : 5u;
   }
   status |= ST_TRIAL_CAP;

@@ -65,6 +65,22 @@ void bb_set_device(int device);
 /* Banner printing of the reference drivers (BridgeWrapper.cpp:112-117,162-163,200): 0 = quiet (default). */
 void bb_set_verbose(int verbose);
 
+/* Stand-alone scalar samplers exported by the reference's shared object next to the two Gibbs entry points
+ * (declarations BridgeWrapper.h:230-244, bodies BridgeWrapper.cpp:762-984; R callers BridgeWrapper.R:295-537).
+ * Every argument is an array of length *num (R recycles before the call); x receives the draws.  Item i draws
+ * from the Philox stream (seed of bb_set_seed, call counter since bb_set_seed, item i), one GPU thread per item.
+ * rtexpon_rate / rtnorm take -Inf / +Inf bounds as the reference's non-R branch does (BridgeWrapper.cpp:830-835,
+ * 927-938).  rrtgamma_rate: `scale` is the SHAPE of the gamma law (the reference's own argument name,
+ * BridgeWrapper.cpp:949,961).  On a CUDA failure the call prints to stderr and NaN-fills x. */
+void rtexpon_rate_left(double *x, double *left, double *rate, int *num);
+void rtexpon_rate_both(double *x, double *left, double *right, double *rate, int *num);
+void rtexpon_rate(double *x, double *left, double *right, double *rate, int *num);
+void rtnorm_left(double *x, double *left, double *mu, double *sig, int *num);
+void rtnorm_both(double *x, double *left, double *right, double *mu, double *sig, int *num);
+void rtnorm(double *x, double *left, double *right, double *mu, double *sig, int *num);
+void rrtgamma_rate(double *x, double *scale, double *rate, double *right_t, int *num);
+void retstable_LD(double *x, double *alpha, double *V0, double *h, int *num);
+
 /* ---------------------------------------------------------------------------------------- */
 /* Part 2: sampler interface                                                                 */
 /* ---------------------------------------------------------------------------------------- */

@@ -389,6 +389,23 @@ def draw_many(kind, n, params=(), seed=1):
     return out
 
 
+SC_KINDS = {"rtexpon_rate_left": 0, "rtexpon_rate_both": 1, "rtexpon_rate": 2, "rtnorm_left": 3, "rtnorm_both": 4,
+            "rtnorm": 5, "rrtgamma_rate": 6, "retstable_LD": 7}
+
+
+def draw_vec(name, params, seed=1, it=0):
+    """the stand-alone sampler entry points (BridgeWrapper.cpp:762-984) on per-item parameter arrays, in the
+    argument order of the .C symbol `name`; see bbo_draw_vec."""
+    L = Port().L
+    L.bbo_draw_vec.argtypes = [C.c_int, C.c_int, _dp, _dp, _dp, _dp, C.c_uint64, C.c_uint32, _dp]
+    ps = [_f64(p) for p in params]
+    n = ps[0].size
+    out = np.zeros(n)
+    ps4 = ps + [None] * (4 - len(ps))
+    L.bbo_draw_vec(SC_KINDS[name], n, *[None if p is None else _p(p) for p in ps4], seed, it, _p(out))
+    return out
+
+
 def philox(ctr, key):
     L = Port().L
     c = (C.c_uint32 * 4)(*ctr); k = (C.c_uint32 * 2)(*key); o = (C.c_uint32 * 4)()

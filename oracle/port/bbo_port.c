@@ -601,6 +601,35 @@ void bbo_draw_many(int kind, int n, const double *p, uint64_t seed, double *out)
     }
   }
 }
+/* The stand-alone sampler entry points of the reference's shared object, vectorised over n parameter sets
+   (Code/C/BridgeWrapper.cpp:762-984, the non-R branches for infinite bounds :830-835, :927-938).  Item i draws
+   from (seed, chain 0, iter, BBO_ST_SCALAR, item i).  kind: 0 rtexpon_rate_left(left=p0, rate=p1),
+   1 rtexpon_rate_both(left, right, rate), 2 rtexpon_rate(left, right, rate), 3 rtnorm_left(left, mu, sig),
+   4 rtnorm_both(left, right, mu, sig), 5 rtnorm(left, right, mu, sig), 6 rrtgamma_rate(shape, rate, right),
+   7 retstable_LD(alpha=p0, V0=p1, h=p2). */
+void bbo_draw_vec(int kind, int n, const double *p0, const double *p1, const double *p2, const double *p3,
+                  uint64_t seed, uint32_t iter, double *out) {
+  bbo_rng r; bbo_rng_key(&r, seed, 0);
+  for (int i = 0; i < n; ++i) {
+    bbo_rng_at(&r, iter, BBO_ST_SCALAR, (uint32_t)i);
+    switch (kind) {
+      case 0: out[i] = bbo_texpon_rate_left(&r, p0[i], p1[i]); break;
+      case 1: out[i] = bbo_texpon_rate_both(&r, p0[i], p1[i], p2[i]); break;
+      case 2: out[i] = isfinite(p1[i]) ? bbo_texpon_rate_both(&r, p0[i], p1[i], p2[i]) : bbo_texpon_rate_left(&r, p0[i], p2[i]); break;
+      case 3: out[i] = bbo_tnorm_left(&r, p0[i], p1[i], p2[i]); break;
+      case 4: out[i] = bbo_tnorm(&r, p0[i], p1[i], p2[i], p3[i]); break;
+      case 5:
+        if (isfinite(p0[i]) && isfinite(p1[i])) out[i] = bbo_tnorm(&r, p0[i], p1[i], p2[i], p3[i]);
+        else if (isfinite(p0[i])) out[i] = bbo_tnorm_left(&r, p0[i], p2[i], p3[i]);
+        else if (isfinite(p1[i])) out[i] = -1.0 * bbo_tnorm_left(&r, -1.0 * p1[i], -1.0 * p2[i], p3[i]);
+        else out[i] = p2[i] + p3[i] * bbo_norm(&r);
+        break;
+      case 6: out[i] = bbo_rtgamma_rate(&r, p0[i], p1[i], p2[i]); break;
+      case 7: out[i] = bbo_retstable_LD(p2[i], p0[i], p1[i], &r); break;
+      default: out[i] = NAN;
+    }
+  }
+}
 /* raw Philox block for known-answer tests */
 void bbo_philox(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) { bbo_philox4x32_10(ctr, key, out); }
 /* single derived draws at an explicit counter position (teacher-forced per-coordinate checks) */

@@ -15,7 +15,8 @@ def test_library_exports_header_symbols():
     L = bb._lib.load()
     hdr = open(os.path.join(ROOT, "include", "bayesbridge_b200.h")).read()
     body = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
-    declared = set(re.findall(r"\b(bb_[a-z0-9_]+|bridge_regression|bridge_reg_stable)\s*\(", body))
+    # every function prototype of the header: `<type> [*]name(` at the start of a declaration
+    declared = set(re.findall(r"^(?:const\s+)?(?:unsigned\s+)?(?:long\s+)*\w+\s+\**([A-Za-z_]\w*)\s*\(", body, flags=re.M))
     assert declared == set(bb._lib.EXPORTS)
     for s in declared:
         assert hasattr(L, s), s
@@ -66,3 +67,32 @@ def test_ess_estimators():
     assert abs(ess.ess_ar(w) / 5000 - 1) < 0.2
     s = ess.summary(np.stack([x[:5000], x[5000:10000]])[:, :, None], runtime=2.0)
     assert s["ESS"].shape == (1,) and s["ESS.sec"][0] == s["ESS"][0] / 2.0
+
+
+def test_scalar_sampler_front_ends_check_parameters(capsys):
+    """the R front ends print and return NA on bad parameters (BridgeWrapper.R:295-537); no device is touched"""
+    from bayesbridge_b200 import samplers as S
+    assert np.isnan(S.rtnorm(10, sig=-1.0)) and np.isnan(S.rtexp(10, rate=0.0)) and np.isnan(S.rrtgamma(10, shape=-1.0))
+    assert np.isnan(S.retstable_ld(10, alpha=1.5)) and np.isnan(S.rtnorm_both(10, left=2.0, right=1.0))
+    assert np.isnan(S.rtexp_left(0)) and np.isnan(S.retstable_ld(3, h=-1.0))
+    assert "must be" in capsys.readouterr().out
+
+
+def test_port_vector_entry_points_agree_with_the_bulk_draws():
+    """bbo_draw_vec (per-item parameters, the .C symbols' argument order) against bbo_draw_many (one parameter set)"""
+    import bb_oracle as O
+    n = 200
+    one = np.ones(n)
+    cases = [("rtnorm_both", [-0.5 * one, 1.5 * one, 0.2 * one, 0.7 * one], 3, (-0.5, 1.5, 0.2, 0.7)),
+             ("rtnorm_left", [1.0 * one, 0.0 * one, 2.0 * one], 4, (1.0, 0.0, 2.0)),
+             ("rtexpon_rate_left", [0.3 * one, 2.0 * one], 5, (0.3, 2.0)),
+             ("rtexpon_rate_both", [0.3 * one, 0.9 * one, 2.0 * one], 6, (0.3, 0.9, 2.0)),
+             ("rrtgamma_rate", [2.5 * one, 1.5 * one, 1.0 * one], 7, (2.5, 1.5, 1.0)),
+             ("retstable_LD", [0.25 * one, 1.0 * one, 3.0 * one], 8, (3.0, 0.25, 1.0))]
+    for name, ps, kind, scalars in cases:
+        assert np.array_equal(O.draw_vec(name, ps, seed=11, it=0), O.draw_many(kind, n, scalars, seed=11)), name
+    # infinite bounds select the one-sided forms (BridgeWrapper.cpp:830-835, 927-938)
+    inf = np.inf * one
+    assert np.array_equal(O.draw_vec("rtnorm", [1.0 * one, inf, 0.0 * one, 2.0 * one], seed=11), O.draw_many(4, n, (1.0, 0.0, 2.0), seed=11))
+    assert np.array_equal(O.draw_vec("rtnorm", [-inf, -1.0 * one, 0.0 * one, 2.0 * one], seed=11), -O.draw_many(4, n, (1.0, -0.0, 2.0), seed=11))
+    assert np.array_equal(O.draw_vec("rtexpon_rate", [0.3 * one, inf, 2.0 * one], seed=11), O.draw_many(5, n, (0.3, 2.0), seed=11))
