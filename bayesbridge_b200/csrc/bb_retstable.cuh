@@ -9,6 +9,7 @@
 // rounds were scheduled.
 #pragma once
 #include "bb_rng.cuh"
+#include "bb_math.cuh"
 
 namespace bb {
 
@@ -46,7 +47,10 @@ struct RetAlpha {
 
 // per-item constants (retstable.cpp:121-147); h = beta_j^2/tau^2
 struct RetConst {
-  double h, lambda_alpha, log_la, gamma, sgamma, xi, psi, w1, w2, w3;
+  double h, lambda_alpha, log_la, gamma, sgamma, inv_sgamma, xi, psi;
+  double r1, r3;   // branch thresholds w1/(w1+w2) (gamma >= 1) and w3/(w2+w3) (gamma < 1) of the proposal for U (:162-175)
+  // 1: every constant is an ordinary finite number, the straight-line round (bb_math.cuh) applies; 0 (h = 0, overflow): libm round
+  int simple;
   // log_v0 = log(V0): 0 for the sweep (V0 = 1, BridgeRegression.cpp:509); general V0 only for the exported scalar sampler
   __device__ __forceinline__ void init(double h_, const RetAlpha& A, double log_v0 = 0.0) {
     h = h_;
@@ -58,9 +62,13 @@ struct RetConst {
     const double c3 = c2 * sgamma;
     xi = (1. + RS_SQRT2 * c3) / RS_PI;
     psi = c3 * exp(-gamma * RS_PI * RS_PI / 8.) / RS_SQRT_PI;
-    w1 = RS_C1 * xi / sgamma;
-    w2 = 2. * RS_SQRT_PI * psi;
-    w3 = xi * RS_PI;
+    const double w1 = RS_C1 * xi / sgamma;
+    const double w2 = 2. * RS_SQRT_PI * psi;
+    const double w3 = xi * RS_PI;
+    r1 = w1 / (w1 + w2);
+    r3 = w3 / (w2 + w3);
+    inv_sgamma = 1. / sgamma;
+    simple = h > 1e-250 && h < 1e250 && sgamma > 1e-120 && lambda_alpha < 1e100 && r1 == r1 && r3 == r3;
   }
 };
 
@@ -70,7 +78,7 @@ struct RetConst {
 // behind a branch.  Returns 0 = inner trial rejected (3 blocks consumed), 1 = outer trial rejected
 // (5 blocks), 2 = accepted (value in `out`).  The blocks are the ones the sequential reference would
 // consume at that position of its stream, so the accepted value does not depend on scheduling.
-__device__ __forceinline__ int retstable_round_at(const RetAlpha& A, const RetConst& c, const Stream& s, uint32_t k, double& out) {
+static __device__ __noinline__ int retstable_round_libm(const RetAlpha& A, const RetConst& c, const Stream& s, uint32_t k, double& out) {
   const double alpha = A.alpha, Ialpha = A.Ialpha;
   double u0, u0b, u1a, u1b, u2, u2b, u3, u3b, u4a, u4b;
   s.block(k, u0, u0b); s.block(k + 1, u1a, u1b); s.block(k + 2, u2, u2b); s.block(k + 3, u3, u3b); s.block(k + 4, u4a, u4b);
@@ -78,10 +86,10 @@ __device__ __forceinline__ int retstable_round_at(const RetAlpha& A, const RetCo
   const double V = u0;
   double U;
   if (c.gamma >= 1) {
-    if (V < c.w1 / (c.w1 + c.w2)) U = fabs(box_muller(u1a, u1b)) / c.sgamma;
+    if (V < c.r1) U = fabs(box_muller(u1a, u1b)) / c.sgamma;
     else U = RS_PI * (1. - u1a * u1a);
   } else {
-    if (V < c.w3 / (c.w2 + c.w3)) U = RS_PI * u1a;
+    if (V < c.r3) U = RS_PI * u1a;
     else U = RS_PI * (1. - u1a * u1a);
   }
   const double W = u2;
@@ -123,6 +131,59 @@ __device__ __forceinline__ int retstable_round_at(const RetAlpha& A, const RetCo
   else if (X > m + delta) cc -= E_;
   if (!inner_ok) return 0;
   return (X >= 0 && cc <= E) ? 2 : 1;
+}
+
+// The same round as ONE basic block (bb_math.cuh): every alternative of the reference's if/else chains is
+// computed and selected, reciprocals replace divisions where the operand is ready early (exp(-la) for 1/a,
+// exp(lm - la) for m/a), and the only branch left is the rarely taken normal proposal for U.  The independent
+// chains (five Philox blocks, three sinc/log pairs, the outer trial's constants) overlap; measured latency of
+// a round drops from ~8000 to the length of its critical path.  Decisions and draws agree with the libm round
+// to rounding error (each elementary function within a few ulp).  Requires c.simple.
+__device__ __forceinline__ int retstable_round_fast(const RetAlpha& A, const RetConst& c, const Stream& s, uint32_t k, double& out) {
+  const double alpha = A.alpha, Ialpha = A.Ialpha;
+  double u0, u0b, u1a, u1b, u2, u2b, u3, u3b, u4a, u4b;
+  s.block(k, u0, u0b); s.block(k + 1, u1a, u1b); s.block(k + 2, u2, u2b); s.block(k + 3, u3, u3b); s.block(k + 4, u4a, u4b);
+  // ---- inner trial (retstable.cpp:162-207) ----
+  const bool ge1 = c.gamma >= 1;
+  double U;
+  if (ge1 && u0 < c.r1) U = fabs(x_box_muller(u1a, u1b)) * c.inv_sgamma;
+  else U = (!ge1 && u0 < c.r3) ? RS_PI * u1a : RS_PI * (1. - u1a * u1a);
+  const double sA = x_sinc(alpha * U), sI = x_sinc(Ialpha * U), sU = x_sinc(U);
+  const double lsA = x_log(sA), lsI = x_log(sI), lsU = x_log(sU);
+  const double lden = alpha * lsA + Ialpha * lsI;            // log BdB0 denominator (:73-77)
+  const double izeta2 = x_exp(lden) * x_rcp(sU);             // 1 / zeta^2
+  double izeta, zeta;                                        // 1/zeta = sqrt(izeta2), zeta
+  x_sqrt_pair(izeta2, izeta, zeta);
+  const double z = -x_rcp(x_expm1(-x_log1p(alpha * zeta * c.inv_sgamma) * A.inv_alpha));
+  const double rho = RS_PI * x_exp(-c.lambda_alpha * (1. - izeta2)) * x_rcp((1. + RS_C1) * c.sgamma * izeta + z);
+  const double dg = c.xi * (ge1 ? x_exp(-0.5 * c.gamma * U * U) : 1.0);
+  const double dp = U < RS_PI ? c.psi * x_rsqrt(RS_PI - U) : 0.0;
+  const double Z = u2 * rho * (dg + dp);
+  const bool inner_ok = (U < RS_PI && Z <= 1.);
+  // ---- outer trial, speculative (:212-256) ----
+  const double lAval = Ialpha * (A.lI + lsI) + alpha * (A.lA + lsA) - lsU;
+  const double la = lAval * A.inv_Ialpha;
+  const double lm = alpha * (A.log_b - la) + c.log_la;
+  const double a = x_exp(la), ia = x_exp(-la), m = x_exp(lm);
+  const double delta = x_sqrt(alpha * x_exp(lm - la));       // sqrt(m alpha / a)
+  const double a1 = delta * RS_C1, a2 = delta, a3 = z * ia;
+  const double rs = x_rcp(a1 + a2 + a3);
+  const double l4 = x_log(u4a);
+  const bool b1 = u3 < a1 * rs, b2 = !b1 && u3 < (a1 + a2) * rs;
+  const double N_ = b1 ? x_sqrt(-2.0 * l4) * x_cos2pi(u4b) : 0.0;
+  const double E_ = (b1 || b2) ? 0.0 : -l4;
+  const double X = b1 ? m - delta * fabs(N_) : (b2 ? m + delta * u4a : m + delta + E_ * a3);
+  const double E = -x_log(Z);
+  out = x_exp(-A.b * x_log(X));                              // X^-b (retstable.cpp:270 with V0 = 1)
+  double cc = a * (X - m);
+  cc += (m != 0) ? c.h * (out - x_exp(-A.b * lm)) : 0.0;     // h (X^-b - m^-b)  (:248)
+  cc -= X < m ? 0.5 * N_ * N_ : (X > m + delta ? E_ : 0.0);
+  if (!inner_ok) return 0;
+  return (X >= 0 && cc <= E) ? 2 : 1;
+}
+__device__ __forceinline__ int retstable_round_at(const RetAlpha& A, const RetConst& c, const Stream& s, uint32_t k, double& out) {
+  if (__builtin_expect(c.simple, 1)) return retstable_round_fast(A, c, s, k, out);
+  return retstable_round_libm(A, c, s, k, out);
 }
 
 // sequential form, one thread per item
