@@ -9,6 +9,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libbayesbridge_b200.so")
+LIB_PATH = os.environ.get("BB_LIB_PATH", LIB_PATH)   # development: try another build of the same library
 
 dp = C.POINTER(C.c_double)
 ip = C.POINTER(C.c_int)

@@ -9,6 +9,7 @@
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
+#include "bb_math.cuh"
 
 namespace bb {
 
@@ -198,13 +199,15 @@ __device__ __forceinline__ double tnorm(const Stream& s, double left, double rig
 // without the squeeze; trial t consumes blocks first+2t (normal) and first+2t+1 (uniform).
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ bool mt_trial(const Stream& s, uint32_t first, uint32_t t, double d, double c, double& dv) {
-  const double x = s.norm(first + 2 * t);
+  double na, nb;
+  s.block(first + 2 * t, na, nb);
+  const double x = x_box_muller(na, nb);     // straight-line math (bb_math.cuh): the trial is one basic block
   const double u = s.unif(first + 2 * t + 1);
   double v = 1.0 + c * x;
-  if (!(v > 0.0)) return false;
+  const bool pos = v > 0.0;
   v = v * v * v;
   dv = d * v;
-  return log(u) < 0.5 * x * x + d - dv + d * log(v);
+  return pos && x_log(u) < 0.5 * x * x + d - dv + d * x_log(pos ? v : 1.0);
 }
 
 template <bool WARP>

@@ -32,7 +32,10 @@ int launch_stb_small(const StbLaunch& L, cudaStream_t st) {
   if (L.m.P <= 64) {
     static const bool scalar_path = std::getenv("BB_STB64_SCALAR") != nullptr;   // development: the pre-DMMA Cholesky
     static const int nch_env = std::getenv("BB_STB64_NCH") ? std::atoi(std::getenv("BB_STB64_NCH")) : 0;
-    const int nch = nch_env > 0 ? nch_env : (L.nchains >= 4 * 148 / 2 ? 4 : L.nchains >= 148 ? 2 : 1);
+    // two chains per CTA, two CTAs per SM: the CTAs of an SM drift apart, so one runs its latency-bound Cholesky
+    // while the other fills the FP64 pipe with the lambda stage (4 chains in one CTA, in lock step: 10% slower;
+    // one chain per CTA, 4 CTAs per SM: 40% slower; a forced start skew between the two CTAs changes nothing)
+    const int nch = nch_env > 0 ? nch_env : (L.nchains > 2 * 148 ? 2 : 1);
     if (scalar_path) launch64<false, 4>(L, st);
     else if (nch >= 4) launch64<true, 4>(L, st);
     else if (nch >= 2) launch64<true, 2>(L, st);

@@ -49,7 +49,7 @@ __device__ __forceinline__ void chol8_inverse(const double* __restrict__ tile, d
   for (int k = 0; k < 8; ++k) {
     const double piv = a[k][k];
     if (!(piv > 0.0)) status |= ST_CHOL_FAIL;
-    rs[k] = rsqrt(piv);
+    rs[k] = x_rsqrt(piv);
 #pragma unroll
     for (int r = k + 1; r < 8; ++r) a[r][k] *= rs[k];
 #pragma unroll
@@ -124,6 +124,8 @@ __global__ void __launch_bounds__(S64_T * NCH, 4 / NCH) stb64_kernel(const StbLa
   for (int e = tid; e < 8 * 8 * S64_PB; e += S64_T) wi_s[e] = 0.0;   // the upper triangles stay zero
   __syncthreads();
 
+  const int bar_id = 1 + cslot;   // named barrier of this chain's 128 threads (inside the factorisation only)
+
   for (int it = -L.pre_tau; it < L.niter; ++it) {
     const bool pre = it < 0;
     const uint32_t tt = L.iter0 + (pre ? 0u : (uint32_t)it);
@@ -134,7 +136,7 @@ __global__ void __launch_bounds__(S64_T * NCH, 4 / NCH) stb64_kernel(const StbLa
     double p_tau = 0.0, p_q = 0.0, p_g = 0.0;
     if (tid < P) {
       const double b = beta_s[tid];
-      p_tau = exp(alpha * log(fabs(b)));                       // BridgeRegression.cpp:459
+      p_tau = x_exp(alpha * x_log(fabs(b)));                       // BridgeRegression.cpp:459
       if (!pre && do_sig2) {                                   // rss = r0 - 2 d'g + d'XXd, d = beta - bc
         double s = 0.0;
         for (int j = 0; j < P; ++j) s = fma(__ldg(L.m.XX + tid + (size_t)j * P), dl_s[j], s);
@@ -241,7 +243,7 @@ __global__ void __launch_bounds__(S64_T * NCH, 4 / NCH) stb64_kernel(const StbLa
       // registers as DMMA accumulator fragments: tile n = i(i+1)/2 + j belongs to warp n & 3, slot n >> 2.
       // Block column s:  publish tiles (i,s) -> warp 0 factors the diagonal block and inverts its factor
       // (registers, static indices) -> panel L(i,s) = T(i,s) W_s' by DMMA -> trailing T(i,j) -= L(i,s) L(j,s)'
-      // by DMMA.  3 barriers per block column, 24 in all (the scalar path needs 64).
+      // by DMMA.  3 barriers per block column, among the chain's own 4 warps (named barrier).
       const double f = sig2 / (tau * tau);
       const int fr = lane >> 2, fc = 2 * (lane & 3);      // accumulator fragment: row fr, columns fc, fc+1
       const int ar = lane >> 2, ak = lane & 3;            // A/B fragment: row ar, k = ak
@@ -249,8 +251,8 @@ __global__ void __launch_bounds__(S64_T * NCH, 4 / NCH) stb64_kernel(const StbLa
       int ti[9], tj[9];
 #pragma unroll
       for (int sl = 0; sl < 9; ++sl) {
-        const int n = sl * 4 + warp;
-        int i = 0;
+        const int n = sl * 4 + warp;   // recomputed every iteration: keeping 18 indices (even packed in two words)
+        int i = 0;                     // alive across the lambda stage costs more in spills than these few integer ops
         while ((i + 1) * (i + 2) / 2 <= n) ++i;
         ti[sl] = i; tj[sl] = n - i * (i + 1) / 2;
         const int row = 8 * i + fr, col = 8 * tj[sl] + fc;
@@ -270,10 +272,11 @@ __global__ void __launch_bounds__(S64_T * NCH, 4 / NCH) stb64_kernel(const StbLa
 #pragma unroll
         for (int sl = 0; sl < 9; ++sl)
           if (tj[sl] == s) *reinterpret_cast<double2*>(pb_s + (ti[sl] * 8 + fr) * S64_PB + fc) = make_double2(c0[sl], c1[sl]);
-        __syncthreads();
-        // (2) diagonal block: factor and inverse factor (warp 0)
+        bar_sync(bar_id, S64_T);
+        // (2) diagonal block: factor and inverse factor (warp 0; four warps doing it redundantly to save the barrier
+        //     was slower: the FP64 pipe of the SM is shared by the 16 warps of the CTA)
         if (warp == 0) chol8_inverse(pb_s + s * 8 * S64_PB, wi_s + s * 8 * S64_PB, status);
-        __syncthreads();
+        bar_sync(bar_id, S64_T);
         // (3) panel: L(i,s) = T(i,s) W_s'  for i > s, tile i by warp i & 3
         for (int i = s + 1 + ((warp - (s + 1)) & 3); i < 8; i += 4) {
           double d0 = 0.0, d1 = 0.0;
@@ -282,7 +285,7 @@ __global__ void __launch_bounds__(S64_T * NCH, 4 / NCH) stb64_kernel(const StbLa
             dmma_m8n8k4(d0, d1, pb_s[(i * 8 + ar) * S64_PB + k0 + ak], wi_s[(s * 8 + ar) * S64_PB + k0 + ak]);
           *reinterpret_cast<double2*>(S + (8 * i + fr) * LD + 8 * s + fc) = make_double2(d0, d1);
         }
-        __syncthreads();
+        bar_sync(bar_id, S64_T);
         // (4) trailing update of my tiles (i,j), i >= j > s
 #pragma unroll
         for (int sl = 0; sl < 9; ++sl)
