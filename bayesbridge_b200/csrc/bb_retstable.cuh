@@ -208,14 +208,30 @@ __device__ inline double retstable_scalar(const Stream& s, double h, double alph
 // The stream position of an item after some rejected rounds is k0 + 3a + 5b.  Every such offset
 // {0,3,5,6,8,9,10,...} can be evaluated independently because block indices are counters, so when
 // fewer items than threads are unfinished, G = 2..32 lanes take ONE item and evaluate the rounds
-// at the first G reachable offsets at once; a shuffle walk then follows the path the sequential
+// at G reachable offsets at once; a shuffle walk then follows the path the sequential
 // sampler would have taken (0 -> +3 on an inner rejection, +5 on an outer one) and either finds
 // the accepting round or leaves the item at the first offset that was not covered.  The result is
 // bit-identical to the one-round-at-a-time schedule; only the number of passes (each costing the
 // latency of one round, the bottleneck: the rejection tail of max_j trials_j) shrinks.
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ int rs_reach(int i) { return i < 4 ? ((0x6530 >> (4 * i)) & 0xF) : i + 4; }     // 0,3,5,6,8,9,10,...
-__device__ __forceinline__ int rs_slot_of(int pos) { return pos >= 8 ? pos - 4 : (pos == 0 ? 0 : pos == 3 ? 1 : pos == 5 ? 2 : pos == 6 ? 3 : 64); }
+// The G offsets evaluated for one item: the G positions the sequential sampler is MOST LIKELY to visit (an inner
+// rejection, +3, has probability ~0.72 per round, an outer one, +5, ~0.09): 0,3,6,9,12,15,18,11,14,8,17,21,20,5,...
+// Any set gives the same draws; this one needs about one pass in twenty fewer than the first G reachable positions.
+// Tables packed 6 bits per entry.
+__device__ __forceinline__ int rs_unpack(unsigned long long w0, unsigned long long w1, unsigned long long w2, unsigned long long w3, int i) {
+  const int q = i / 10;
+  const unsigned long long w = q == 0 ? w0 : q == 1 ? w1 : q == 2 ? w2 : w3;
+  return (int)((w >> (6 * (i - 10 * q))) & 63ull);
+}
+__device__ __forceinline__ int rs_reach(int i) {        // i-th offset, i < 32
+  return rs_unpack(148105469521846464ull, 584744086747301201ull, 657330275283769566ull, 1058ull, i);
+}
+__device__ __forceinline__ int rs_slot_of(int pos) {    // index of the lane group member that evaluates `pos`, 63: none
+  return pos >= 40 ? 63 : rs_unpack(56853699704127424ull, 488123725904626175ull, 331371938842247884ull, 1142504548344608532ull, pos);
+}
+__device__ __forceinline__ int rs_levels(int G) {       // longest walk through the first G offsets: max offset / 3 + 1
+  return G >= 32 ? 13 : G >= 16 ? 9 : G >= 8 ? 7 : G >= 4 ? 4 : G >= 2 ? 2 : 1;
+}
 
 // NT: threads serving one chain (multiple of 32); every thread of the CTA must call.  beta: per-item
 // coordinate values (shared or global), lam_out: where 2*draw goes (shared or global).
@@ -241,7 +257,7 @@ __device__ inline void lambda_stage_cta(const int tid, int P, const double* beta
     while (G < 32 && n_act * (G * 2) <= NT) G *= 2;
     const int per_pass = NT / G;
     const int sub = tid & (G - 1);
-    int nlvl = rs_reach(G - 1) / 3 + 1;
+    const int nlvl = rs_levels(G);
     for (int base = 0; base < n_act; base += per_pass) {   // (no pass for a chain that is already done: n_act = 0)
       const int slot = base + tid / G;
       const bool valid = slot < n_act;
