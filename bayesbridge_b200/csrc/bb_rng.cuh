@@ -127,26 +127,37 @@ __device__ __forceinline__ TnPlan tn_setup_fast(double a, double b) {
     if (b < 0.0) { p.sgn = -1.0; p.a = -b; p.b = -a; }
     const double aa = p.a, w = p.b - aa;
     if (w * (aa + 1.0) < 1.0) { p.mode = 3; return p; }
-    const double sq = sqrt(aa * aa + 4.0);
+    const double sq = x_sqrt(aa * aa + 4.0);
     p.lam = 0.5 * (aa + sq);
     if (w * fmax(1.0, aa) > 1.648721271) { p.mode = 2; return p; }
-    const double thresh = aa + exp(0.5 + 0.25 * (aa * aa - aa * sq)) / p.lam;
+    const double thresh = aa + x_exp(0.5 + 0.25 * (aa * aa - aa * sq)) * x_rcp(p.lam);
     p.mode = (p.b > thresh) ? 2 : 3;
     return p;
   }
   p.mode = (b - a >= SQRT_2PI) ? 0 : 1;
   return p;
 }
-// one trial from (ua, ub) with nlu = -log(ua) and lub = log(ub) computed ahead of time; the acceptance
-// tests `ub <= exp(t)` of tn_eval are taken in log form, `log(ub) <= t` (same event up to the last ulp).
-__device__ __forceinline__ bool tn_eval_log(const TnPlan& p, double ua, double ub, double nlu, double lub, double& x) {
+// What a trial needs from its two uniforms, computed as soon as the Philox block is there (before the bounds of
+// the step are known): nlu = -log(ua), lub = log(ub) and the Box-Muller normal xn (straight-line math, bb_math.cuh).
+struct TnDraw {
+  double ua, ub, nlu, lub, xn;
+  __device__ __forceinline__ void set(double ua_, double ub_) {
+    ua = ua_; ub = ub_;
+    nlu = -x_log(ua_); lub = x_log(ub_);
+    xn = x_sqrt(2.0 * nlu) * x_cos2pi(ub_);
+  }
+};
+// one trial from a prepared TnDraw; the acceptance tests `ub <= exp(t)` of tn_eval are taken in log form,
+// `log(ub) <= t` (same event up to the last ulp).
+__device__ __forceinline__ bool tn_eval_log(const TnPlan& p, const TnDraw& d, double& x) {
+  const double ua = d.ua, nlu = d.nlu, lub = d.lub;
   if (p.mode & 1) {   // 1: uniform proposal around 0, 3: uniform proposal in the tail -- log density (c0 - x^2)/2, c0 = 0 | a^2
     x = p.a + (p.b - p.a) * ua;
     const double c0 = p.mode == 3 ? p.a * p.a : 0.0;
     return lub <= 0.5 * (c0 - x * x);
   }
-  if (p.mode == 0) { x = sqrt(2.0 * nlu) * cos(TWO_PI * ub); return x >= p.a && x <= p.b; }
-  x = p.a + nlu / p.lam;
+  if (p.mode == 0) { x = d.xn; return x >= p.a && x <= p.b; }
+  x = p.a + nlu * x_rcp(p.lam);
   const double t = x - p.lam;
   return x <= p.b && lub <= -0.5 * t * t;
 }

@@ -380,13 +380,13 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
     const double isig_d = 1.0 / sig_d;
     // RNG look-ahead: the Philox block of a lane's first trial and its two logarithms do not depend on the
     // bounds.  With W > 1 the warp that draws step i+1 prepares them while the drawer of step i is busy.
-    double ua = 0.5, ub = 0.5, nlu = 0.0, lub = 0.0;
+    TnDraw td; td.ua = 0.5; td.ub = 0.5; td.nlu = 0.0; td.lub = 0.0; td.xn = 0.0;
     bool have_rng = false;
     for (int sw = 0; do_beta && sw < nsweep; ++sw) {
       for (int i = 0; i < P; ++i) {
         const bool drawer = (W == 1) || (w == i % W);
         Stream s(L.key, gch_d, t, ST_BETA, (uint32_t)(sw * P + i));
-        if (drawer && !have_rng) { s.block((uint32_t)sl, ua, ub); nlu = -log(ua); lub = log(ub); }
+        if (drawer && !have_rng) { double ua, ub; s.block((uint32_t)sl, ua, ub); td.set(ua, ub); }
         have_rng = false;
         next_column();
         double di = 0.0, mean = 0.0, sd = 1.0, isd = 1.0;
@@ -412,7 +412,7 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
           bar_sync(bar_id, bar_n);
           if (!drawer && i + 1 < P && w == (i + 1) % W) {   // idle until the draw is done: prepare the next step's trial
             Stream sn(L.key, gch_d, t, ST_BETA, (uint32_t)(sw * P + i + 1));
-            sn.block((uint32_t)sl, ua, ub); nlu = -log(ua); lub = log(ub);
+            double ua, ub; sn.block((uint32_t)sl, ua, ub); td.set(ua, ub);
             have_rng = true;
           }
         }
@@ -440,7 +440,7 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
             uint32_t base = 0;
             while (true) {
               double xt = 0.0;
-              const bool acc_ = !fin && tn_eval_log(p, ua, ub, nlu, lub, xt);
+              const bool acc_ = !fin && tn_eval_log(p, td, xt);
               const uint32_t mine = __ballot_sync(0xffffffffu, acc_) & slmask;
               const int src = mine ? (__ffs(mine) - 1) : lane;
               const double xs = __shfl_sync(0xffffffffu, xt, src);
@@ -448,13 +448,13 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
               if (__ballot_sync(0xffffffffu, !fin) == 0u) break;
               base += SL;
               if (base >= K_CAP - 32) { if (!fin) { status |= ST_TRIAL_CAP; x = nan(""); fin = true; } break; }
-              if (!fin) { s.block(base + (uint32_t)sl, ua, ub); nlu = -log(ua); lub = log(ub); }
+              if (!fin) { double ua, ub; s.block(base + (uint32_t)sl, ua, ub); td.set(ua, ub); }
             }
             znew = mean + sd * x;
             if (znew < lm) znew = lm;
             if (znew > rm) znew = rm;
           } else {            // flat(lmax, rmin), BridgeRegression.cpp:280
-            const double u0 = __shfl_sync(0xffffffffu, ua, dc * SL);
+            const double u0 = __shfl_sync(0xffffffffu, td.ua, dc * SL);
             znew = lm + (rm - lm) * u0;
           }
           if (sl == 0) { zg[dc * P + i] = znew; bc[g * C + dc] = znew - zold; }
