@@ -276,7 +276,7 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
         double a = 0.0, r = 0.0;
 #pragma unroll
         for (int jj = 0; jj < J; ++jj)
-          if (jj * 32 * W + 32 * w + lane < P) a += exp(alpha * log(fabs(cur[c][jj])));   // BridgeRegression.cpp:459
+          if (jj * 32 * W + 32 * w + lane < P) a += x_exp(alpha * x_log(fabs(cur[c][jj])));   // BridgeRegression.cpp:459
         if (!pre && do_sig2)
           for (int i = 32 * w + lane; i < P; i += 32 * W) {   // ||y - X beta||^2 = r0 + sum d_i^2 (z_i - zc_i)^2
             const double dz = zg[c * P + i] - __ldg(L.m.zc + i);
@@ -339,23 +339,24 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
           // sample_omega, BridgeRegression.cpp:130-147
           double om; bool one = true;
           if (do_omega) {
-            const double a_j = exp(alpha * log(ab / ((1 - uo) * tau)));
+            const double a_j = x_exp(alpha * x_log(ab / ((1 - uo) * tau)));
             const double prob = alpha / (1 + alpha * a_j);
             Stream so(L.key, gch, t, ST_OMEGA, (uint32_t)j);
             double e1, e2; so.block(1, e1, e2);
             one = so.unif(0) > prob;
-            om = (one ? -log(e1) : -log(e1 * e2)) + a_j;
+            om = -x_log(one ? e1 : e1 * e2) + a_j;
           } else om = L.omega[(size_t)lch[c] * P + j];
           // sample_u, BridgeRegression.cpp:97-110
           double un = uo;
           if (do_u) {
             Stream su(L.key, gch, t, ST_U, (uint32_t)j);
-            const double right = 1 - ab / tau * exp(-1.0 * log(om) / alpha);
+            const double lom = x_log(om) / alpha;
+            const double right = 1 - ab / tau * x_exp(-lom);
             un = right * su.unif(0);
             ug[c * P + j] = un;
           }
           // b_j, BridgeRegression.cpp:409-411
-          bb_[c][jj] = (1.0 - un) * exp(log(om) / alpha) * tau;
+          bb_[c][jj] = (1.0 - un) * x_exp(x_log(om) / alpha) * tau;
           if (valid[c]) {
             if (store) {
               const size_t o = ((size_t)lch[c] * L.sink.chain_stride + slot) * P + j;
