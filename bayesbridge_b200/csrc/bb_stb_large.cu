@@ -1,5 +1,5 @@
 // bb_stb_large.cu -- host side of the large-P stable sweep (bb_stb_large.cuh): one Gibbs iteration =
-// scalar stage, build, blocked Cholesky (potrf / trsm / DMMA syrk per block column), solve.
+// scalar stage, build, blocked left-looking Cholesky (DMMA update / potrf / trsm per block column), solve.
 #include "bb_stb_large.cuh"
 
 namespace bb {
@@ -10,7 +10,7 @@ void stb_large_prepare(int P) {
   const size_t smem_sy = (size_t)2 * SL_NB * SL_LD * sizeof(double);
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_scalar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sc));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));
-  BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
+  BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
 }
 
 int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
@@ -27,13 +27,11 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
     return n;
   }
   stbl_build_kernel<<<dim3(64, nch), 256, 0, st>>>(L); ++n;
-  for (int kb = 0; kb < nblk; ++kb) {
+  for (int kb = 0; kb < nblk; ++kb) {   // left-looking: bring block column kb up to date, factor its diagonal block, solve its panel
+    if (kb > 0) { stbl_update_kernel<<<dim3(nblk - kb, nch), 256, smem_sy, st>>>(L.A, P, kb); ++n; }
     stbl_potrf_kernel<<<nch, SL_T, 0, st>>>(L.A, P, kb, L.status); ++n;
     const int rem = nblk - kb - 1;
-    if (rem > 0) {
-      stbl_trsm_kernel<<<dim3(rem, nch), SL_NB, 0, st>>>(L.A, P, kb); ++n;
-      stbl_syrk_kernel<<<dim3(rem * (rem + 1) / 2, nch), 256, smem_sy, st>>>(L.A, P, kb); ++n;
-    }
+    if (rem > 0) { stbl_trsm_kernel<<<dim3(rem, nch), SL_NB, 0, st>>>(L.A, P, kb); ++n; }
   }
   stbl_solve_kernel<<<nch, SL_T, smem_sv, st>>>(L); ++n;
   if (do_alpha) { stbl_alpha_kernel<<<(nch + 7) / 8, 256, 0, st>>>(L); ++n; }

@@ -333,7 +333,7 @@ def kernel_name(method, P):
         return "tri_sweep_kernel"
     if P <= 64:
         return "stb64_kernel"
-    return "stb_small_kernel" if P <= 128 else "stbl_syrk_kernel (+potrf/trsm/solve)"
+    return "stb_small_kernel" if P <= 128 else "stbl_update_kernel (+potrf/trsm/solve)"
 
 
 def measured_hbm():
