@@ -171,7 +171,7 @@ struct bb_chains {
   double *beta = nullptr, *u = nullptr, *aux = nullptr, *shape = nullptr, *z = nullptr;
   double *sig2 = nullptr, *tau = nullptr, *alpha = nullptr;
   uint32_t* status = nullptr;
-  double *A = nullptr, *sdel = nullptr;     // large-P stable workspace
+  double *A = nullptr, *W = nullptr;        // large-P stable workspace: factors, inverse diagonal blocks
   // draw buffer
   long long nslots = 0; int out_mask = 0;
   double *o_beta = nullptr, *o_u = nullptr, *o_omega = nullptr, *o_shape = nullptr, *o_lambda = nullptr;
@@ -182,7 +182,7 @@ struct bb_chains {
   void free_draws() { dfree(o_beta); dfree(o_u); dfree(o_omega); dfree(o_shape); dfree(o_lambda); dfree(o_sig2); dfree(o_tau); dfree(o_alpha); nslots = 0; out_mask = 0; }
   ~bb_chains() {
     cudaSetDevice(device);
-    dfree(beta); dfree(u); dfree(aux); dfree(shape); dfree(z); dfree(sig2); dfree(tau); dfree(alpha); dfree(status); dfree(A); dfree(sdel);
+    dfree(beta); dfree(u); dfree(aux); dfree(shape); dfree(z); dfree(sig2); dfree(tau); dfree(alpha); dfree(status); dfree(A); dfree(W);
     free_draws();
     if (ev0) cudaEventDestroy(ev0);
     if (ev1) cudaEventDestroy(ev1);
@@ -275,11 +275,11 @@ void chains_run(bb_chains* c, const bb_hyper* hh, unsigned iter0, int niter, int
     L.sink = make_sink(c, thin, slot0);
     launched(bb::launch_stb_small(L, st));
   } else {
-    if (!c->A) { c->A = dalloc<double>((size_t)c->nchains * P * P); c->sdel = dalloc<double>((size_t)c->nchains * P); }
+    if (!c->A) { c->A = dalloc<double>((size_t)c->nchains * P * P); c->W = dalloc<double>((size_t)c->nchains * 64 * 64); }
     bb::StbLargeLaunch L;
     L.m = m->view(); L.h = h; L.key = key; L.nchains = c->nchains; L.chain0 = c->chain0; L.stages = stages;
     L.beta = c->beta; L.lambda = c->aux; L.sig2 = c->sig2; L.tau = c->tau; L.alpha = c->alpha; L.status = c->status;
-    L.A = c->A; L.sdel = c->sdel; L.sink = make_sink(c, thin, slot0);
+    L.A = c->A; L.W = c->W; L.sink = make_sink(c, thin, slot0);
     bb::stb_large_prepare(P);
     for (int it = -pre_tau; it < niter; ++it) {
       L.pre = it < 0; L.iter = iter0 + (it < 0 ? 0 : it);

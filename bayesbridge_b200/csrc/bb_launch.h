@@ -64,7 +64,7 @@ struct StbLargeLaunch {
   double *beta, *lambda, *sig2, *tau, *alpha;
   uint32_t* status;
   double* A;               // [nchains][P][P] column-major workspace (lower triangle holds L)
-  double* sdel;            // [nchains][P] scratch: X'X (beta - bc)
+  double* W;               // [nchains][64][64] inverse of the current diagonal block of the factor (column-major)
   DrawSink sink;
   long long slot;          // sink slot for this iteration, -1 = do not store
 };

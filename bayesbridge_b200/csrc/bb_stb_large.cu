@@ -6,17 +6,20 @@ namespace bb {
 
 void stb_large_prepare(int P) {
   const size_t smem_sc = ((size_t)P + 26) * sizeof(double) + ((size_t)3 * P + 2) * sizeof(int);
-  const size_t smem_sv = (size_t)P * sizeof(double);
+  const size_t smem_sv = ((size_t)P + SL_NB * (SL_NB + 1) + SL_NB) * sizeof(double);
   const size_t smem_sy = (size_t)2 * SL_NB * SL_LD * sizeof(double);
+  const size_t smem_pf = (size_t)2 * SL_NB * (SL_NB + 1) * sizeof(double);
+  BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_potrf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pf));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_scalar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sc));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
+  BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_trsm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
 }
 
 int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
   const int P = L.m.P, nch = L.nchains;
   const size_t smem_sc = ((size_t)P + 26) * sizeof(double) + ((size_t)3 * P + 2) * sizeof(int);
-  const size_t smem_sv = (size_t)P * sizeof(double);
+  const size_t smem_sv = ((size_t)P + SL_NB * (SL_NB + 1) + SL_NB) * sizeof(double);
   const size_t smem_sy = (size_t)2 * SL_NB * SL_LD * sizeof(double);
   const int nblk = (P + SL_NB - 1) / SL_NB;
   int n = 0;
@@ -29,9 +32,9 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
   stbl_build_kernel<<<dim3(64, nch), 256, 0, st>>>(L); ++n;
   for (int kb = 0; kb < nblk; ++kb) {   // left-looking: bring block column kb up to date, factor its diagonal block, solve its panel
     if (kb > 0) { stbl_update_kernel<<<dim3(nblk - kb, nch), 256, smem_sy, st>>>(L.A, P, kb); ++n; }
-    stbl_potrf_kernel<<<nch, SL_T, 0, st>>>(L.A, P, kb, L.status); ++n;
+    stbl_potrf_kernel<<<nch, SL_T, (size_t)2 * SL_NB * (SL_NB + 1) * sizeof(double), st>>>(L.A, L.W, P, kb, L.status); ++n;
     const int rem = nblk - kb - 1;
-    if (rem > 0) { stbl_trsm_kernel<<<dim3(rem, nch), SL_NB, 0, st>>>(L.A, P, kb); ++n; }
+    if (rem > 0) { stbl_trsm_kernel<<<dim3(rem, nch), 256, smem_sy, st>>>(L.A, L.W, P, kb); ++n; }
   }
   stbl_solve_kernel<<<nch, SL_T, smem_sv, st>>>(L); ++n;
   if (do_alpha) { stbl_alpha_kernel<<<(nch + 7) / 8, 256, 0, st>>>(L); ++n; }

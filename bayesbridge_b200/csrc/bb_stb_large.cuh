@@ -16,6 +16,20 @@ namespace bb {
 
 constexpr int SL_NB = 64;
 constexpr int SL_T = 256;
+constexpr int SL_LD = 72;    // smem row stride of a staged 64 x 64 tile (k-major; minimal 2-way pattern)
+
+// acc(64 x 64, 8 warps x 8 rows) += A(64 x 64) B(64 x 64)' with As[k][r] = A(r,k), Bs[k][c] = B(c,k) staged in smem
+__device__ __forceinline__ void tile_mma(const double* As, const double* Bs, double (&acc)[8][2], int lane, int warp) {
+#pragma unroll 4
+  for (int kk = 0; kk < SL_NB; kk += 4) {
+    const double a = As[(kk + (lane & 3)) * SL_LD + warp * 8 + (lane >> 2)];
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+      const double b = Bs[(kk + (lane & 3)) * SL_LD + t * 8 + (lane >> 2)];
+      dmma_m8n8k4(acc[t][0], acc[t][1], a, b);
+    }
+  }
+}
 
 // ---- tau, sig2, lambda: one CTA per chain -------------------------------------------------
 __global__ void __launch_bounds__(SL_T) stbl_scalar_kernel(const StbLargeLaunch L) {
@@ -87,9 +101,12 @@ __global__ void stbl_build_kernel(const StbLargeLaunch L) {
   }
 }
 
-// ---- Cholesky of the diagonal block kb (<= 64 x 64) in shared memory ----
-__global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, int P, int kb, uint32_t* status) {
-  __shared__ double S[SL_NB][SL_NB + 1];
+// ---- Cholesky of the diagonal block kb (<= 64 x 64) in shared memory, and the inverse of its factor ----
+__global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, double* Wall, int P, int kb, uint32_t* status) {
+  extern __shared__ double smem[];
+  typedef double Row[SL_NB + 1];
+  Row* S = reinterpret_cast<Row*>(smem);                              // [64][65] the block / its factor
+  Row* Wm = reinterpret_cast<Row*>(smem + SL_NB * (SL_NB + 1));       // [64][65] inverse factor
   const int ch = blockIdx.x, tid = threadIdx.x;
   double* A = Aall + (size_t)ch * P * P;
   const int k0 = kb * SL_NB, nb = min(SL_NB, P - k0);
@@ -110,33 +127,55 @@ __global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, int P, i
     __syncthreads();
   }
   for (int e = tid; e < nb * nb; e += SL_T) { const int r = e % nb, c = e / nb; if (r >= c) A[(k0 + r) + (size_t)(k0 + c) * P] = S[r][c]; }
-}
-
-// ---- panel: rows below the diagonal block,  X L_kk' = A_panel  (one thread per row) ----
-__global__ void __launch_bounds__(SL_NB) stbl_trsm_kernel(double* Aall, int P, int kb) {
-  __shared__ double Lk[SL_NB][SL_NB + 1];
-  const int ch = blockIdx.y, tid = threadIdx.x;
-  double* A = Aall + (size_t)ch * P * P;
-  const int k0 = kb * SL_NB, nb = min(SL_NB, P - k0);
-  const int r0 = k0 + nb + blockIdx.x * SL_NB;
-  for (int e = tid; e < nb * nb; e += SL_NB) { const int r = e % nb, c = e / nb; Lk[r][c] = A[(k0 + r) + (size_t)(k0 + c) * P]; }
-  __syncthreads();
-  const int row = r0 + tid;
-  if (row >= P) return;
-  double x[SL_NB];
-#pragma unroll
-  for (int c = 0; c < SL_NB; ++c) x[c] = c < nb ? A[row + (size_t)(k0 + c) * P] : 0.0;
-#pragma unroll
-  for (int c = 0; c < SL_NB; ++c) {
+  // W = L^-1 (lower), one thread per column: W(c,c) = 1/L(c,c), W(r,c) = -(sum_{m=c}^{r-1} L(r,m) W(m,c)) / L(r,r).
+  // The panel solve below the block is then a DMMA product with W' (stbl_trsm_kernel).
+  if (tid < SL_NB) {
+    const int c = tid;
+    for (int r = 0; r < SL_NB; ++r) Wm[r][c] = 0.0;
     if (c < nb) {
-      double s = x[c];
-#pragma unroll
-      for (int k = 0; k < SL_NB; ++k) if (k < c) s = fma(-x[k], Lk[c][k], s);
-      x[c] = s / Lk[c][c];
+      Wm[c][c] = 1.0 / S[c][c];
+      for (int r = c + 1; r < nb; ++r) {
+        double sum = 0.0;
+        for (int m = c; m < r; ++m) sum = fma(S[r][m], Wm[m][c], sum);
+        Wm[r][c] = -sum / S[r][r];
+      }
     }
   }
+  __syncthreads();
+  double* W = Wall + (size_t)ch * SL_NB * SL_NB;
+  for (int e = tid; e < SL_NB * SL_NB; e += SL_T) { const int r = e % SL_NB, c = e / SL_NB; W[e] = Wm[r][c]; }
+}
+
+// ---- panel: rows below the diagonal block,  L(i,kb) = C(i,kb) W_kb'  on the FP64 tensor cores ----
+// (X L_kk' = C solved as a product with the inverse factor of the 64 x 64 diagonal block: one 64^3 DMMA tile product
+// per row tile instead of 64 dependent substitution steps per row.)
+__global__ void __launch_bounds__(256) stbl_trsm_kernel(double* Aall, const double* Wall, int P, int kb) {
+  extern __shared__ double smem[];
+  double* As = smem;
+  double* Bs = smem + SL_NB * SL_LD;
+  const int ch = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double* A = Aall + (size_t)ch * P * P;
+  const double* W = Wall + (size_t)ch * SL_NB * SL_NB;
+  const int k0 = kb * SL_NB, nb = min(SL_NB, P - k0);
+  const int i0 = k0 + SL_NB + blockIdx.x * SL_NB;
+  for (int e = tid; e < SL_NB * SL_NB; e += 256) {
+    const int r = e % SL_NB, k = e / SL_NB;
+    As[k * SL_LD + r] = (i0 + r < P && k < nb) ? A[(i0 + r) + (size_t)(k0 + k) * P] : 0.0;
+    Bs[k * SL_LD + r] = W[r + k * SL_NB];          // B(k, c) = W(c, k)
+  }
+  __syncthreads();
+  double acc[8][2];
 #pragma unroll
-  for (int c = 0; c < SL_NB; ++c) if (c < nb) A[row + (size_t)(k0 + c) * P] = x[c];
+  for (int t = 0; t < 8; ++t) { acc[t][0] = 0.0; acc[t][1] = 0.0; }
+  tile_mma(As, Bs, acc, lane, warp);
+#pragma unroll
+  for (int t = 0; t < 8; ++t) {
+    const int r = i0 + warp * 8 + (lane >> 2), c = t * 8 + 2 * (lane & 3);
+    if (r < P) {
+      if (c < nb) A[r + (size_t)(k0 + c) * P] = acc[t][0];
+      if (c + 1 < nb) A[r + (size_t)(k0 + c + 1) * P] = acc[t][1];
+    }
+  }
 }
 
 // ---- block column jb, LEFT-looking, on the FP64 tensor cores:  C(i,jb) = A(i,jb) - sum_{k<jb} L(i,k) L(jb,k)'  ----
@@ -147,7 +186,6 @@ __global__ void __launch_bounds__(SL_NB) stbl_trsm_kernel(double* Aall, int P, i
 // traffic, 27 % of the DGEMM peak.  Left-looking moves 3.3x fewer bytes: each L(i,k) tile is read once per
 // block column below it, the L(jb,k) tiles are shared by the CTAs of a chain through L2.)
 // Panels are staged k-major in smem (ld 72: minimal 2-way pattern).
-constexpr int SL_LD = 72;
 __global__ void __launch_bounds__(256) stbl_update_kernel(double* Aall, int P, int jb) {
   extern __shared__ double smem[];
   double* As = smem;
@@ -167,15 +205,7 @@ __global__ void __launch_bounds__(256) stbl_update_kernel(double* Aall, int P, i
       Bs[k * SL_LD + r] = (j0 + r < P) ? A[(j0 + r) + (size_t)(k0 + k) * P] : 0.0;
     }
     __syncthreads();
-#pragma unroll 4
-    for (int kk = 0; kk < SL_NB; kk += 4) {
-      const double a = As[(kk + (lane & 3)) * SL_LD + warp * 8 + (lane >> 2)];
-#pragma unroll
-      for (int t = 0; t < 8; ++t) {
-        const double b = Bs[(kk + (lane & 3)) * SL_LD + t * 8 + (lane >> 2)];
-        dmma_m8n8k4(acc[t][0], acc[t][1], a, b);
-      }
-    }
+    tile_mma(As, Bs, acc, lane, warp);
     __syncthreads();
   }
 #pragma unroll
@@ -193,27 +223,35 @@ __global__ void __launch_bounds__(SL_T) stbl_solve_kernel(const StbLargeLaunch L
   extern __shared__ double smem[];
   const int P = L.m.P, tid = threadIdx.x, ch = blockIdx.x;
   if (ch >= L.nchains) return;
-  double* x = smem;   // [P]
+  double* x = smem;                 // [P]
+  double* D = x + P;                // [64][65] diagonal block of the factor, staged so that the 64 dependent
+  double* ps = D + SL_NB * (SL_NB + 1);   // pivot steps read shared memory, not HBM;  [64] partial dot products
   const double* A = L.A + (size_t)ch * P * P;
   const uint32_t gch = L.chain0 + (uint32_t)ch;
+  const int lane = tid & 31, warp = tid >> 5;
   const double sig = sqrt(L.sig2[ch]);
   for (int j = tid; j < P; j += SL_T) x[j] = __ldg(L.m.Xy + j);
-  __syncthreads();
+  auto stage_diag = [&](int k0, int nb) {
+    for (int e = tid; e < nb * nb; e += SL_T) { const int r = e % nb, c = e / nb; D[r * (SL_NB + 1) + c] = A[(k0 + r) + (size_t)(k0 + c) * P]; }
+  };
   // forward: L w = Xy, column-oriented
   for (int k0 = 0; k0 < P; k0 += SL_NB) {
     const int nb = min(SL_NB, P - k0);
+    stage_diag(k0, nb);
+    __syncthreads();
     if (tid < 32) {   // diagonal block by one warp
-      for (int k = k0; k < k0 + nb; ++k) {
-        const double xk = x[k] / A[k + (size_t)k * P];
+      for (int k = 0; k < nb; ++k) {
+        const double xk = x[k0 + k] / D[k * (SL_NB + 1) + k];
         __syncwarp();
-        if (tid == 0) x[k] = xk;
-        for (int r = k + 1 + tid; r < k0 + nb; r += 32) x[r] = fma(-A[r + (size_t)k * P], xk, x[r]);
+        if (tid == 0) x[k0 + k] = xk;
+        for (int r = k + 1 + tid; r < nb; r += 32) x[k0 + r] = fma(-D[r * (SL_NB + 1) + k], xk, x[k0 + r]);
         __syncwarp();
       }
     }
     __syncthreads();
-    for (int r = k0 + nb + tid; r < P; r += SL_T) {
+    for (int r = k0 + nb + tid; r < P; r += SL_T) {   // rows below: coalesced along r
       double s = x[r];
+#pragma unroll 8
       for (int k = k0; k < k0 + nb; ++k) s = fma(-A[r + (size_t)k * P], x[k], s);
       x[r] = s;
     }
@@ -221,27 +259,32 @@ __global__ void __launch_bounds__(SL_T) stbl_solve_kernel(const StbLargeLaunch L
   }
   for (int j = tid; j < P; j += SL_T) { Stream s(L.key, gch, L.iter, ST_BETA_STB, (uint32_t)j); x[j] = fma(sig, s.norm(0), x[j]); }
   __syncthreads();
-  // backward: L' b = x ; row-oriented over the stored lower triangle
+  // backward: L' b = x over the stored lower triangle: column k of L is contiguous, one warp per column, lanes along r
   const int nblk = (P + SL_NB - 1) / SL_NB;
   for (int kbk = nblk - 1; kbk >= 0; --kbk) {
     const int k0 = kbk * SL_NB, nb = min(SL_NB, P - k0);
-    // x[k0..k0+nb) -= L[r, k0..]' x[r] for r >= k0+nb : each thread handles one k and strides over r? use 4 threads per k
-    {
-      const int k = k0 + (tid & (SL_NB - 1)), part = tid / SL_NB;   // 4 parts
-      double s = 0.0;
-      if (k < k0 + nb) for (int r = k0 + nb + part; r < P; r += SL_T / SL_NB) s = fma(A[r + (size_t)k * P], x[r], s);
-      __shared__ double ps[SL_T];
-      ps[tid] = s;
-      __syncthreads();
-      if (tid < nb) x[k0 + tid] -= ps[tid] + ps[tid + SL_NB] + ps[tid + 2 * SL_NB] + ps[tid + 3 * SL_NB];
-      __syncthreads();
+    stage_diag(k0, nb);
+    for (int kk = warp; kk < nb; kk += SL_T / 32) {
+      const double* col = A + (size_t)(k0 + kk) * P;
+      double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+      int r = k0 + nb + lane;
+      for (; r + 96 < P; r += 128) {
+        s0 = fma(col[r], x[r], s0); s1 = fma(col[r + 32], x[r + 32], s1);
+        s2 = fma(col[r + 64], x[r + 64], s2); s3 = fma(col[r + 96], x[r + 96], s3);
+      }
+      for (; r < P; r += 32) s0 = fma(col[r], x[r], s0);
+      const double sum = warp_sum((s0 + s1) + (s2 + s3));
+      if (lane == 0) ps[kk] = sum;
     }
+    __syncthreads();
+    if (tid < nb) x[k0 + tid] -= ps[tid];
+    __syncthreads();
     if (tid < 32) {
-      for (int k = k0 + nb - 1; k >= k0; --k) {
-        const double xk = x[k] / A[k + (size_t)k * P];
+      for (int k = nb - 1; k >= 0; --k) {
+        const double xk = x[k0 + k] / D[k * (SL_NB + 1) + k];
         __syncwarp();
-        if (tid == 0) x[k] = xk;
-        for (int r = k0 + tid; r < k; r += 32) x[r] = fma(-A[k + (size_t)r * P], xk, x[r]);
+        if (tid == 0) x[k0 + k] = xk;
+        for (int r = tid; r < k; r += 32) x[k0 + r] = fma(-D[k * (SL_NB + 1) + r], xk, x[k0 + r]);
         __syncwarp();
       }
     }
