@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(256) stbl_trsm_kernel(double* Aall, const doub
 // traffic, 27 % of the DGEMM peak.  Left-looking moves 3.3x fewer bytes: each L(i,k) tile is read once per
 // block column below it, the L(jb,k) tiles are shared by the CTAs of a chain through L2.)
 // Panels are staged k-major in smem (ld 72: minimal 2-way pattern).
-__global__ void __launch_bounds__(256) stbl_update_kernel(double* Aall, int P, int jb) {
+__global__ void __launch_bounds__(256, 2) stbl_update_kernel(double* Aall, int P, int jb) {
   extern __shared__ double smem[];
   double* As = smem;
   double* Bs = smem + SL_NB * SL_LD;
@@ -197,23 +197,35 @@ __global__ void __launch_bounds__(256) stbl_update_kernel(double* Aall, int P, i
   double acc[8][2];
 #pragma unroll
   for (int t = 0; t < 8; ++t) { acc[t][0] = 0.0; acc[t][1] = 0.0; }
-  for (int kb = 0; kb < jb; ++kb) {
-    const int k0 = kb * SL_NB;
-    for (int e = tid; e < SL_NB * SL_NB; e += 256) {
-      const int r = e % SL_NB, k = e / SL_NB;
-      As[k * SL_LD + r] = (i0 + r < P) ? A[(i0 + r) + (size_t)(k0 + k) * P] : 0.0;
-      Bs[k * SL_LD + r] = (j0 + r < P) ? A[(j0 + r) + (size_t)(k0 + k) * P] : 0.0;
+  // thread -> 16 elements of each 64 x 64 tile: row r = tid & 63, columns k = (tid >> 6) + 4 q (coalesced along r)
+  const int r = tid & (SL_NB - 1), kq = tid >> 6;
+  const bool ra = i0 + r < P, rb = j0 + r < P;
+  const double* pa_src = A + (i0 + r) + (size_t)kq * P;
+  const double* pb_src = A + (j0 + r) + (size_t)kq * P;
+  double pa[16], pb[16];
+  auto fetch = [&](int kb) {   // the global loads of the NEXT step are in flight while this step's tile product runs
+    const size_t off = (size_t)kb * SL_NB * P;
+#pragma unroll
+    for (int q = 0; q < 16; ++q) {
+      pa[q] = ra ? pa_src[off + (size_t)(4 * q) * P] : 0.0;
+      pb[q] = rb ? pb_src[off + (size_t)(4 * q) * P] : 0.0;
     }
+  };
+  if (jb > 0) fetch(0);
+  for (int kb = 0; kb < jb; ++kb) {
+#pragma unroll
+    for (int q = 0; q < 16; ++q) { As[(kq + 4 * q) * SL_LD + r] = pa[q]; Bs[(kq + 4 * q) * SL_LD + r] = pb[q]; }
     __syncthreads();
+    if (kb + 1 < jb) fetch(kb + 1);
     tile_mma(As, Bs, acc, lane, warp);
     __syncthreads();
   }
 #pragma unroll
   for (int t = 0; t < 8; ++t) {
-    const int r = i0 + warp * 8 + (lane >> 2), c = j0 + t * 8 + 2 * (lane & 3);
-    if (r < P) {
-      if (c < P && (ti > jb || r >= c)) A[r + (size_t)c * P] -= acc[t][0];
-      if (c + 1 < P && (ti > jb || r >= c + 1)) A[r + (size_t)(c + 1) * P] -= acc[t][1];
+    const int rr = i0 + warp * 8 + (lane >> 2), c = j0 + t * 8 + 2 * (lane & 3);
+    if (rr < P) {
+      if (c < P && (ti > jb || rr >= c)) A[rr + (size_t)c * P] -= acc[t][0];
+      if (c + 1 < P && (ti > jb || rr >= c + 1)) A[rr + (size_t)(c + 1) * P] -= acc[t][1];
     }
   }
 }
