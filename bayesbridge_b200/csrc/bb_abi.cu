@@ -176,8 +176,8 @@ struct bb_chains {
   long long nslots = 0; int out_mask = 0;
   double *o_beta = nullptr, *o_u = nullptr, *o_omega = nullptr, *o_shape = nullptr, *o_lambda = nullptr;
   double *o_sig2 = nullptr, *o_tau = nullptr, *o_alpha = nullptr;
-  cudaStream_t stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaStream_t stream = nullptr, stream2 = nullptr;   // stream2: second half-batch of the large-P stable path
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr, ev_join = nullptr;
 
   void free_draws() { dfree(o_beta); dfree(o_u); dfree(o_omega); dfree(o_shape); dfree(o_lambda); dfree(o_sig2); dfree(o_tau); dfree(o_alpha); nslots = 0; out_mask = 0; }
   ~bb_chains() {
@@ -186,6 +186,9 @@ struct bb_chains {
     free_draws();
     if (ev0) cudaEventDestroy(ev0);
     if (ev1) cudaEventDestroy(ev1);
+    if (ev_fork) cudaEventDestroy(ev_fork);
+    if (ev_join) cudaEventDestroy(ev_join);
+    if (stream2) cudaStreamDestroy(stream2);
     if (stream) cudaStreamDestroy(stream);
   }
 };
@@ -281,12 +284,44 @@ void chains_run(bb_chains* c, const bb_hyper* hh, unsigned iter0, int niter, int
     L.beta = c->beta; L.lambda = c->aux; L.sig2 = c->sig2; L.tau = c->tau; L.alpha = c->alpha; L.status = c->status;
     L.A = c->A; L.W = c->W; L.sink = make_sink(c, thin, slot0);
     bb::stb_large_prepare(P);
+    // Two half-batches on two streams: the low-parallelism kernels of one half (diagonal-block factorisation, panel
+    // solve, substitution: one CTA per chain) run while the other half's update kernel fills the SMs.  The halves
+    // are independent chains, so they only meet again at the end of the call.
+    const int nhalf = c->nchains >= 16 ? 2 : 1;
+    if (nhalf == 2 && !c->stream2) {
+      BB_CUDA_CHECK(cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking));
+      BB_CUDA_CHECK(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+      BB_CUDA_CHECK(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
+    }
+    cudaStream_t sts[2] = {st, c->stream2};
+    if (nhalf == 2) { BB_CUDA_CHECK(cudaEventRecord(c->ev_fork, st)); BB_CUDA_CHECK(cudaStreamWaitEvent(c->stream2, c->ev_fork, 0)); }
+    auto half = [&](int h) {
+      bb::StbLargeLaunch H = L;
+      const int h0 = h == 0 ? 0 : c->nchains / 2;
+      const int n = nhalf == 1 ? c->nchains : (h == 0 ? c->nchains / 2 : c->nchains - c->nchains / 2);
+      const size_t o1 = (size_t)h0, oP = (size_t)h0 * P;
+      H.nchains = n; H.chain0 = L.chain0 + (uint32_t)h0;
+      H.beta += oP; H.lambda += oP; H.sig2 += o1; H.tau += o1; H.alpha += o1; H.status += o1;
+      H.A += oP * P; H.W += o1 * 64 * 64;
+      const size_t os = o1 * (size_t)H.sink.chain_stride;
+      if (H.sink.beta) H.sink.beta += os * P;
+      if (H.sink.lambda) H.sink.lambda += os * P;
+      if (H.sink.sig2) H.sink.sig2 += os;
+      if (H.sink.tau) H.sink.tau += os;
+      if (H.sink.alpha) H.sink.alpha += os;
+      if (H.sink.sum) { H.sink.sum += oP; H.sink.sumsq += oP; }
+      return H;
+    };
     for (int it = -pre_tau; it < niter; ++it) {
       L.pre = it < 0; L.iter = iter0 + (it < 0 ? 0 : it);
       const bool store = c->nslots > 0 && thin > 0 && it >= 0 && ((it + 1) % thin) == 0;
       L.slot = store ? slot0 + (it + 1) / thin - 1 : -1;
-      launched(bb::launch_stb_large_iter(L, (stages & BB_ST_BETA) != 0, st));
+      for (int h = 0; h < nhalf; ++h) {
+        bb::StbLargeLaunch H = half(h);
+        launched(bb::launch_stb_large_iter(H, (stages & BB_ST_BETA) != 0, sts[h]));
+      }
     }
+    if (nhalf == 2) { BB_CUDA_CHECK(cudaEventRecord(c->ev_join, c->stream2)); BB_CUDA_CHECK(cudaStreamWaitEvent(st, c->ev_join, 0)); }
     check_launch();
   }
   BB_CUDA_CHECK(cudaEventRecord(c->ev1, st));

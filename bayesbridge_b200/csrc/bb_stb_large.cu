@@ -36,7 +36,7 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
     const int rem = nblk - kb - 1;
     if (rem > 0) { stbl_trsm_kernel<<<dim3(rem, nch), 256, smem_sy, st>>>(L.A, L.W, P, kb); ++n; }
   }
-  stbl_solve_kernel<<<nch, SL_T, smem_sv, st>>>(L); ++n;
+  stbl_solve_kernel<<<nch, SV_T, smem_sv, st>>>(L); ++n;
   if (do_alpha) { stbl_alpha_kernel<<<(nch + 7) / 8, 256, 0, st>>>(L); ++n; }
   return n;
 }

@@ -231,7 +231,8 @@ __global__ void __launch_bounds__(256, 2) stbl_update_kernel(double* Aall, int P
 }
 
 // ---- beta = L^-T (L^-1 Xy + sig eps): one CTA per chain, blocked substitution ----
-__global__ void __launch_bounds__(SL_T) stbl_solve_kernel(const StbLargeLaunch L) {
+constexpr int SV_T = 1024;   // threads of the solve kernel: one CTA streams a chain's 16 MB factor twice, it needs the loads in flight
+__global__ void __launch_bounds__(SV_T) stbl_solve_kernel(const StbLargeLaunch L) {
   extern __shared__ double smem[];
   const int P = L.m.P, tid = threadIdx.x, ch = blockIdx.x;
   if (ch >= L.nchains) return;
@@ -242,9 +243,9 @@ __global__ void __launch_bounds__(SL_T) stbl_solve_kernel(const StbLargeLaunch L
   const uint32_t gch = L.chain0 + (uint32_t)ch;
   const int lane = tid & 31, warp = tid >> 5;
   const double sig = sqrt(L.sig2[ch]);
-  for (int j = tid; j < P; j += SL_T) x[j] = __ldg(L.m.Xy + j);
+  for (int j = tid; j < P; j += SV_T) x[j] = __ldg(L.m.Xy + j);
   auto stage_diag = [&](int k0, int nb) {
-    for (int e = tid; e < nb * nb; e += SL_T) { const int r = e % nb, c = e / nb; D[r * (SL_NB + 1) + c] = A[(k0 + r) + (size_t)(k0 + c) * P]; }
+    for (int e = tid; e < nb * nb; e += SV_T) { const int r = e % nb, c = e / nb; D[r * (SL_NB + 1) + c] = A[(k0 + r) + (size_t)(k0 + c) * P]; }
   };
   // forward: L w = Xy, column-oriented
   for (int k0 = 0; k0 < P; k0 += SL_NB) {
@@ -261,7 +262,7 @@ __global__ void __launch_bounds__(SL_T) stbl_solve_kernel(const StbLargeLaunch L
       }
     }
     __syncthreads();
-    for (int r = k0 + nb + tid; r < P; r += SL_T) {   // rows below: coalesced along r
+    for (int r = k0 + nb + tid; r < P; r += SV_T) {   // rows below: coalesced along r
       double s = x[r];
 #pragma unroll 8
       for (int k = k0; k < k0 + nb; ++k) s = fma(-A[r + (size_t)k * P], x[k], s);
@@ -269,14 +270,14 @@ __global__ void __launch_bounds__(SL_T) stbl_solve_kernel(const StbLargeLaunch L
     }
     __syncthreads();
   }
-  for (int j = tid; j < P; j += SL_T) { Stream s(L.key, gch, L.iter, ST_BETA_STB, (uint32_t)j); x[j] = fma(sig, s.norm(0), x[j]); }
+  for (int j = tid; j < P; j += SV_T) { Stream s(L.key, gch, L.iter, ST_BETA_STB, (uint32_t)j); x[j] = fma(sig, s.norm(0), x[j]); }
   __syncthreads();
   // backward: L' b = x over the stored lower triangle: column k of L is contiguous, one warp per column, lanes along r
   const int nblk = (P + SL_NB - 1) / SL_NB;
   for (int kbk = nblk - 1; kbk >= 0; --kbk) {
     const int k0 = kbk * SL_NB, nb = min(SL_NB, P - k0);
     stage_diag(k0, nb);
-    for (int kk = warp; kk < nb; kk += SL_T / 32) {
+    for (int kk = warp; kk < nb; kk += SV_T / 32) {
       const double* col = A + (size_t)(k0 + kk) * P;
       double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
       int r = k0 + nb + lane;
@@ -303,7 +304,7 @@ __global__ void __launch_bounds__(SL_T) stbl_solve_kernel(const StbLargeLaunch L
     __syncthreads();
   }
   double* beta = L.beta + (size_t)ch * P;
-  for (int j = tid; j < P; j += SL_T) {
+  for (int j = tid; j < P; j += SV_T) {
     beta[j] = x[j];
     if (L.slot >= 0) {
       const size_t o = ((size_t)ch * L.sink.chain_stride + L.slot) * P + j;
