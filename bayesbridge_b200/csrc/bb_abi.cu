@@ -46,6 +46,7 @@ struct bb_model {
   double *d = nullptr, *a = nullptr, *mean = nullptr, *zc = nullptr, *d2 = nullptr, *gc = nullptr, *bc = nullptr, *bz = nullptr;
   double r0z = 0, r0b = 0, yy = 0;
   bool singular = false;
+  bool lazy_svd = false;   // P > N: the SVD factors (triangle sampler only) are built on first use, see ensure_svd
   double precompute_ms = 0;
   cudaStream_t stream = nullptr;
 
@@ -76,16 +77,16 @@ void model_alloc(bb_model* m) {
 }
 
 // After tV/Vc/VQ/d/a/mean/zc/d2, XX, Xy, bhat are in place: expansion centres and residuals.
-void model_finish(bb_model* m, bool have_rows) {
+void model_finish(bb_model* m, bool have_rows, bool stable_only = false) {
   const int P = m->P; cudaStream_t st = m->stream;
-  // z-space centre zc -> beta-space bz = V zc
-  launched(bb::vz_device(m->Vc, m->zc, P, m->ldv, m->bz, st));
+  // z-space centre zc -> beta-space bz = V zc   (triangle sampler)
+  if (!stable_only) launched(bb::vz_device(m->Vc, m->zc, P, m->ldv, m->bz, st));
   // beta-space centre for the stable path: bhat (0 if singular)
   BB_CUDA_CHECK(cudaMemcpyAsync(m->bc, m->bhat, P * sizeof(double), cudaMemcpyDeviceToDevice, st));
   launched(bb::grad_device(m->XX, m->Xy, m->bc, P, m->gc, st));
   if (have_rows) {
     int nl = 0;
-    m->r0z = bb::resid_device(m->X, m->y, m->bz, m->N, P, st, &nl);
+    if (!stable_only) m->r0z = bb::resid_device(m->X, m->y, m->bz, m->N, P, st, &nl);
     m->r0b = bb::resid_device(m->X, m->y, m->bc, m->N, P, st, &nl);
     launched(nl);
   }
@@ -340,6 +341,21 @@ int guarded(F&& f) {
   return 1;
 }
 
+void ensure_svd(const bb_model* cm) {
+  bb_model* m = const_cast<bb_model*>(cm);
+  if (!m->lazy_svd) return;
+  auto t0 = std::chrono::steady_clock::now();
+  const int P = m->P;
+  double* W = dalloc<double>((size_t)P * P);
+  BB_CUDA_CHECK(cudaMemcpyAsync(W, m->XX, (size_t)P * P * sizeof(double), cudaMemcpyDeviceToDevice, m->stream));
+  model_factor(m, W, P, true);
+  dfree(W);
+  model_finish(m, m->X != nullptr);
+  BB_CUDA_CHECK(cudaStreamSynchronize(m->stream));
+  m->lazy_svd = false;
+  m->precompute_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+}
+
 }  // namespace
 
 // ===========================================================================================
@@ -368,13 +384,15 @@ bb_model* bb_model_create(const double* X, const double* y, int N, int P, int de
       BB_CUDA_CHECK(cudaMemcpyAsync(W, m->X, (size_t)N * P * sizeof(double), cudaMemcpyDeviceToDevice, m->stream));
       model_factor(m, W, N, false);
       dfree(W);
+      model_finish(m, true);
     } else {
-      double* W = dalloc<double>((size_t)P * P);
-      BB_CUDA_CHECK(cudaMemcpyAsync(W, m->XX, (size_t)P * P * sizeof(double), cudaMemcpyDeviceToDevice, m->stream));
-      model_factor(m, W, P, true);
-      dfree(W);
+      // P > N: X'X is singular by rank, so the least-squares start is 0 (BridgeRegression.cpp:79-91) and the stable
+      // sampler needs nothing else.  The P x P eigen-decomposition (0.9 s at P = 2000) is only used by the rotated
+      // sweep of the triangle sampler: built when such chains (or the factors) are first asked for.
+      m->lazy_svd = true; m->singular = true;
+      BB_CUDA_CHECK(cudaMemsetAsync(m->bhat, 0, P * sizeof(double), m->stream));
+      model_finish(m, true, true);
     }
-    model_finish(m, true);
     BB_CUDA_CHECK(cudaStreamSynchronize(m->stream));
     m->precompute_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
   });
@@ -450,6 +468,7 @@ double bb_model_precompute_ms(const bb_model* m) { return m->precompute_ms; }
 int bb_model_get(const bb_model* m, double* XX, double* Xy, double* bhat, double* tV, double* d, double* a) {
   return guarded([&] {
     BB_CUDA_CHECK(cudaSetDevice(m->device));
+    if (tV || d || a) ensure_svd(m);
     const size_t P = m->P;
     if (XX) BB_CUDA_CHECK(cudaMemcpy(XX, m->XX, P * P * sizeof(double), cudaMemcpyDeviceToHost));
     if (Xy) BB_CUDA_CHECK(cudaMemcpy(Xy, m->Xy, P * sizeof(double), cudaMemcpyDeviceToHost));
@@ -465,6 +484,7 @@ bb_chains* bb_chains_create(const bb_model* m, int method, int ortho, int nchain
   const int rc = guarded([&] {
     if (!m || nchains < 1) throw std::string("bb_chains_create: bad arguments");
     BB_CUDA_CHECK(cudaSetDevice(m->device));
+    if (method == BB_TRI && !ortho) ensure_svd(m);
     c = new bb_chains();
     c->m = m; c->device = m->device; c->method = method; c->ortho = ortho; c->nchains = nchains; c->seed = seed; c->chain0 = chain0;
     BB_CUDA_CHECK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));

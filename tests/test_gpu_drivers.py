@@ -110,3 +110,27 @@ def test_chain_ids_are_shard_invariant():
     tri = bb.bridge_batched(y, X, 5, method="triangle", nchains=5, seed=5, burn=2, want=("beta",))
     t2 = bb.bridge_batched(y, X, 5, method="triangle", nchains=2, seed=5, chain0=3, burn=2, want=("beta",))
     assert np.array_equal(tri["beta"][3:], t2["beta"])
+
+
+def test_wide_design_builds_svd_factors_on_demand():
+    """P > N: the model skips the P x P eigen-decomposition until the rotated sweep (or the factors) need it; the
+    stable sampler runs without it, and the factors that then appear are the SVD of X."""
+    import bayesbridge_b200 as bb
+    from bayesbridge_b200._lib import ST_ALL
+    X, y, _ = small_problem(40, 60, seed=21)
+    model = bb.Model(X, y)
+    fast_ms = model.L.bb_model_precompute_ms(model.h) if hasattr(model, "L") else None
+    hyp = bb.make_hyper(alpha=0.5)
+    stb = model.chains("stable", 4, seed=5)
+    stb.run(hyp, 50, 0, ST_ALL, pre_tau=1)
+    s = stb.get()
+    assert not s["status"].any() and np.isfinite(s["beta"]).all()
+    tri = model.chains("triangle", 4, seed=5)                  # triggers the factorisation
+    tri.run(hyp, 50, 0, ST_ALL, pre_tau=1)
+    t = tri.get()
+    assert not t["status"].any() and np.isfinite(t["beta"]).all()
+    f = model.factors()
+    sv = np.linalg.svd(X, compute_uv=False)
+    assert rel_err(f["d"][:40], sv) < 1e-6 and not f["d"][40:].any() and not np.abs(f["bhat"]).any()
+    if fast_ms is not None:
+        assert model.L.bb_model_precompute_ms(model.h) >= fast_ms
