@@ -14,13 +14,15 @@ except Exception:
     print(f"{name:28s} FAILED: {last[:300]}")
 PY
 }
-timeout 300 python -m pytest tests -m gpu -q -x 2>&1 | tail -5
-run c1_default c1 A=1
-run c1_W1 c1 BB_TRI_W=1
 run c3_default c3 A=1
 run c3_W8 c3 BB_TRI_W=8
+run c3_W8_NG1 c3 BB_TRI_W=8 BB_TRI_NG=1
+run c3_C1_NG2 c3 BB_TRI_C=1 BB_TRI_NG=2
+run c3_W2_NG4 c3 BB_TRI_W=2 BB_TRI_NG=4
+run c3_W2_C1_NG4 c3 BB_TRI_W=2 BB_TRI_C=1 BB_TRI_NG=4
 run c5_default c5 A=1
 run c5_W4 c5 BB_TRI_W=4
-run c5_C1 c5 BB_TRI_C=1 BB_TRI_NG=2
-run c5_C1_NG1 c5 BB_TRI_C=1 BB_TRI_NG=1
+run c5_W2 c5 BB_TRI_W=2
+run c5_C1_NG2 c5 BB_TRI_C=1 BB_TRI_NG=2
 run c5_C1_NG1_W8 c5 BB_TRI_C=1 BB_TRI_NG=1 BB_TRI_W=8
+run c5_C2_NG1_W8 c5 BB_TRI_C=2 BB_TRI_NG=1 BB_TRI_W=8
