@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <string>
@@ -123,6 +124,57 @@ void model_factor(bb_model* m, double* W, int M, bool w_is_gram) {
   else launched(bb::vz_device(m->Vc, m->zc, P, m->ldv, m->bhat, st));
   BB_CUDA_CHECK(cudaStreamSynchronize(st));
   dfree(V); dfree(nrm); dfree(d_perm);
+}
+
+// Tall designs (N >= 4 P): the factors from the Cholesky factor of the Gram matrix instead of from X itself.
+// X = Q L' with L = chol(X'X), so the right singular vectors of X are the LEFT singular vectors of L and the singular
+// values coincide: one-sided Jacobi on the P x P matrix L (Veselic-Hari: rotating the columns of the Cholesky factor
+// converges in fewer sweeps than rotating X, and no V is accumulated -- the converged columns, normalised, ARE the
+// vectors).  Each round touches 8 P^2 bytes instead of 8 (N + P) P: 11x less at c3, 390x less at c5.
+// Forming X'X squares the condition number, so the result is accepted only when the factorisation succeeds and the
+// singular values it delivers span less than 1e3 (relative error of d about kappa^2 eps <= 1e-10); otherwise the
+// caller falls back to the rotation of X.  BB_SVD_DIRECT=1 forces the fall-back.
+bool model_factor_chol(bb_model* m) {
+  const int P = m->P; cudaStream_t st = m->stream;
+  const char* env = std::getenv("BB_SVD_DIRECT");
+  if (env && env[0] == '1') return false;
+  double* W = dalloc<double>((size_t)P * P);
+  double* Winv = dalloc<double>(64 * 64);
+  uint32_t* d_status = dalloc<uint32_t>(1);
+  double* nrm = dalloc<double>(P);
+  int* d_perm = dalloc<int>(P);
+  bool ok = false;
+  BB_CUDA_CHECK(cudaMemcpyAsync(W, m->XX, (size_t)P * P * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  BB_CUDA_CHECK(cudaMemsetAsync(d_status, 0, sizeof(uint32_t), st));
+  launched(bb::chol_lower_device(W, P, Winv, d_status, st));
+  uint32_t status = 0;
+  BB_CUDA_CHECK(cudaMemcpyAsync(&status, d_status, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+  BB_CUDA_CHECK(cudaStreamSynchronize(st));
+  if (status == 0) {
+    launched(bb::zero_upper_device(W, P, st));
+    launched(bb::jacobi_device(W, nullptr, P, P, st));
+    launched(bb::colnorm_device(W, P, P, nrm, st));
+    std::vector<double> h(P);
+    BB_CUDA_CHECK(cudaMemcpyAsync(h.data(), nrm, P * sizeof(double), cudaMemcpyDeviceToHost, st));
+    BB_CUDA_CHECK(cudaStreamSynchronize(st));
+    double dmax = 0, dmin = 1e300;
+    bool finite = true;
+    for (int i = 0; i < P; ++i) { finite = finite && std::isfinite(h[i]); dmax = std::max(dmax, h[i]); dmin = std::min(dmin, h[i]); }
+    if (finite && dmin > 1e-3 * dmax) {
+      std::vector<int> perm(P);
+      for (int i = 0; i < P; ++i) perm[i] = i;
+      std::stable_sort(perm.begin(), perm.end(), [&](int x, int y) { return h[x] > h[y]; });
+      launched(bb::colscale_device(W, P, P, nrm, st));
+      BB_CUDA_CHECK(cudaMemcpyAsync(d_perm, perm.data(), P * sizeof(int), cudaMemcpyHostToDevice, st));
+      launched(bb::derive_device(W, d_perm, nrm, m->Xy, P, m->ldv, m->tV, m->Vc, m->VQ, m->d, m->a, m->mean, m->d2, m->zc, st));
+      m->singular = false;
+      launched(bb::vz_device(m->Vc, m->zc, P, m->ldv, m->bhat, st));   // least squares: V (a / d^2)
+      BB_CUDA_CHECK(cudaStreamSynchronize(st));
+      ok = true;
+    }
+  }
+  dfree(W); dfree(Winv); dfree(d_status); dfree(nrm); dfree(d_perm);
+  return ok;
 }
 
 bb_model* model_new(int N, int P, int device) {
@@ -379,7 +431,9 @@ bb_model* bb_model_create(const double* X, const double* y, int N, int P, int de
     model_take_rows(m, X, y, mem);
     model_gram(m);
     // SVD factors by one-sided Jacobi: on a copy of X when N >= P (most accurate), else on X'X
-    if (N >= P) {
+    if (N >= 4 * (long long)P && model_factor_chol(m)) {
+      model_finish(m, true);
+    } else if (N >= P) {
       double* W = dalloc<double>((size_t)N * P);
       BB_CUDA_CHECK(cudaMemcpyAsync(W, m->X, (size_t)N * P * sizeof(double), cudaMemcpyDeviceToDevice, m->stream));
       model_factor(m, W, N, false);
@@ -438,10 +492,13 @@ bb_model* bb_model_create_gram(const double* G_dev, int N, int P, int device) {
     double* d_yy = dalloc<double>(1);
     launched(bb::gram_unpack(G_dev, P, m->XX, m->Xy, d_yy, m->stream));
     BB_CUDA_CHECK(cudaMemcpyAsync(&m->yy, d_yy, sizeof(double), cudaMemcpyDeviceToHost, m->stream));
-    double* W = dalloc<double>((size_t)P * P);
-    BB_CUDA_CHECK(cudaMemcpyAsync(W, m->XX, (size_t)P * P * sizeof(double), cudaMemcpyDeviceToDevice, m->stream));
-    model_factor(m, W, P, true);
-    dfree(W); dfree(d_yy);
+    if (!(N >= 4 * (long long)P && model_factor_chol(m))) {
+      double* W = dalloc<double>((size_t)P * P);
+      BB_CUDA_CHECK(cudaMemcpyAsync(W, m->XX, (size_t)P * P * sizeof(double), cudaMemcpyDeviceToDevice, m->stream));
+      model_factor(m, W, P, true);
+      dfree(W);
+    }
+    dfree(d_yy);
     model_finish(m, false);
     // without the rows: r0 from the normal equations (replaced by bb_model_set_r0 after the shard all-reduce)
     BB_CUDA_CHECK(cudaStreamSynchronize(m->stream));

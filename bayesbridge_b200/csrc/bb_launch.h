@@ -81,6 +81,7 @@ int launch_ortho(const OrthoLaunch& L, bool stable, cudaStream_t st);      // bb
 // one iteration of the large-P stable sweep (P > 128); `store_slot` < 0: no draw is stored
 int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st);   // bb_stb_large.cu
 void stb_large_prepare(int P);                                             // opt-in shared memory sizes, once per P
+int chol_lower_device(double* A, int P, double* Winv, uint32_t* status, cudaStream_t st);   // one matrix, lower factor in place
 
 // ---- one-time precompute (bb_pre.cu) ----
 int gram_device(const double* X, const double* y, int N, int P, double* G, cudaStream_t st);   // G = [X y]'[X y]
@@ -88,6 +89,8 @@ int gram_unpack(const double* G, int P, double* XX, double* Xy, double* yy_dev, 
 int jacobi_device(double* W, double* V, int M, int P, cudaStream_t st);
 double resid_device(const double* X, const double* y, const double* b, int N, int P, cudaStream_t st, int* launches);
 int colnorm_device(const double* W, int M, int P, double* nrm, cudaStream_t st);
+int zero_upper_device(double* A, int P, cudaStream_t st);
+int colscale_device(double* W, int M, int P, const double* nrm, cudaStream_t st);
 int derive_device(const double* V, const int* perm, const double* dsrc, const double* Xy, int P, int ldv, double* tV, double* Vc,
                   double* VQ, double* d, double* a, double* mean, double* d2, double* zc, cudaStream_t st);
 int derive_from_tv_device(const double* tV, const double* d, const double* a, int P, int ldv, double* Vc, double* VQ, double* mean,

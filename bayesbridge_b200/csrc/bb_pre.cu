@@ -63,7 +63,7 @@ int jacobi_device(double* W, double* V, int M, int P, cudaStream_t st) {
   int* d_sched = dalloc<int>(sched.size());
   BB_CUDA_CHECK(cudaMemcpyAsync(d_sched, sched.data(), sched.size() * sizeof(int), cudaMemcpyHostToDevice, st));
   unsigned long long* d_conv = dalloc<unsigned long long>(1);
-  set_identity_kernel<<<296, 256, 0, st>>>(V, P); check_launch(); ++n;
+  if (V) { set_identity_kernel<<<296, 256, 0, st>>>(V, P); check_launch(); ++n; }
   // one cooperative launch when every pair's CTA can be resident at once (always, up to P ~ 2000)
   constexpr int MAX_SWEEPS = 40;
   int dev = 0, nsm = 0, per_sm = 0, coop = 0;
@@ -111,6 +111,14 @@ double resid_device(const double* X, const double* y, const double* b, int N, in
   return s;
 }
 
+int zero_upper_device(double* A, int P, cudaStream_t st) {
+  zero_upper_kernel<<<296, 256, 0, st>>>(A, P); check_launch();
+  return 1;
+}
+int colscale_device(double* W, int M, int P, const double* nrm, cudaStream_t st) {
+  colscale_kernel<<<P, 128, 0, st>>>(W, M, P, nrm); check_launch();
+  return 1;
+}
 int colnorm_device(const double* W, int M, int P, double* nrm, cudaStream_t st) {
   colnorm_kernel<<<P, 128, 0, st>>>(W, M, P, nrm); check_launch();
   return 1;

@@ -141,6 +141,7 @@ __global__ void __launch_bounds__(256) jacobi_round_kernel(double* __restrict__ 
   const double c = cs[0], s = cs[1];
   if (s == 0.0) return;
   for (int k = tid; k < M; k += 256) { const double a = wp[k], b = wq[k]; wp[k] = c * a - s * b; wq[k] = s * a + c * b; }
+  if (V == nullptr) return;   // Cholesky-preconditioned form: the singular vectors are the columns of W themselves
   double* vp = V + (size_t)p * P; double* vq = V + (size_t)q * P;
   for (int k = tid; k < P; k += 256) { const double a = vp[k], b = vq[k]; vp[k] = c * a - s * b; vq[k] = s * a + c * b; }
 }
@@ -174,8 +175,10 @@ __device__ __forceinline__ void jacobi_rotate_pair(double* __restrict__ W, doubl
   const double c = cs[0], s = cs[1];
   if (s != 0.0) {
     for (int k = tid; k < M; k += 256) { const double a = __ldcg(wp + k), b = __ldcg(wq + k); wp[k] = c * a - s * b; wq[k] = s * a + c * b; }
-    double* vp = V + (size_t)p * P; double* vq = V + (size_t)q * P;
-    for (int k = tid; k < P; k += 256) { const double a = __ldcg(vp + k), b = __ldcg(vq + k); vp[k] = c * a - s * b; vq[k] = s * a + c * b; }
+    if (V != nullptr) {
+      double* vp = V + (size_t)p * P; double* vq = V + (size_t)q * P;
+      for (int k = tid; k < P; k += 256) { const double a = __ldcg(vp + k), b = __ldcg(vq + k); vp[k] = c * a - s * b; vq[k] = s * a + c * b; }
+    }
   }
   __syncthreads();
 }
@@ -216,6 +219,19 @@ __global__ void __launch_bounds__(256) jacobi_persistent_kernel(double* __restri
 __global__ void set_identity_kernel(double* V, int P) {
   for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < (size_t)P * P; e += (size_t)gridDim.x * blockDim.x)
     V[e] = (e % P == e / P) ? 1.0 : 0.0;
+}
+
+// strict upper triangle of a P x P column-major matrix := 0 (the Cholesky kernels leave the input there)
+__global__ void zero_upper_kernel(double* A, int P) {
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < (size_t)P * P; e += (size_t)gridDim.x * blockDim.x)
+    if ((int)(e % P) < (int)(e / P)) A[e] = 0.0;
+}
+// w_i /= nrm_i (columns with nrm_i == 0 are left alone)
+__global__ void colscale_kernel(double* W, int M, int P, const double* __restrict__ nrm) {
+  const int i = blockIdx.x; if (i >= P) return;
+  const double s = nrm[i]; if (!(s > 0.0)) return;
+  const double r = 1.0 / s;
+  for (int k = threadIdx.x; k < M; k += blockDim.x) W[(size_t)i * M + k] *= r;
 }
 
 // column norms of W (M x P): nrm[i] = ||w_i||

@@ -41,4 +41,22 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
   return n;
 }
 
+// Cholesky of ONE P x P matrix with the same kernels (a batch of one chain): on return the lower triangle of A
+// holds L (A = L L'), the strict upper triangle still holds the input.  Winv: 64 x 64 scratch, status: one word,
+// ST_CHOL_FAIL is set when a pivot is not positive.  Used by the Cholesky-preconditioned SVD of the constructor.
+int chol_lower_device(double* A, int P, double* Winv, uint32_t* status, cudaStream_t st) {
+  stb_large_prepare(P);
+  const size_t smem_sy = (size_t)2 * SL_NB * SL_LD * sizeof(double);
+  const int nblk = (P + SL_NB - 1) / SL_NB;
+  int n = 0;
+  for (int kb = 0; kb < nblk; ++kb) {
+    if (kb > 0) { stbl_update_kernel<<<dim3(nblk - kb, 1), 256, smem_sy, st>>>(A, P, kb); ++n; }
+    stbl_potrf_kernel<<<1, SL_T, (size_t)2 * SL_NB * (SL_NB + 1) * sizeof(double), st>>>(A, Winv, P, kb, status); ++n;
+    const int rem = nblk - kb - 1;
+    if (rem > 0) { stbl_trsm_kernel<<<dim3(rem, 1), 256, smem_sy, st>>>(A, Winv, P, kb); ++n; }
+  }
+  BB_CUDA_CHECK(cudaGetLastError());
+  return n;
+}
+
 }  // namespace bb
