@@ -687,9 +687,42 @@ void run_driver(int method, int ortho, const double* X, const double* y, int N, 
   lap("model (upload+factors)");
   g.c = bb_chains_create(g.m, method, ortho, nchains, seed, chain0);
   if (!g.c) throw std::string(g_err);
-  int mask = BB_OUT_BETA | BB_OUT_SIG2 | BB_OUT_TAU | BB_OUT_ALPHA;
-  mask |= (method == BB_TRI) ? (BB_OUT_U | BB_OUT_OMEGA | BB_OUT_SHAPE) : BB_OUT_LAMBDA;
+  // only the outputs the caller asked for are stored by the kernels (8 P bytes per chain-iteration each)
+  struct Out { int which; double* host; const double* dev; int w; };
+  Out outs[8] = {{BB_OUT_BETA, beta, nullptr, P},
+                 {method == BB_TRI ? BB_OUT_U : BB_OUT_LAMBDA, aux1, nullptr, P},
+                 {BB_OUT_OMEGA, method == BB_TRI ? aux2 : nullptr, nullptr, P},
+                 {BB_OUT_SHAPE, method == BB_TRI ? aux3 : nullptr, nullptr, P},
+                 {BB_OUT_SIG2, sig2, nullptr, 1}, {BB_OUT_TAU, tau, nullptr, 1}, {BB_OUT_ALPHA, alpha, nullptr, 1}, {0, nullptr, nullptr, 0}};
+  int mask = 0;
+  for (const Out& o : outs) if (o.host) mask |= o.which;
+  if (mask == 0) mask = BB_OUT_BETA;
   if (bb_chains_reserve(g.c, nsamp, mask)) throw std::string(g_err);
+  for (Out& o : outs) {
+    switch (o.host ? o.which : 0) {
+      case BB_OUT_BETA: o.dev = g.c->o_beta; break;
+      case BB_OUT_U: o.dev = g.c->o_u; break;
+      case BB_OUT_OMEGA: o.dev = g.c->o_omega; break;
+      case BB_OUT_SHAPE: o.dev = g.c->o_shape; break;
+      case BB_OUT_LAMBDA: o.dev = g.c->o_lambda; break;
+      case BB_OUT_SIG2: o.dev = g.c->o_sig2; break;
+      case BB_OUT_TAU: o.dev = g.c->o_tau; break;
+      case BB_OUT_ALPHA: o.dev = g.c->o_alpha; break;
+      default: break;
+    }
+  }
+  // The draws of a finished chunk go to the host on a copy stream while the next chunk is sampled: the host array has
+  // the layout of the draw buffer, [chain][sample][w], so a slot range is one strided (2-D) copy per output.
+  struct CopyStream { cudaStream_t s = nullptr; ~CopyStream() { if (s) cudaStreamDestroy(s); } } cps;
+  BB_CUDA_CHECK(cudaStreamCreateWithFlags(&cps.s, cudaStreamNonBlocking));
+  auto download = [&](long long s0, long long ns) {
+    for (const Out& o : outs) {
+      if (!o.dev || ns <= 0) continue;
+      const size_t pitch = (size_t)nsamp * o.w * sizeof(double), off = (size_t)s0 * o.w;
+      BB_CUDA_CHECK(cudaMemcpy2DAsync(o.host + off, pitch, o.dev + off, pitch, (size_t)ns * o.w * sizeof(double), (size_t)nchains,
+                                      cudaMemcpyDeviceToHost, cps.s));
+    }
+  };
   lap("chains + draw buffer");
   if (g_verbose) {
     std::printf("Bridge Regression (%s):", method == BB_TRI ? "mix. of triangles" : "mix. of normals");
@@ -709,7 +742,9 @@ void run_driver(int method, int ortho, const double* X, const double* y, int N, 
   auto t0 = std::chrono::steady_clock::now();
   const long long total = (long long)(nsamp - 1) * thin;
   long long done = 0;
-  const long long chunk = 8192LL * thin;
+  // chunks: at most 8192 stored iterations between two polls, and about four chunks per call so that the download overlaps
+  const long long chunk = std::min(8192LL, std::max(16LL, (total / thin + 3) / 4)) * thin;
+  long long copied = 0;   // slots [0, copied) are on their way to the host
   // the sampling loop of the non-orthogonal stable driver hands (alpha_b, alpha_b) to the alpha step
   // (BridgeWrapper.cpp:294; its burn-in :272 and the other three drivers pass (alpha_a, alpha_b)): kept as written
   bb_hyper hs = *h;
@@ -718,15 +753,14 @@ void run_driver(int method, int ortho, const double* X, const double* y, int N, 
     const long long n = std::min(chunk, total - done);
     chains_run(g.c, &hs, (unsigned)(nburn + done), (int)n, BB_ST_ALL, 0, 0, thin, 1 + done / thin, nullptr);
     done += n;
+    const long long have = 1 + done / thin;
+    download(copied, have - copied); copied = have;
   }
+  download(copied, nsamp - copied);
   const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   if (runtime) *runtime = secs;
   lap("sampling loop");
-  auto fetch = [&](int which, double* out) { if (out && bb_chains_fetch(g.c, which, 0, nsamp, out)) throw std::string(g_err); };
-  fetch(BB_OUT_BETA, beta);
-  if (method == BB_TRI) { fetch(BB_OUT_U, aux1); fetch(BB_OUT_OMEGA, aux2); fetch(BB_OUT_SHAPE, aux3); }
-  else fetch(BB_OUT_LAMBDA, aux1);
-  fetch(BB_OUT_SIG2, sig2); fetch(BB_OUT_TAU, tau); fetch(BB_OUT_ALPHA, alpha);
+  BB_CUDA_CHECK(cudaStreamSynchronize(cps.s));
   if (status && bb_chains_get(g.c, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, status)) throw std::string(g_err);
   lap("download");
   if (g_verbose) std::printf("Sampling complete: %g sec. for %i iterations.\n", secs, nsamp);
