@@ -426,13 +426,26 @@ bb_model* bb_model_create(const double* X, const double* y, int N, int P, int de
   bb_model* m = nullptr;
   const int rc = guarded([&] {
     auto t0 = std::chrono::steady_clock::now();
+    auto tp = t0;
+    auto lap = [&](const char* what) {
+      if (g_verbose < 2) return;
+      cudaStreamSynchronize(m->stream);
+      auto n = std::chrono::steady_clock::now();
+      std::printf("  [model]  %-22s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(n - tp).count()); tp = n;
+    };
     m = model_new(N, P, device);
     if (!m) throw std::string(g_err);
+    lap("alloc");
     model_take_rows(m, X, y, mem);
+    lap("upload X, y");
     model_gram(m);
-    // SVD factors by one-sided Jacobi: on a copy of X when N >= P (most accurate), else on X'X
+    lap("Gram");
+    // SVD factors by one-sided Jacobi: on the Cholesky factor of X'X for tall well-conditioned designs, on a copy of X
+    // when N >= P otherwise (most accurate), else on X'X
     if (N >= 4 * (long long)P && model_factor_chol(m)) {
+      lap("Cholesky + Jacobi");
       model_finish(m, true);
+      lap("centres, residuals");
     } else if (N >= P) {
       double* W = dalloc<double>((size_t)N * P);
       BB_CUDA_CHECK(cudaMemcpyAsync(W, m->X, (size_t)N * P * sizeof(double), cudaMemcpyDeviceToDevice, m->stream));

@@ -1,6 +1,8 @@
 // bb_pre.cu -- host side of the one-time precompute kernels (bb_pre.cuh): Gram build, one-sided
 // Jacobi SVD, derived layouts (the role of the BridgeRegression constructor, BridgeRegression.cpp:13-69).
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 #include <vector>
 #include "bb_pre.cuh"
 
@@ -54,11 +56,67 @@ std::vector<int> tournament(int P, int& rounds, int& npairs) {
   }
   return out;
 }
+// the same tournament over column blocks of 8: pairs (I, J) with J = -1 for the padding block (the CTA then only
+// rotates within block I)
+std::vector<int> block_tournament(int P, int& rounds, int& npairs) {
+  const int nb = (P + BJ_B - 1) / BJ_B;
+  const int n = std::max(2, nb + (nb & 1));
+  rounds = n - 1; npairs = n / 2;
+  std::vector<int> out((size_t)rounds * npairs * 2);
+  std::vector<int> ring(n);
+  for (int i = 0; i < n; ++i) ring[i] = i;
+  for (int r = 0; r < rounds; ++r) {
+    for (int k = 0; k < npairs; ++k) {
+      int p = ring[k], q = ring[n - 1 - k];
+      if (p > q) std::swap(p, q);
+      if (q >= nb) q = -1;
+      if (p >= nb) p = -1;
+      out[((size_t)r * npairs + k) * 2] = p; out[((size_t)r * npairs + k) * 2 + 1] = q;
+    }
+    int last = ring[n - 1];
+    for (int i = n - 1; i > 1; --i) ring[i] = ring[i - 1];
+    ring[1] = last;
+  }
+  return out;
+}
 }  // namespace
 
 // One-sided Jacobi on W (M x P, destroyed): on return W = W0 V, V orthogonal, columns of W orthogonal.
 int jacobi_device(double* W, double* V, int M, int P, cudaStream_t st) {
   int rounds, npairs, n = 0;
+  // block form (one cooperative launch, 8-column blocks) unless BB_JACOBI_PAIRWISE=1 or the device cannot co-launch
+  {
+    const char* env = std::getenv("BB_JACOBI_PAIRWISE");
+    int dev = 0, nsm = 0, per_sm = 0, coop = 0;
+    BB_CUDA_CHECK(cudaGetDevice(&dev));
+    BB_CUDA_CHECK(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));
+    BB_CUDA_CHECK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+    BB_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, jacobi_block_kernel, 256, 0));
+    std::vector<int> bs = block_tournament(P, rounds, npairs);
+    if (!(env && env[0] == '1') && coop && npairs <= nsm * per_sm) {
+      constexpr int MAX_SWEEPS = 40;
+      int* d_sched = dalloc<int>(bs.size());
+      BB_CUDA_CHECK(cudaMemcpyAsync(d_sched, bs.data(), bs.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+      if (V) { set_identity_kernel<<<296, 256, 0, st>>>(V, P); check_launch(); ++n; }
+      unsigned long long* d_convs = dalloc<unsigned long long>(MAX_SWEEPS);
+      unsigned int* d_counter = dalloc<unsigned int>(1);
+      BB_CUDA_CHECK(cudaMemsetAsync(d_convs, 0, MAX_SWEEPS * sizeof(unsigned long long), st));
+      BB_CUDA_CHECK(cudaMemsetAsync(d_counter, 0, sizeof(unsigned int), st));
+      int max_sweeps = MAX_SWEEPS;
+      void* args[] = {&W, &V, &M, &P, &d_sched, &rounds, &npairs, &d_convs, &d_counter, &max_sweeps};
+      BB_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)jacobi_block_kernel, dim3(npairs), dim3(256), args, 0, st));
+      ++n;
+      BB_CUDA_CHECK(cudaStreamSynchronize(st));
+      if (std::getenv("BB_JACOBI_VERBOSE")) {
+        unsigned long long hc[MAX_SWEEPS];
+        BB_CUDA_CHECK(cudaMemcpy(hc, d_convs, sizeof(hc), cudaMemcpyDeviceToHost));
+        int ns = 0; while (ns < MAX_SWEEPS && hc[ns] != 0ull) ++ns;
+        std::printf("  [jacobi] block form: M %d P %d, %d rounds x %d pairs, %d sweeps rotated\n", M, P, rounds, npairs, ns);
+      }
+      dfree(d_sched); dfree(d_convs); dfree(d_counter);
+      return n;
+    }
+  }
   std::vector<int> sched = tournament(P, rounds, npairs);
   int* d_sched = dalloc<int>(sched.size());
   BB_CUDA_CHECK(cudaMemcpyAsync(d_sched, sched.data(), sched.size() * sizeof(int), cudaMemcpyHostToDevice, st));

@@ -8,6 +8,7 @@
 //   resid_kernel     || y - X b ||^2 for the rss expansions
 #pragma once
 #include "bb_launch.h"
+#include "bb_math.cuh"
 
 namespace bb {
 
@@ -210,6 +211,218 @@ __global__ void __launch_bounds__(256) jacobi_persistent_kernel(double* __restri
     for (int r = 0; r < rounds; ++r) {
       const int p = sched[((size_t)r * npairs + blockIdx.x) * 2], q = sched[((size_t)r * npairs + blockIdx.x) * 2 + 1];
       if (p >= 0 && q >= 0 && p < P && q < P) jacobi_rotate_pair(W, V, M, P, p, q, conv + sweep, red, cs);
+      grid_barrier(counter, epoch);
+    }
+    if (*((volatile unsigned long long*)(conv + sweep)) == 0ull) break;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Block one-sided Jacobi.  A CTA owns a PAIR OF COLUMN BLOCKS (8 + 8 columns) per round instead of a pair of columns:
+//   1. G = B'B of its 16 columns on the FP64 tensor cores (DMMA m8n8k4, the A fragment of a column block is also its
+//      B fragment; warps split the rows, fixed-order reduction through shared memory);
+//   2. one cyclic sweep of two-sided rotations on the 16 x 16 matrix G in shared memory (15 inner rounds of 8 disjoint
+//      pairs, thread (i,j) owns G(i,j) and the accumulated rotation J(i,j));
+//   3. B <- B J (and V <- V J when V is wanted), again as DMMA tile products, in place.
+// A sweep is P/8 - 1 rounds instead of P - 1, and every round moves the same bytes as a round of the pairwise form:
+// 8x fewer grid barriers and 8x less L2 traffic per sweep.  conv[s] = largest |cos| between two columns met in sweep s
+// when it exceeds 1e-14 (the stop test); rotations are applied down to 1e-15.
+// ------------------------------------------------------------------------------------------
+constexpr int BJ_B = 8;
+constexpr int BJ_N = 2 * BJ_B;
+
+struct BjSmem {
+  double part[8][3][64];
+  double G[2][BJ_N][BJ_N + 1];     // ping-pong: an inner round reads one copy and writes the other (one barrier per round)
+  double Jm[2][BJ_N][BJ_N + 1];
+  double red[8];
+  unsigned char partner[BJ_N - 1][BJ_N];   // inner round r: the column rotated against column i
+  int rotate;
+};
+
+__device__ __forceinline__ void bj_inner_schedule(BjSmem& sm) {
+  if (threadIdx.x == 0) {
+    int ring[BJ_N];
+    for (int i = 0; i < BJ_N; ++i) ring[i] = i;
+    for (int r = 0; r < BJ_N - 1; ++r) {
+      for (int k = 0; k < BJ_B; ++k) {
+        int p = ring[k], q = ring[BJ_N - 1 - k];
+        if (p > q) { const int t = p; p = q; q = t; }
+        sm.partner[r][p] = (unsigned char)q; sm.partner[r][q] = (unsigned char)p;
+      }
+      const int last = ring[BJ_N - 1];
+      for (int i = BJ_N - 1; i > 1; --i) ring[i] = ring[i - 1];
+      ring[1] = last;
+    }
+  }
+  __syncthreads();
+}
+
+// T <- T Jm for the 16 columns {8 I .., 8 J ..} of T (rows x ., leading dimension ld), 8-row tiles split over the warps
+__device__ __forceinline__ void bj_apply(double* __restrict__ T, int rows, int ld, int P, int I, int J, const BjSmem& sm) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  double bf[2][4];
+#pragma unroll
+  for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+    for (int kq = 0; kq < 4; ++kq) bf[nt][kq] = sm.Jm[(BJ_N - 1) & 1][4 * kq + (lane & 3)][8 * nt + (lane >> 2)];
+  // columns this lane loads (k index 4 kq + lane%4) and stores (n index 8 nt + 2 (lane%4) + e)
+  size_t lo[4]; bool lv[4];
+#pragma unroll
+  for (int kq = 0; kq < 4; ++kq) {
+    const int k = 4 * kq + (lane & 3);
+    const int col = k < BJ_B ? I * BJ_B + k : (J < 0 ? P : J * BJ_B + k - BJ_B);
+    lv[kq] = col < P; lo[kq] = (size_t)(lv[kq] ? col : 0) * ld;
+  }
+  size_t so[2][2]; bool sv[2][2];
+#pragma unroll
+  for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int n = 8 * nt + 2 * (lane & 3) + e;
+      const int col = n < BJ_B ? I * BJ_B + n : (J < 0 ? P : J * BJ_B + n - BJ_B);
+      sv[nt][e] = col < P; so[nt][e] = (size_t)(sv[nt][e] ? col : 0) * ld;
+    }
+  constexpr int U = 4;   // row tiles in flight per warp
+  for (int r0 = 8 * warp; r0 < rows; r0 += 64 * U) {
+    double a[U][4];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int r = r0 + 64 * u + (lane >> 2);
+#pragma unroll
+      for (int kq = 0; kq < 4; ++kq) a[u][kq] = (r < rows && lv[kq]) ? __ldcg(T + lo[kq] + r) : 0.0;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (r0 + 64 * u >= rows) break;          // warp-uniform
+      double acc[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+#pragma unroll
+      for (int kq = 0; kq < 4; ++kq) {         // mma.sync: every lane has read its inputs of this tile before any lane overwrites them
+        dmma_m8n8k4(acc[0][0], acc[0][1], a[u][kq], bf[0][kq]);
+        dmma_m8n8k4(acc[1][0], acc[1][1], a[u][kq], bf[1][kq]);
+      }
+      const int r = r0 + 64 * u + (lane >> 2);
+      if (r < rows) {
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+          for (int e = 0; e < 2; ++e) if (sv[nt][e]) T[so[nt][e] + r] = acc[nt][e];
+      }
+    }
+  }
+}
+
+// Jacobi rotation of a symmetric 2 x 2 block (al ga; ga be): (c, s) with new p = c p - s q, new q = s p + c q orthogonal.
+// Straight-line (bb_math.cuh): t = sgn(be - al) 2 ga / (|be - al| + sqrt((be - al)^2 + 4 ga^2)), c = 1/sqrt(1 + t^2).
+// No rotation when |ga| <= 1e-15 sqrt(al be).
+__device__ __forceinline__ void bj_rot(double al, double be, double ga, double& c, double& s) {
+  const double g2 = ga * ga;
+  const bool go = g2 > 1e-30 * al * be;
+  const double dl = be - al;
+  const double hh = go ? fma(dl, dl, 4.0 * g2) : 1.0;
+  const double t = (dl >= 0.0 ? 2.0 : -2.0) * ga * x_rcp(fabs(dl) + x_sqrt(hh));
+  const double cc = x_rsqrt(fma(t, t, 1.0));
+  c = go ? cc : 1.0; s = go ? cc * t : 0.0;
+}
+
+__device__ __forceinline__ void bj_block_pair(double* __restrict__ W, double* __restrict__ V, int M, int P, int I, int J,
+                                              unsigned long long* conv, BjSmem& sm) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  // ---- 1. G = B'B ----
+  {
+    const int cA = I * BJ_B + (lane >> 2), cB = J < 0 ? P : J * BJ_B + (lane >> 2);
+    const bool vA = cA < P, vB = cB < P;
+    const double* pA = W + (size_t)(vA ? cA : 0) * M;
+    const double* pB = W + (size_t)(vB ? cB : 0) * M;
+    double g[3][2] = {{0.0, 0.0}, {0.0, 0.0}, {0.0, 0.0}};
+#pragma unroll 8
+    for (int k0 = 4 * warp; k0 < M; k0 += 32) {
+      const int k = k0 + (lane & 3);
+      const double a = (vA && k < M) ? __ldcg(pA + k) : 0.0;
+      const double b = (vB && k < M) ? __ldcg(pB + k) : 0.0;
+      dmma_m8n8k4(g[0][0], g[0][1], a, a);
+      dmma_m8n8k4(g[1][0], g[1][1], a, b);
+      dmma_m8n8k4(g[2][0], g[2][1], b, b);
+    }
+    const int e = (lane >> 2) * 8 + 2 * (lane & 3);
+#pragma unroll
+    for (int t = 0; t < 3; ++t) { sm.part[warp][t][e] = g[t][0]; sm.part[warp][t][e + 1] = g[t][1]; }
+  }
+  __syncthreads();
+  const int i = tid >> 4, j = tid & 15;
+  const int lo_ = i < j ? i : j, hi_ = i < j ? j : i;     // both triangles read the same element: G is exactly symmetric
+  {
+    int t, e;
+    if (hi_ < BJ_B) { t = 0; e = lo_ * 8 + hi_; }
+    else if (lo_ >= BJ_B) { t = 2; e = (lo_ - BJ_B) * 8 + (hi_ - BJ_B); }
+    else { t = 1; e = lo_ * 8 + (hi_ - BJ_B); }
+    double sum = 0.0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) sum += sm.part[w][t][e];
+    sm.G[0][i][j] = sum;
+    sm.Jm[0][i][j] = i == j ? 1.0 : 0.0;
+  }
+  __syncthreads();
+  // ---- largest |cos| among the 120 column pairs of this CTA ----
+  {
+    double rel = 0.0;
+    if (i < j) {
+      const double den = sqrt(sm.G[0][i][i] * sm.G[0][j][j]);
+      rel = den > 0.0 ? fabs(sm.G[0][i][j]) / den : 0.0;
+    }
+    rel = warp_max(rel);
+    if (lane == 0) sm.red[warp] = rel;
+    __syncthreads();
+    if (tid == 0) {
+      double m = 0.0;
+      for (int w = 0; w < 8; ++w) m = fmax(m, sm.red[w]);
+      sm.rotate = m > 1e-15;
+      if (m > 1e-14) atomicMax(conv, (unsigned long long)__double_as_longlong(m));
+    }
+    __syncthreads();
+  }
+  if (!sm.rotate) return;
+  // ---- 2. one cyclic sweep on G, J accumulates the rotations ----
+  // Thread (i,j) needs the rotations of the pairs holding i and j: it computes both itself from the current copy of G
+  // (two independent straight-line chains) instead of waiting for 8 threads to publish them: ONE barrier per inner round.
+  for (int r = 0; r < BJ_N - 1; ++r) {
+    const double (*G)[BJ_N + 1] = sm.G[r & 1];
+    const double (*Jc)[BJ_N + 1] = sm.Jm[r & 1];
+    const int pl = sm.partner[r][lo_], ph = sm.partner[r][hi_];
+    double cl, sl, ch, sh;
+    {
+      const int p = lo_ < pl ? lo_ : pl, q = lo_ < pl ? pl : lo_;
+      bj_rot(G[p][p], G[q][q], G[p][q], cl, sl);
+      sl = lo_ == p ? -sl : sl;
+    }
+    {
+      const int p = hi_ < ph ? hi_ : ph, q = hi_ < ph ? ph : hi_;
+      bj_rot(G[p][p], G[q][q], G[p][q], ch, sh);
+      sh = hi_ == p ? -sh : sh;
+    }
+    const double gn = cl * ch * G[lo_][hi_] + cl * sh * G[lo_][ph] + sl * ch * G[pl][hi_] + sl * sh * G[pl][ph];
+    const int pj = j == lo_ ? pl : ph;
+    const double cj = j == lo_ ? cl : ch, sj = j == lo_ ? sl : sh;
+    const double jn = cj * Jc[i][j] + sj * Jc[i][pj];
+    sm.G[(r + 1) & 1][i][j] = gn; sm.Jm[(r + 1) & 1][i][j] = jn;
+    __syncthreads();
+  }
+  // ---- 3. B <- B J, V <- V J ----
+  bj_apply(W, M, M, P, I, J, sm);
+  if (V != nullptr) bj_apply(V, P, P, P, I, J, sm);
+}
+
+// The whole block tournament in ONE cooperative launch: CTA b = block pair b of the round, grid barrier between rounds.
+__global__ void __launch_bounds__(256) jacobi_block_kernel(double* __restrict__ W, double* __restrict__ V, int M, int P,
+                                                           const int* __restrict__ sched, int rounds, int npairs,
+                                                           unsigned long long* conv, unsigned int* counter, int max_sweeps) {
+  __shared__ BjSmem sm;
+  bj_inner_schedule(sm);
+  unsigned int epoch = 0;
+  for (int sweep = 0; sweep < max_sweeps; ++sweep) {
+    for (int r = 0; r < rounds; ++r) {
+      const int I = sched[((size_t)r * npairs + blockIdx.x) * 2], J = sched[((size_t)r * npairs + blockIdx.x) * 2 + 1];
+      if (I >= 0) bj_block_pair(W, V, M, P, I, J, conv + sweep, sm);
       grid_barrier(counter, epoch);
     }
     if (*((volatile unsigned long long*)(conv + sweep)) == 0ull) break;
