@@ -276,6 +276,22 @@ class Chains:
         self._ck(self.L.bb_chains_fetch(self.h, _OUT[name], slot0, nslots, out.ctypes.data))
         return out
 
+    def summary(self, name="beta", slot0=0, nslots=None, runtime=None, per_chain=False):
+        """sum.stat (Code/R/PublicBenchmark.R:112-134) of the stored draws, computed on the device: dict of
+        mean, sd, ESS (coda definition, summed over chains), ESS.sec, t, Q.1, Q.9 per coefficient over all chains
+        pooled; with per_chain=True also "chains": [nchains, 5, P] = mean, sd, ESS, Q.1, Q.9 of each chain."""
+        nslots = self.nslots - slot0 if nslots is None else nslots
+        pooled = np.zeros((7, self.P))
+        pc = np.zeros((self.nchains, 5, self.P)) if per_chain else None
+        self._ck(self.L.bb_chains_summary(self.h, _OUT[name], slot0, nslots, float(runtime or 0.0),
+                                          pc.ctypes.data if per_chain else None, pooled.ctypes.data))
+        out = dict(zip(("mean", "sd", "ESS", "ESS.sec", "t", "Q.1", "Q.9"), pooled))
+        if runtime is None:
+            del out["ESS.sec"]
+        if per_chain:
+            out["chains"] = pc
+        return out
+
     # ---- the conditionals of class BridgeRegression, one launch each over all chains ----
     def sample_tau_marg(self, hyper, it):  # BridgeRegression.cpp:453-465
         return self.run(hyper, 1, it, ST_TAU)

@@ -648,6 +648,33 @@ int bb_chains_store_state(bb_chains* c, long long slot) {
   });
 }
 
+int bb_chains_summary(const bb_chains* c, int which, long long slot0, long long nslots, double runtime_sec, double* per_chain,
+                      double* pooled) {
+  return guarded([&] {
+    BB_CUDA_CHECK(cudaSetDevice(c->m->device));
+    const double* src = nullptr;
+    switch (which) {
+      case BB_OUT_BETA: src = c->o_beta; break;
+      case BB_OUT_U: src = c->o_u; break;
+      case BB_OUT_OMEGA: src = c->o_omega; break;
+      case BB_OUT_SHAPE: src = c->o_shape; break;
+      case BB_OUT_LAMBDA: src = c->o_lambda; break;
+      default: break;
+    }
+    if (!src) throw std::string("bb_chains_summary: that output is not a reserved vector output");
+    if (slot0 < 0 || nslots < 2 || slot0 + nslots > c->nslots) throw std::string("bb_chains_summary: slot range out of bounds");
+    if (nslots > 16384) throw std::string("bb_chains_summary: at most 16384 stored draws per chain (thin the run or fetch the draws)");
+    const size_t P = c->m->P, n1 = (size_t)c->nchains * 5 * P, n2 = 7 * P;
+    double* d_pc = dalloc<double>(n1);
+    double* d_po = dalloc<double>(n2);
+    launched(bb::summary_device(src, (int)P, c->nslots, slot0, (int)nslots, c->nchains, runtime_sec, d_pc, d_po, c->stream));
+    if (per_chain) BB_CUDA_CHECK(cudaMemcpyAsync(per_chain, d_pc, n1 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (pooled) BB_CUDA_CHECK(cudaMemcpyAsync(pooled, d_po, n2 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    BB_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    dfree(d_pc); dfree(d_po);
+  });
+}
+
 int bb_chains_fetch(const bb_chains* c, int which, long long slot0, long long nslots, double* out) {
   return guarded([&] {
     BB_CUDA_CHECK(cudaSetDevice(c->m->device));

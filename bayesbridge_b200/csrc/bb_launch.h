@@ -83,6 +83,10 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st); 
 void stb_large_prepare(int P);                                             // opt-in shared memory sizes, once per P
 int chol_lower_device(double* A, int P, double* Winv, uint32_t* status, cudaStream_t st);   // one matrix, lower factor in place
 
+// ---- sum.stat on the device (bb_summary.cu) ----
+int summary_device(const double* draws, int P, long long chain_stride, long long slot0, int n, int nchains, double runtime_sec,
+                   double* per_chain_dev, double* pooled_dev, cudaStream_t st);
+
 // ---- one-time precompute (bb_pre.cu) ----
 int gram_device(const double* X, const double* y, int N, int P, double* G, cudaStream_t st);   // G = [X y]'[X y]
 int gram_unpack(const double* G, int P, double* XX, double* Xy, double* yy_dev, cudaStream_t st);

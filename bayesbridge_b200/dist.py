@@ -100,6 +100,16 @@ def max_over_ranks(x, device=None):
     return float(t.item())
 
 
+def sum_over_ranks(v, device=None):
+    """element-wise sum of a float64 numpy vector over the ranks (the per-coefficient ESS of sharded chains adds up)"""
+    import numpy as np
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return np.asarray(v, dtype=np.float64)
+    t = torch.as_tensor(np.asarray(v, dtype=np.float64), device=device if device is not None else "cpu")
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return t.cpu().numpy()
+
+
 def barrier():
     if dist.is_initialized() and dist.get_world_size() > 1:
         dist.barrier()

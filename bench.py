@@ -38,10 +38,10 @@ UNIT = "coefficient-draws/s"
 WORKLOADS = {
     "c1": dict(desc="bridge.reg.tri n=442 p=64 alpha=0.5, 1 chain", chains=1, iters=2000),
     "c2": dict(desc="bridge.reg.stb n=442 p=64 alpha=0.5, 512 chains/GPU", chains=512, iters=200),
-    "c3": dict(desc="bridge.reg.tri n=10000 p=1000 alpha=0.5, 512 chains/GPU (4096 on 8)", chains=512, iters=4),
-    "c4": dict(desc="bridge.reg.stb n=500 p=2000 alpha=0.25 (p>n), 128 chains/GPU (1024 on 8)", chains=128, iters=1),
-    "c5": dict(desc="bridge.reg.tri n=100000 p=256 alpha=0.5 row-sharded Gram, 256 chains/GPU", chains=256, iters=20),
-    "c5s": dict(desc="bridge.reg.stb n=100000 p=256 alpha=0.5 row-sharded Gram, 256 chains/GPU", chains=256, iters=4),
+    "c3": dict(desc="bridge.reg.tri n=10000 p=1000 alpha=0.5, 512 chains/GPU (4096 on 8)", chains=512, iters=40),
+    "c4": dict(desc="bridge.reg.stb n=500 p=2000 alpha=0.25 (p>n), 128 chains/GPU (1024 on 8)", chains=128, iters=2),
+    "c5": dict(desc="bridge.reg.tri n=100000 p=256 alpha=0.5 row-sharded Gram, 256 chains/GPU", chains=256, iters=100),
+    "c5s": dict(desc="bridge.reg.stb n=100000 p=256 alpha=0.5 row-sharded Gram, 256 chains/GPU", chains=256, iters=20),
 }
 
 
@@ -295,16 +295,26 @@ def run_ours(args):
                 "note": "FP64 path: no bf16/HBM roofline applies; the sweep kernels are issue/latency-bound (sequential Gibbs steps, "
                         "3.5 chains per SM), see profiles/*.md for fp64-pipe utilisation and stall breakdowns"}
 
-    # ---- ESS/sec from the draws of the timed region (coda definition, bayesbridge_b200/ess.py) ----
+    # ---- ESS/sec: sum.stat on the device over EVERY chain and coefficient of the timed region (bb_chains_summary:
+    # coda's effectiveSize per series, summed over chains and ranks); the host estimator cross-checks one chain ----
     ess_info = None
-    if args.ess and rank == 0:
-        draws = chains.fetch(out_name)              # [chain, K*ips, P]
-        nc = min(nch, 8)
-        cols = np.unique(np.linspace(0, P - 1, min(P, 64)).astype(int))
-        e = np.array([[bess.ess_ar(draws[c, :, j]) for j in cols] for c in range(nc)]).mean(0) * total_chains
-        ess_info = {"min": float(e.min() / T), "median": float(np.median(e) / T), "unit": "ESS/s summed over chains",
-                    "estimator": f"coda AR spectral, {nc} chains x {len(cols)} coefficients sampled", "n_per_chain": int(draws.shape[1])}
-        del draws
+    if args.ess:
+        nsl = min(args.steps * ips, 16384)
+        t_s = time.perf_counter()
+        sm = chains.summary(out_name, slot0=0, nslots=nsl)
+        summary_s = time.perf_counter() - t_s
+        e = bdist.sum_over_ranks(sm["ESS"], dev) * (args.steps * ips / nsl)
+        if rank == 0:
+            cols = np.unique(np.linspace(0, P - 1, min(P, 8)).astype(int))
+            d0 = chains.fetch(out_name, 0, nsl)[0] if nch * nsl * P <= (1 << 27) else None
+            check = None
+            if d0 is not None:
+                pc = chains.summary(out_name, slot0=0, nslots=nsl, per_chain=True)["chains"]
+                check = float(max(abs(pc[0, 2, j] / bess.ess_ar(d0[:, j]) - 1.0) for j in cols))
+            ess_info = {"min": float(e.min() / T), "median": float(np.median(e) / T), "unit": "ESS/s summed over all chains",
+                        "estimator": "coda AR spectral (bb_chains_summary, on the device), all chains x all coefficients",
+                        "n_per_chain": int(nsl), "summary_s": summary_s, "host_check_max_rel_diff": check,
+                        "posterior_mean_beta0": float(sm["mean"][0]), "q10_q90_beta0": [float(sm["Q.1"][0]), float(sm["Q.9"][0])]}
 
     # ---- end to end through the public C ABI call with host buffers ----
     e2e = run_e2e(L, torch, bb, method, X, y, alpha, nch, chain0, ips, args, dev, world)

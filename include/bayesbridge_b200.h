@@ -165,6 +165,14 @@ int bb_chains_run(bb_chains *c, const bb_hyper *h, unsigned int iter0, int niter
 int bb_chains_store_state(bb_chains *c, long long slot);
 /* copy stored draws to host: out[(chain*nslots + s)*P + j] (or [chain*nslots + s] for scalars) */
 int bb_chains_fetch(const bb_chains *c, int which, long long slot0, long long nslots, double *out);
+/* sum.stat on the device (Code/R/PublicBenchmark.R:112-134) over slots [slot0, slot0 + nslots) of a stored VECTOR
+ * output (`which` = BB_OUT_BETA, ...), 2 <= nslots <= 16384.  Host outputs, either may be NULL:
+ *   per_chain[(chain*5 + k)*P + j], k = mean, sd, ESS, Q.1, Q.9 of chain `chain`'s series of coefficient j
+ *   pooled[k*P + j], k = mean, sd, ESS, ESS.sec, t, Q.1, Q.9 over all chains (the columns of sum.stat): ESS is
+ *   coda::effectiveSize (AR spectral estimate, order by AIC) summed over chains, ESS.sec = ESS / runtime_sec (NaN
+ *   when runtime_sec <= 0), t = mean / sd, quantiles are R's type 7 over the pooled draws. */
+int bb_chains_summary(const bb_chains *c, int which, long long slot0, long long nslots, double runtime_sec,
+                      double *per_chain, double *pooled);
 /* number of kernels launched by this library in this process so far */
 long long bb_launch_count(void);
 

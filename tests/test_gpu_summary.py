@@ -1,0 +1,77 @@
+"""-m gpu: sum.stat on the device (bb_chains_summary) against the host restatement
+bayesbridge_b200/ess.py (coda's effectiveSize definition, R's type-7 quantiles) on the same stored draws."""
+import numpy as np
+import pytest
+
+from helpers import small_problem
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(method, N, P, nch, nsamp, seed=3):
+    import bayesbridge_b200 as bb
+    from bayesbridge_b200._lib import ST_ALL
+    X, y, _ = small_problem(N, P, seed=seed)
+    model = bb.Model(X, y)
+    ch = model.chains(method, nch, seed=77)
+    hyp = bb.make_hyper(alpha=0.5)
+    ch.reserve(nsamp, ("beta",))
+    ch.run(hyp, 50, 0, ST_ALL, pre_tau=1)
+    ch.run(hyp, nsamp, 50, ST_ALL, thin=1, slot0=0)
+    return ch
+
+
+@pytest.mark.parametrize("method,N,P,nch,nsamp", [("stable", 120, 9, 5, 300), ("triangle", 80, 13, 3, 257), ("stable", 442, 64, 4, 1000)])
+def test_device_summary_matches_host(method, N, P, nch, nsamp):
+    from bayesbridge_b200 import ess
+    ch = _run(method, N, P, nch, nsamp)
+    draws = ch.fetch("beta")
+    host = ess.summary(draws, runtime=2.0)
+    dev = ch.summary("beta", runtime=2.0, per_chain=True)
+    for k in ("mean", "sd", "t", "Q.1", "Q.9"):
+        np.testing.assert_allclose(dev[k], host[k], rtol=1e-10, atol=1e-12, err_msg=k)
+    np.testing.assert_allclose(dev["ESS"], host["ESS"], rtol=1e-7, err_msg="ESS")
+    np.testing.assert_allclose(dev["ESS.sec"], host["ESS"] / 2.0, rtol=1e-7)
+    # per-chain block: mean, sd, ESS, Q.1, Q.9 of every chain's own series
+    pc = dev["chains"]
+    for c in range(nch):
+        np.testing.assert_allclose(pc[c, 0], draws[c].mean(0), rtol=1e-11, atol=1e-13)
+        np.testing.assert_allclose(pc[c, 1], draws[c].std(0, ddof=1), rtol=1e-10)
+        np.testing.assert_allclose(pc[c, 2], [ess.ess_ar(draws[c, :, j]) for j in range(P)], rtol=1e-7)
+        np.testing.assert_allclose(pc[c, 3], np.quantile(draws[c], 0.1, axis=0), rtol=1e-10, atol=1e-12)
+        np.testing.assert_allclose(pc[c, 4], np.quantile(draws[c], 0.9, axis=0), rtol=1e-10, atol=1e-12)
+
+
+def test_summary_slot_window_and_errors():
+    ch = _run("stable", 100, 6, 2, 64)
+    draws = ch.fetch("beta")
+    s = ch.summary("beta", slot0=10, nslots=40)
+    np.testing.assert_allclose(s["mean"], draws[:, 10:50].reshape(-1, 6).mean(0), rtol=1e-11, atol=1e-13)
+    np.testing.assert_allclose(s["Q.9"], np.quantile(draws[:, 10:50].reshape(-1, 6), 0.9, axis=0), rtol=1e-10, atol=1e-12)
+    assert "ESS.sec" not in s
+    with pytest.raises(RuntimeError):
+        ch.summary("beta", slot0=60, nslots=10)       # out of range
+    with pytest.raises(RuntimeError):
+        ch.summary("lambda")                          # not reserved
+
+
+def test_summary_with_ties_and_constant_series():
+    """quantiles with repeated values (the `shape` indicator of the triangle sampler is 1 or 2) and ESS = 0 for a
+    constant series follow the host definitions."""
+    import bayesbridge_b200 as bb
+    from bayesbridge_b200 import ess
+    from bayesbridge_b200._lib import ST_ALL
+    X, y, _ = small_problem(90, 7, seed=5)
+    model = bb.Model(X, y)
+    ch = model.chains("triangle", 3, seed=5)
+    hyp = bb.make_hyper(alpha=0.5)
+    ch.reserve(200, ("beta", "shape"))
+    ch.run(hyp, 200, 0, ST_ALL, pre_tau=1, thin=1, slot0=0)
+    sh = ch.fetch("shape")
+    dev = ch.summary("shape")
+    flat = sh.reshape(-1, 7)
+    np.testing.assert_allclose(dev["Q.1"], np.quantile(flat, 0.1, axis=0), rtol=0, atol=1e-12)
+    np.testing.assert_allclose(dev["Q.9"], np.quantile(flat, 0.9, axis=0), rtol=0, atol=1e-12)
+    np.testing.assert_allclose(dev["mean"], flat.mean(0), rtol=1e-12)
+    host_ess = np.array([sum(ess.ess_ar(sh[c, :, j]) for c in range(3)) for j in range(7)])
+    np.testing.assert_allclose(dev["ESS"], host_ess, rtol=1e-7)
