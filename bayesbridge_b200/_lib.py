@@ -27,7 +27,7 @@ EXPORTS = [
     "bb_model_create_gram", "bb_model_resid_partial", "bb_model_set_r0", "bb_model_free", "bb_model_get",
     "bb_model_precompute_ms", "bb_chains_create", "bb_chains_free", "bb_chains_set", "bb_chains_get", "bb_chains_alpha",
     "bb_chains_reserve", "bb_chains_run", "bb_chains_store_state", "bb_chains_fetch", "bb_chains_summary", "bb_launch_count",
-    "bb_bridge_batched",
+    "bb_bridge_batched", "bb_bridge_batched_summary",
     "rtexpon_rate_left", "rtexpon_rate_both", "rtexpon_rate", "rtnorm_left", "rtnorm_both", "rtnorm", "rrtgamma_rate", "retstable_LD",
 ]
 
@@ -90,6 +90,8 @@ def load():
     L.bb_chains_summary.argtypes = [vp, C.c_int, C.c_longlong, C.c_longlong, C.c_double, vp, vp]
     L.bb_bridge_batched.argtypes = [C.c_int, C.c_int, dp, dp, C.c_int, C.c_int, C.POINTER(Hyper), C.c_int, C.c_ulonglong,
                                     C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int] + [dp] * 7 + [up, dp]
+    L.bb_bridge_batched_summary.argtypes = [C.c_int, C.c_int, dp, dp, C.c_int, C.c_int, C.POINTER(Hyper), C.c_int, C.c_ulonglong,
+                                            C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int] + [dp] * 4 + [up, dp]
     for name, nd in (("rtexpon_rate_left", 3), ("rtexpon_rate_both", 4), ("rtexpon_rate", 4), ("rtnorm_left", 4),
                      ("rtnorm_both", 5), ("rtnorm", 5), ("rrtgamma_rate", 4), ("retstable_LD", 4)):
         fn = getattr(L, name)

@@ -153,6 +153,32 @@ def bridge_batched(y, X, nsamp, method="triangle", nchains=1, seed=20121027, cha
     return out
 
 
+def bridge_batched_summary(y, X, nsamp, method="triangle", nchains=1, seed=20121027, chain0=0, burn=500, thin=1, ortho=False,
+                           device=0, per_chain=False, **hyper):
+    """bridge_batched in summary mode (bb_bridge_batched_summary): the draws stay on the device, the result is the table
+    of sum.stat (Code/R/PublicBenchmark.R:112-134) -- mean, sd, ESS, ESS.sec, t, Q.1, Q.9 per coefficient over all chains."""
+    L = _lib.load()
+    X = np.asfortranarray(X, dtype=np.float64)
+    y = _f(y)
+    N, P = X.shape
+    meth = BB_TRI if method in ("triangle", "tri") else BB_STB
+    h = make_hyper(**hyper)
+    pooled = np.zeros((7, P))
+    pc = np.zeros((nchains, 5, P)) if per_chain else None
+    sig2, tau = np.zeros((nchains, nsamp)), np.zeros((nchains, nsamp))
+    status = np.zeros(nchains, dtype=np.uint32)
+    rt = C.c_double(0.0)
+    rc = L.bb_bridge_batched_summary(meth, int(bool(ortho)), _p(X), _p(y), N, P, C.byref(h), nchains, seed, chain0, burn, nsamp,
+                                     thin, device, _p(pooled), _p(pc), _p(sig2), _p(tau), status.ctypes.data_as(up), C.byref(rt))
+    if rc:
+        raise RuntimeError("bb_bridge_batched_summary: " + _lib.last_error())
+    out = dict(zip(("mean", "sd", "ESS", "ESS.sec", "t", "Q.1", "Q.9"), pooled))
+    out.update(sig2=sig2, tau=tau, status=status, runtime=rt.value)
+    if per_chain:
+        out["chains"] = pc
+    return out
+
+
 class Model:
     """BridgeRegression::BridgeRegression(X, y) (BridgeRegression.cpp:13-69) on the device."""
 

@@ -714,7 +714,7 @@ void nan_fill(double* p, size_t n) { if (p) for (size_t i = 0; i < n; ++i) p[i] 
 void run_driver(int method, int ortho, const double* X, const double* y, int N, int P, const bb_hyper* h,
                 int nchains, unsigned long long seed, unsigned int chain0, int burn, int nsamp, int thin, int device,
                 double* beta, double* aux1, double* aux2, double* aux3, double* sig2, double* tau, double* alpha,
-                unsigned int* status, double* runtime) {
+                unsigned int* status, double* runtime, double* sum_pooled = nullptr, double* sum_chain = nullptr) {
   if (nsamp < 1 || burn < 0 || nchains < 1) throw std::string("bridge driver: need nsamp >= 1, burn >= 0, nchains >= 1");
   if (thin < 1) thin = 1;
   struct Guard { bb_model* m = nullptr; bb_chains* c = nullptr; ~Guard() { delete c; delete m; } } g;
@@ -736,7 +736,7 @@ void run_driver(int method, int ortho, const double* X, const double* y, int N, 
                  {BB_OUT_SIG2, sig2, nullptr, 1}, {BB_OUT_TAU, tau, nullptr, 1}, {BB_OUT_ALPHA, alpha, nullptr, 1}, {0, nullptr, nullptr, 0}};
   int mask = 0;
   for (const Out& o : outs) if (o.host) mask |= o.which;
-  if (mask == 0) mask = BB_OUT_BETA;
+  if (mask == 0 || sum_pooled || sum_chain) mask |= BB_OUT_BETA;
   if (bb_chains_reserve(g.c, nsamp, mask)) throw std::string(g_err);
   for (Out& o : outs) {
     switch (o.host ? o.which : 0) {
@@ -801,6 +801,8 @@ void run_driver(int method, int ortho, const double* X, const double* y, int N, 
   if (runtime) *runtime = secs;
   lap("sampling loop");
   BB_CUDA_CHECK(cudaStreamSynchronize(cps.s));
+  // summary mode: sum.stat of beta over the nsamp stored samples, on the device (the draws need not leave the GPU)
+  if ((sum_pooled || sum_chain) && bb_chains_summary(g.c, BB_OUT_BETA, 0, nsamp, secs, sum_chain, sum_pooled)) throw std::string(g_err);
   if (status && bb_chains_get(g.c, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, status)) throw std::string(g_err);
   lap("download");
   if (g_verbose) std::printf("Sampling complete: %g sec. for %i iterations.\n", secs, nsamp);
@@ -817,6 +819,16 @@ int bb_bridge_batched(int method, int ortho, const double* X, const double* y, i
   return guarded([&] {
     run_driver(method, ortho, X, y, N, P, h, nchains, seed, chain0, burn, nsamp, thin, device, beta, aux1, aux2, aux3, sig2, tau,
                alpha, status, runtime);
+  });
+}
+
+int bb_bridge_batched_summary(int method, int ortho, const double* X, const double* y, int N, int P, const bb_hyper* h,
+                              int nchains, unsigned long long seed, unsigned int chain0, int burn, int nsamp, int thin, int device,
+                              double* pooled, double* per_chain, double* sig2, double* tau, unsigned int* status, double* runtime) {
+  return guarded([&] {
+    if (!pooled && !per_chain) throw std::string("bb_bridge_batched_summary: pooled and per_chain are both NULL");
+    run_driver(method, ortho, X, y, N, P, h, nchains, seed, chain0, burn, nsamp, thin, device, nullptr, nullptr, nullptr, nullptr,
+               sig2, tau, nullptr, status, runtime, pooled, per_chain);
   });
 }
 

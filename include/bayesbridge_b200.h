@@ -191,6 +191,17 @@ int bb_bridge_batched(int method, int ortho,
                       double *beta, double *aux1, double *aux2, double *aux3,
                       double *sig2, double *tau, double *alpha, unsigned int *status, double *runtime);
 
+/* The same run in SUMMARY mode: the draws of beta stay in HBM and sum.stat is taken on the
+ * device.  pooled: [7][P] (mean, sd, ESS, ESS.sec, t, Q.1, Q.9 over all chains, ESS.sec = ESS / runtime of the
+ * post-burn-in loop); per_chain: [nchains][5][P] (mean, sd, ESS, Q.1, Q.9); either may be NULL (not both).
+ * sig2 / tau: [nchains][nsamp] or NULL.  2 <= nsamp <= 16384. */
+int bb_bridge_batched_summary(int method, int ortho,
+                              const double *X, const double *y, int N, int P, const bb_hyper *h,
+                              int nchains, unsigned long long seed, unsigned int chain0,
+                              int burn, int nsamp, int thin, int device,
+                              double *pooled, double *per_chain, double *sig2, double *tau,
+                              unsigned int *status, double *runtime);
+
 #ifdef __cplusplus
 }
 #endif

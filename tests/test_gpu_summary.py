@@ -75,3 +75,20 @@ def test_summary_with_ties_and_constant_series():
     np.testing.assert_allclose(dev["mean"], flat.mean(0), rtol=1e-12)
     host_ess = np.array([sum(ess.ess_ar(sh[c, :, j]) for c in range(3)) for j in range(7)])
     np.testing.assert_allclose(dev["ESS"], host_ess, rtol=1e-7)
+
+
+def test_summary_mode_driver_equals_draws_mode():
+    """bb_bridge_batched_summary == sum.stat of the draws bb_bridge_batched returns for the same seed."""
+    import bayesbridge_b200 as bb
+    from bayesbridge_b200 import ess
+    X, y, _ = small_problem(150, 8, seed=9)
+    kw = dict(method="stable", nchains=6, seed=99, burn=30, alpha=0.5)
+    full = bb.bridge_batched(y, X, 120, want=("beta", "sig2", "tau"), **kw)
+    sm = bb.bridge_batched_summary(y, X, 120, per_chain=True, **kw)
+    host = ess.summary(full["beta"])
+    for k in ("mean", "sd", "t", "Q.1", "Q.9"):
+        np.testing.assert_allclose(sm[k], host[k], rtol=1e-10, atol=1e-12, err_msg=k)
+    np.testing.assert_allclose(sm["ESS"], host["ESS"], rtol=1e-7)
+    np.testing.assert_allclose(sm["ESS.sec"] * sm["runtime"], sm["ESS"], rtol=1e-12)
+    assert np.array_equal(sm["sig2"], full["sig2"]) and np.array_equal(sm["tau"], full["tau"])
+    assert sm["chains"].shape == (6, 5, 8) and not sm["status"].any()
