@@ -163,7 +163,7 @@ def run_reference_arm(args):
         return
     import multiprocessing as mp
     cfg, (X, y, _) = make_data(args.workload)
-    method, alpha, P = cfg["method"], cfg["alpha"], X.shape[1]
+    method, alpha, P = cfg["method"], (args.alpha if args.alpha > 0 else cfg["alpha"]), X.shape[1]
     kind = cpu_kind()
     cores = os.cpu_count() or 1
     per_step_s = max(2.0, min(20.0, 150.0 / max(1, args.steps + args.warmup)))
@@ -225,7 +225,7 @@ def run_ours(args):
         L.bb_set_verbose(int(os.environ["BB_VERBOSE"]))   # 2: per-phase timings of the batched driver on stdout
     wl = WORKLOADS[args.workload]
     cfg, (X, y, _) = make_data(args.workload)
-    method, alpha = cfg["method"], cfg["alpha"]
+    method, alpha = cfg["method"], (args.alpha if args.alpha > 0 else cfg["alpha"])
     N, P = X.shape
     nch = args.chains or wl["chains"]
     ips = args.iters or wl["iters"]
@@ -401,6 +401,7 @@ def main():
     ap.add_argument("--chains", type=int, default=0, help="chains per GPU (default: the workload's)")
     ap.add_argument("--iters", type=int, default=0, help="Gibbs iterations per step (default: the workload's)")
     ap.add_argument("--burn", type=int, default=None)
+    ap.add_argument("--alpha", type=float, default=0.0, help="override the workload's alpha (the c5 sweep: 0.125, 0.5, 0.9)")
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true")
