@@ -1,4 +1,5 @@
 // bb_stb.cu -- host launcher of the on-chip stable-mixture sweep kernel (bb_stb.cuh, P <= 128).
+#include <cstdio>
 #include <cstdlib>
 #include "bb_stb.cuh"
 #include "bb_stb64.cuh"
@@ -24,6 +25,18 @@ void launch64(const StbLaunch& L, cudaStream_t st) {
   BB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   kern<<<(L.nchains + NCH - 1) / NCH, S64_T * NCH, smem, st>>>(L);
   check_launch();
+#ifdef BB_PHASES
+  BB_CUDA_CHECK(cudaStreamSynchronize(st));
+  unsigned long long h[8];
+  BB_CUDA_CHECK(cudaMemcpyFromSymbol(h, bb_phase_cyc, sizeof(h)));
+  static unsigned long long prev[8] = {0};
+  const char* nm[8] = {"tau+sig2", "lambda", "tiles+normals", "factorisation", "solves", "alpha+store", "-", "loop head"};
+  double tot = 0; for (int k = 0; k < 8; ++k) tot += (double)(h[k] - prev[k]);
+  std::printf("  [stb64 phases, CTA 0, %d iterations]", L.niter);
+  for (int k = 0; k < 8; ++k) if (h[k] != prev[k]) std::printf(" %s %.0f cyc/it (%.1f%%)", nm[k], (double)(h[k] - prev[k]) / L.niter, 100.0 * (h[k] - prev[k]) / tot);
+  std::printf("\n");
+  for (int k = 0; k < 8; ++k) prev[k] = h[k];
+#endif
 }
 
 }  // namespace

@@ -74,6 +74,14 @@ __device__ __forceinline__ void chol8_inverse(const double* __restrict__ tile, d
   }
 }
 
+// Phase timing (development, -DBB_PHASES): thread 0 of CTA 0 accumulates the cycles between the phase marks of its chain.
+#ifdef BB_PHASES
+__device__ unsigned long long bb_phase_cyc[8];
+#define BB_PHASE_MARK(k) do { if (blockIdx.x == 0 && threadIdx.x == 0) { const long long now_ = clock64(); bb_phase_cyc[k] += (unsigned long long)(now_ - ph_t); ph_t = now_; } } while (0)
+#else
+#define BB_PHASE_MARK(k) do { } while (0)
+#endif
+
 // NCH chains share one CTA (128 threads each).  All barriers are CTA-wide, so the chains of an SM walk
 // through the kernel's phases together and the instruction cache holds ONE phase at a time; with four
 // independent CTAs per SM the same code ran at four different places and `stall_no_instruction` was the
@@ -126,9 +134,13 @@ __global__ void __launch_bounds__(S64_T * NCH, 4 / NCH) stb64_kernel(const StbLa
 
   const int bar_id = 1 + cslot;   // named barrier of this chain's 128 threads (inside the factorisation only)
 
+#ifdef BB_PHASES
+  long long ph_t = clock64();
+#endif
   for (int it = -L.pre_tau; it < L.niter; ++it) {
     const bool pre = it < 0;
     const uint32_t tt = L.iter0 + (pre ? 0u : (uint32_t)it);
+    BB_PHASE_MARK(7);
 
     // ---- partial sums for tau and the residual sum of squares ----
     if (tid < PP) dl_s[tid] = tid < P ? beta_s[tid] - __ldg(L.m.bc + tid) : 0.0;
@@ -169,10 +181,12 @@ __global__ void __launch_bounds__(S64_T * NCH, 4 / NCH) stb64_kernel(const StbLa
     __syncthreads();
     if (pre) continue;
     const double tau = sc_s[0], sig2 = sc_s[1];
+    BB_PHASE_MARK(0);
 
     // ---- lambda_j = 2 * retstable(beta_j^2 / tau^2, alpha/2): retry queue + speculative look-ahead ----
     if (do_lambda) lambda_stage_cta<S64_T>(tid, P, beta_s, lam_s, tau, 0.5 * alpha, L.key, gch, tt, rc_s, q_s, PP, qn_s, kk_s, status);
     else __syncthreads();
+    BB_PHASE_MARK(1);
 
     if (do_beta && !TC) {
       // ---- S = X'X + diag(lambda sig2 / tau^2)   (BridgeRegression.cpp:554-556), lower triangle ----
@@ -266,6 +280,7 @@ __global__ void __launch_bounds__(S64_T * NCH, 4 / NCH) stb64_kernel(const StbLa
       double eps = 0.0;
       if (tid < P) { Stream s(L.key, gch, tt, ST_BETA_STB, (uint32_t)tid); eps = s.norm(0); }
       if (tid < PP) rhs_s[tid] = tid < P ? __ldg(L.m.Xy + tid) : 0.0;
+      BB_PHASE_MARK(2);
 
       for (int s = 0; s < 8; ++s) {
         // (1) publish the tiles of block column s
@@ -296,6 +311,7 @@ __global__ void __launch_bounds__(S64_T * NCH, 4 / NCH) stb64_kernel(const StbLa
           }
       }
       __syncthreads();
+      BB_PHASE_MARK(3);
       // ---- w = L^-1 Xy (the reference's first trsm, :564), blocked with the inverse diagonal blocks ----
       const double sig = sqrt(sig2);
       if (warp == 0) {
@@ -348,6 +364,7 @@ __global__ void __launch_bounds__(S64_T * NCH, 4 / NCH) stb64_kernel(const StbLa
         }
       }
       __syncthreads();
+      BB_PHASE_MARK(4);
     }  // do_beta, tensor-core path
 
     // ---- alpha (only when it is unknown): BridgeRegression.cpp:477-503 ----
@@ -381,6 +398,7 @@ __global__ void __launch_bounds__(S64_T * NCH, 4 / NCH) stb64_kernel(const StbLa
         if (L.sink.alpha) L.sink.alpha[o] = alpha;
       }
     }
+    BB_PHASE_MARK(5);
   }
 
   __syncthreads();
