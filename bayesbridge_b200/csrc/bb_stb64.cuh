@@ -144,7 +144,27 @@ __global__ void __launch_bounds__(S64_T * NCH, 4 / NCH) stb64_kernel(const StbLa
 
     // ---- partial sums for tau and the residual sum of squares ----
     if (tid < PP) dl_s[tid] = tid < P ? beta_s[tid] - __ldg(L.m.bc + tid) : 0.0;
+    // Warps 2 and 3 have nothing to do until the lambda stage (the partial sums and the gamma draws below belong to
+    // warps 0 and 1): in those two windows they stage X'X (lower 8 x 8 tiles, diagonal tiles in full) into S -- free
+    // until the panel step of the factorisation writes it -- and draw the normals of the noise term (:567-568), so
+    // that after the lambda stage the tile fragments come from shared memory instead of 18 global loads per thread.
+    const bool stager = TC && do_beta && !pre && warp >= 2;
+    auto stage_rows = [&](int i0, int i1) {
+      const int u = tid - 64, er = u & 7, ec = u >> 3;
+#pragma unroll 1
+      for (int i = i0; i < i1; ++i) {
+        const int row = 8 * i + er;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          if (j <= i) {
+            const int col = 8 * j + ec;
+            S[row * LD + col] = (row < P && col < P) ? __ldg(L.m.XX + row + (size_t)col * P) : (row == col ? 1.0 : 0.0);
+          }
+        }
+      }
+    };
     __syncthreads();
+    if (stager) stage_rows(0, 5);
     double p_tau = 0.0, p_q = 0.0, p_g = 0.0;
     if (tid < P) {
       const double b = beta_s[tid];
@@ -159,6 +179,13 @@ __global__ void __launch_bounds__(S64_T * NCH, 4 / NCH) stb64_kernel(const StbLa
     p_tau = warp_sum(p_tau); p_q = warp_sum(p_q); p_g = warp_sum(p_g);
     if (lane == 0) { red_s[warp] = p_tau; red_s[8 + warp] = p_q; red_s[16 + warp] = p_g; }
     __syncthreads();
+    if (stager) {
+      stage_rows(5, 8);
+      const int u = tid - 64;
+      double e = 0.0;
+      if (u < P) { Stream s(L.key, gch, tt, ST_BETA_STB, (uint32_t)u); e = s.norm(0); }
+      ip_s[u] = e;
+    }
     if (warp == 0 && (do_tau || (pre && !know_tau))) {          // BridgeRegression.cpp:453-465
       double st = lane < NW ? red_s[lane] : 0.0;
       st = warp_sum(st);
@@ -270,15 +297,12 @@ __global__ void __launch_bounds__(S64_T * NCH, 4 / NCH) stb64_kernel(const StbLa
         while ((i + 1) * (i + 2) / 2 <= n) ++i;
         ti[sl] = i; tj[sl] = n - i * (i + 1) / 2;
         const int row = 8 * i + fr, col = 8 * tj[sl] + fc;
-        double v0 = (row < P && col < P) ? __ldg(L.m.XX + row + (size_t)col * P) : (row == col ? 1.0 : 0.0);
-        double v1 = (row < P && col + 1 < P) ? __ldg(L.m.XX + row + (size_t)(col + 1) * P) : (row == col + 1 ? 1.0 : 0.0);
+        const double2 v = *reinterpret_cast<const double2*>(S + row * LD + col);   // staged during the scalar stage
+        double v0 = v.x, v1 = v.y;
         if (row == col && row < P) v0 += lam_s[row] * f;
         if (row == col + 1 && row < P) v1 += lam_s[row] * f;
         c0[sl] = v0; c1[sl] = v1;
       }
-      // normals for the noise term (BridgeRegression.cpp:567-568), one item per coordinate
-      double eps = 0.0;
-      if (tid < P) { Stream s(L.key, gch, tt, ST_BETA_STB, (uint32_t)tid); eps = s.norm(0); }
       if (tid < PP) rhs_s[tid] = tid < P ? __ldg(L.m.Xy + tid) : 0.0;
       BB_PHASE_MARK(2);
 
@@ -336,10 +360,10 @@ __global__ void __launch_bounds__(S64_T * NCH, 4 / NCH) stb64_kernel(const StbLa
           __syncwarp();
         }
         // rhs = w + sig eps;  then  L' x = rhs  backwards (:565, :570-574)
-        rhs_s[lane] = lane < P ? fma(sig, eps, rb_s[lane]) : 0.0;
+        rhs_s[lane] = lane < P ? fma(sig, ip_s[lane], rb_s[lane]) : 0.0;      // ip_s: the normals drawn in the scalar stage
       }
       __syncthreads();
-      if (warp == 1) rhs_s[32 + lane] = (32 + lane) < P ? fma(sig, eps, rb_s[32 + lane]) : 0.0;
+      if (warp == 1) rhs_s[32 + lane] = (32 + lane) < P ? fma(sig, ip_s[32 + lane], rb_s[32 + lane]) : 0.0;
       __syncthreads();
       if (warp == 0) {
         for (int s = 7; s >= 0; --s) {
