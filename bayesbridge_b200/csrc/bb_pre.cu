@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <vector>
 #include "bb_pre.cuh"
 
@@ -100,20 +101,50 @@ int jacobi_device(double* W, double* V, int M, int P, cudaStream_t st) {
       if (V) { set_identity_kernel<<<296, 256, 0, st>>>(V, P); check_launch(); ++n; }
       unsigned long long* d_convs = dalloc<unsigned long long>(MAX_SWEEPS);
       unsigned int* d_counter = dalloc<unsigned int>(1);
+      const int nblocks = (P + BJ_B - 1) / BJ_B;
+      unsigned int* d_ver = dalloc<unsigned int>(nblocks);
       BB_CUDA_CHECK(cudaMemsetAsync(d_convs, 0, MAX_SWEEPS * sizeof(unsigned long long), st));
       BB_CUDA_CHECK(cudaMemsetAsync(d_counter, 0, sizeof(unsigned int), st));
+      BB_CUDA_CHECK(cudaMemsetAsync(d_ver, 0, nblocks * sizeof(unsigned int), st));
+      // columns whose squared norm is below 1e-29 of the largest are numerically zero (the callers zero every singular
+      // value below 1e-13 d_max, 1e-7 d_max on the Gram path, i.e. squared column norms below 1e-26 / 1e-28 of the largest)
+      double floor2 = 0.0;
+      {
+        double* nrm = dalloc<double>(P);
+        colnorm_kernel<<<P, 128, 0, st>>>(W, M, P, nrm); check_launch(); ++n;
+        std::vector<double> h(P);
+        BB_CUDA_CHECK(cudaMemcpyAsync(h.data(), nrm, P * sizeof(double), cudaMemcpyDeviceToHost, st));
+        BB_CUDA_CHECK(cudaStreamSynchronize(st));
+        dfree(nrm);
+        double mx = 0.0; for (double v : h) mx = std::max(mx, v);
+        floor2 = 1e-29 * mx * mx;
+      }
       int max_sweeps = MAX_SWEEPS;
-      void* args[] = {&W, &V, &M, &P, &d_sched, &rounds, &npairs, &d_convs, &d_counter, &max_sweeps};
+      void* args[] = {&W, &V, &M, &P, &d_sched, &rounds, &npairs, &d_convs, &d_counter, &d_ver, &floor2, &max_sweeps};
       BB_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)jacobi_block_kernel, dim3(npairs), dim3(256), args, 0, st));
       ++n;
       BB_CUDA_CHECK(cudaStreamSynchronize(st));
+#ifdef BB_PHASES
+      {
+        unsigned long long h[8];
+        BB_CUDA_CHECK(cudaMemcpyFromSymbol(h, bj_phase_cyc, sizeof(h)));
+        static unsigned long long prev[8] = {0};
+        const char* nm[8] = {"gram", "reduce+cos", "inner sweep", "apply", "barrier+sched", "", "", ""};
+        std::printf("  [jacobi phases, CTA 0, M %d P %d]", M, P);
+        for (int k = 0; k < 5; ++k) std::printf(" %s %.0f kcyc", nm[k], (double)(h[k] - prev[k]) / 1e3);
+        std::printf("\n");
+        for (int k = 0; k < 8; ++k) prev[k] = h[k];
+      }
+#endif
       if (std::getenv("BB_JACOBI_VERBOSE")) {
         unsigned long long hc[MAX_SWEEPS];
         BB_CUDA_CHECK(cudaMemcpy(hc, d_convs, sizeof(hc), cudaMemcpyDeviceToHost));
         int ns = 0; while (ns < MAX_SWEEPS && hc[ns] != 0ull) ++ns;
-        std::printf("  [jacobi] block form: M %d P %d, %d rounds x %d pairs, %d sweeps rotated\n", M, P, rounds, npairs, ns);
+        std::printf("  [jacobi] block form: M %d P %d, %d rounds x %d pairs, %d sweeps rotated; max |cos| per sweep:", M, P, rounds, npairs, ns);
+        for (int k = 0; k < ns; ++k) { double v; std::memcpy(&v, &hc[k], sizeof(v)); std::printf(" %.1e", v); }
+        std::printf("\n");
       }
-      dfree(d_sched); dfree(d_convs); dfree(d_counter);
+      dfree(d_sched); dfree(d_convs); dfree(d_counter); dfree(d_ver);
       return n;
     }
   }

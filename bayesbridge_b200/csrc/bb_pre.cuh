@@ -228,6 +228,12 @@ __global__ void __launch_bounds__(256) jacobi_persistent_kernel(double* __restri
 // 8x fewer grid barriers and 8x less L2 traffic per sweep.  conv[s] = largest |cos| between two columns met in sweep s
 // when it exceeds 1e-14 (the stop test); rotations are applied down to 1e-15.
 // ------------------------------------------------------------------------------------------
+#ifdef BB_PHASES
+__device__ unsigned long long bj_phase_cyc[8];
+#define BJ_MARK(k) do { if (blockIdx.x == 0 && threadIdx.x == 0) { const long long now_ = clock64(); bj_phase_cyc[k] += (unsigned long long)(now_ - bj_t); bj_t = now_; } } while (0)
+#else
+#define BJ_MARK(k) do { } while (0)
+#endif
 constexpr int BJ_B = 8;
 constexpr int BJ_N = 2 * BJ_B;
 
@@ -237,35 +243,43 @@ struct BjSmem {
   double Jm[2][BJ_N][BJ_N + 1];
   double red[8];
   unsigned char partner[BJ_N - 1][BJ_N];   // inner round r: the column rotated against column i
-  int rotate;
 };
 
+// Inner schedule: rounds 0..6 rotate the pairs WITHIN each of the two blocks (a round-robin tournament of 8, both blocks at
+// once), rounds 7..14 the 64 pairs ACROSS the blocks (i, 8 + (i + r) mod 8).  A block's own pairs are rotated once per
+// sweep (in the first round of the sweep); every other round runs the cross rounds only.
+constexpr int BJ_CROSS0 = BJ_B - 1;
 __device__ __forceinline__ void bj_inner_schedule(BjSmem& sm) {
   if (threadIdx.x == 0) {
-    int ring[BJ_N];
-    for (int i = 0; i < BJ_N; ++i) ring[i] = i;
-    for (int r = 0; r < BJ_N - 1; ++r) {
-      for (int k = 0; k < BJ_B; ++k) {
-        int p = ring[k], q = ring[BJ_N - 1 - k];
-        if (p > q) { const int t = p; p = q; q = t; }
+    int ring[BJ_B];
+    for (int i = 0; i < BJ_B; ++i) ring[i] = i;
+    for (int r = 0; r < BJ_B - 1; ++r) {
+      for (int k = 0; k < BJ_B / 2; ++k) {
+        const int p = ring[k], q = ring[BJ_B - 1 - k];
         sm.partner[r][p] = (unsigned char)q; sm.partner[r][q] = (unsigned char)p;
+        sm.partner[r][BJ_B + p] = (unsigned char)(BJ_B + q); sm.partner[r][BJ_B + q] = (unsigned char)(BJ_B + p);
       }
-      const int last = ring[BJ_N - 1];
-      for (int i = BJ_N - 1; i > 1; --i) ring[i] = ring[i - 1];
+      const int last = ring[BJ_B - 1];
+      for (int i = BJ_B - 1; i > 1; --i) ring[i] = ring[i - 1];
       ring[1] = last;
     }
+    for (int r = 0; r < BJ_B; ++r)
+      for (int i = 0; i < BJ_B; ++i) {
+        const int q = BJ_B + (i + r) % BJ_B;
+        sm.partner[BJ_CROSS0 + r][i] = (unsigned char)q; sm.partner[BJ_CROSS0 + r][q] = (unsigned char)i;
+      }
   }
   __syncthreads();
 }
 
 // T <- T Jm for the 16 columns {8 I .., 8 J ..} of T (rows x ., leading dimension ld), 8-row tiles split over the warps
-__device__ __forceinline__ void bj_apply(double* __restrict__ T, int rows, int ld, int P, int I, int J, const BjSmem& sm) {
+__device__ __forceinline__ void bj_apply(double* __restrict__ T, int rows, int ld, int P, int I, int J, const BjSmem& sm, int buf) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   double bf[2][4];
 #pragma unroll
   for (int nt = 0; nt < 2; ++nt)
 #pragma unroll
-    for (int kq = 0; kq < 4; ++kq) bf[nt][kq] = sm.Jm[(BJ_N - 1) & 1][4 * kq + (lane & 3)][8 * nt + (lane >> 2)];
+    for (int kq = 0; kq < 4; ++kq) bf[nt][kq] = sm.Jm[buf][4 * kq + (lane & 3)][8 * nt + (lane >> 2)];
   // columns this lane loads (k index 4 kq + lane%4) and stores (n index 8 nt + 2 (lane%4) + e)
   size_t lo[4]; bool lv[4];
 #pragma unroll
@@ -283,7 +297,7 @@ __device__ __forceinline__ void bj_apply(double* __restrict__ T, int rows, int l
       const int col = n < BJ_B ? I * BJ_B + n : (J < 0 ? P : J * BJ_B + n - BJ_B);
       sv[nt][e] = col < P; so[nt][e] = (size_t)(sv[nt][e] ? col : 0) * ld;
     }
-  constexpr int U = 4;   // row tiles in flight per warp
+  constexpr int U = 8;   // row tiles in flight per warp
   for (int r0 = 8 * warp; r0 < rows; r0 += 64 * U) {
     double a[U][4];
 #pragma unroll
@@ -312,22 +326,27 @@ __device__ __forceinline__ void bj_apply(double* __restrict__ T, int rows, int l
   }
 }
 
-// Jacobi rotation of a symmetric 2 x 2 block (al ga; ga be): (c, s) with new p = c p - s q, new q = s p + c q orthogonal.
-// Straight-line (bb_math.cuh): t = sgn(be - al) 2 ga / (|be - al| + sqrt((be - al)^2 + 4 ga^2)), c = 1/sqrt(1 + t^2).
-// No rotation when |ga| <= 1e-15 sqrt(al be).
-__device__ __forceinline__ void bj_rot(double al, double be, double ga, double& c, double& s) {
+// Jacobi rotation of a symmetric 2 x 2 block (al ga; ga be): (c, s) with new p = c p - s q, new q = s p + c q orthogonal,
+// |angle| <= pi/4.  With dl = be - al, h = sqrt(dl^2 + 4 ga^2):  c^2 = (1 + |dl| / h) / 2,  s = sgn(dl) ga / (h c)
+// -- two dependent reciprocal square roots (straight-line, bb_math.cuh) instead of sqrt, reciprocal and rsqrt of the
+// tangent form.  No rotation when |ga| <= 1e-15 sqrt(al be), or when a column is numerically zero (norm^2 <= floor2:
+// the null-space columns of a rank-deficient matrix are rounding noise whose mutual angles never settle).
+__device__ __forceinline__ void bj_rot(double al, double be, double ga, double floor2, double& c, double& s) {
   const double g2 = ga * ga;
-  const bool go = g2 > 1e-30 * al * be;
+  const bool go = g2 > 1e-30 * al * be && al > floor2 && be > floor2;
   const double dl = be - al;
   const double hh = go ? fma(dl, dl, 4.0 * g2) : 1.0;
-  const double t = (dl >= 0.0 ? 2.0 : -2.0) * ga * x_rcp(fabs(dl) + x_sqrt(hh));
-  const double cc = x_rsqrt(fma(t, t, 1.0));
-  c = go ? cc : 1.0; s = go ? cc * t : 0.0;
+  const double r1 = x_rsqrt(hh);
+  const double c2 = fma(0.5 * fabs(dl), r1, 0.5);
+  const double rc = x_rsqrt(c2);
+  c = go ? c2 * rc : 1.0;
+  s = go ? (dl >= 0.0 ? ga : -ga) * r1 * rc : 0.0;
 }
 
 __device__ __forceinline__ void bj_block_pair(double* __restrict__ W, double* __restrict__ V, int M, int P, int I, int J,
-                                              unsigned long long* conv, BjSmem& sm) {
+                                              unsigned long long* conv, double floor2, bool within, BjSmem& sm, long long& bj_t) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  BJ_MARK(4);
   // ---- 1. G = B'B ----
   {
     const int cA = I * BJ_B + (lane >> 2), cB = J < 0 ? P : J * BJ_B + (lane >> 2);
@@ -335,7 +354,7 @@ __device__ __forceinline__ void bj_block_pair(double* __restrict__ W, double* __
     const double* pA = W + (size_t)(vA ? cA : 0) * M;
     const double* pB = W + (size_t)(vB ? cB : 0) * M;
     double g[3][2] = {{0.0, 0.0}, {0.0, 0.0}, {0.0, 0.0}};
-#pragma unroll 8
+#pragma unroll 16
     for (int k0 = 4 * warp; k0 < M; k0 += 32) {
       const int k = k0 + (lane & 3);
       const double a = (vA && k < M) ? __ldcg(pA + k) : 0.0;
@@ -349,6 +368,7 @@ __device__ __forceinline__ void bj_block_pair(double* __restrict__ W, double* __
     for (int t = 0; t < 3; ++t) { sm.part[warp][t][e] = g[t][0]; sm.part[warp][t][e + 1] = g[t][1]; }
   }
   __syncthreads();
+  BJ_MARK(0);
   const int i = tid >> 4, j = tid & 15;
   const int lo_ = i < j ? i : j, hi_ = i < j ? j : i;     // both triangles read the same element: G is exactly symmetric
   {
@@ -363,70 +383,94 @@ __device__ __forceinline__ void bj_block_pair(double* __restrict__ W, double* __
     sm.Jm[0][i][j] = i == j ? 1.0 : 0.0;
   }
   __syncthreads();
-  // ---- largest |cos| among the 120 column pairs of this CTA ----
+  // ---- largest cos^2 among the 120 column pairs of this CTA (numerically zero columns do not count) ----
   {
-    double rel = 0.0;
+    double rel2 = 0.0;
     if (i < j) {
-      const double den = sqrt(sm.G[0][i][i] * sm.G[0][j][j]);
-      rel = den > 0.0 ? fabs(sm.G[0][i][j]) / den : 0.0;
+      const double al = sm.G[0][i][i], be = sm.G[0][j][j], ga = sm.G[0][i][j];
+      if (al > floor2 && be > floor2) rel2 = ga * ga * x_rcp(al * be);
     }
-    rel = warp_max(rel);
-    if (lane == 0) sm.red[warp] = rel;
+    rel2 = warp_max(rel2);
+    if (lane == 0) sm.red[warp] = rel2;
     __syncthreads();
-    if (tid == 0) {
-      double m = 0.0;
-      for (int w = 0; w < 8; ++w) m = fmax(m, sm.red[w]);
-      sm.rotate = m > 1e-15;
-      if (m > 1e-14) atomicMax(conv, (unsigned long long)__double_as_longlong(m));
-    }
-    __syncthreads();
+    double m = 0.0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) m = fmax(m, sm.red[w]);
+    if (tid == 0 && m > 1e-28) atomicMax(conv, (unsigned long long)__double_as_longlong(sqrt(m)));
+    if (!(m > 1e-30)) { __syncthreads(); return; }      // nothing to rotate (CTA-uniform); red is reused by the next call
   }
-  if (!sm.rotate) return;
+  BJ_MARK(1);
   // ---- 2. one cyclic sweep on G, J accumulates the rotations ----
   // Thread (i,j) needs the rotations of the pairs holding i and j: it computes both itself from the current copy of G
   // (two independent straight-line chains) instead of waiting for 8 threads to publish them: ONE barrier per inner round.
-  for (int r = 0; r < BJ_N - 1; ++r) {
-    const double (*G)[BJ_N + 1] = sm.G[r & 1];
-    const double (*Jc)[BJ_N + 1] = sm.Jm[r & 1];
+  const int r0 = within ? 0 : BJ_CROSS0;
+  for (int r = r0; r < BJ_N - 1; ++r) {
+    const double (*G)[BJ_N + 1] = sm.G[(r - r0) & 1];
+    const double (*Jc)[BJ_N + 1] = sm.Jm[(r - r0) & 1];
     const int pl = sm.partner[r][lo_], ph = sm.partner[r][hi_];
     double cl, sl, ch, sh;
     {
       const int p = lo_ < pl ? lo_ : pl, q = lo_ < pl ? pl : lo_;
-      bj_rot(G[p][p], G[q][q], G[p][q], cl, sl);
+      bj_rot(G[p][p], G[q][q], G[p][q], floor2, cl, sl);
       sl = lo_ == p ? -sl : sl;
     }
     {
       const int p = hi_ < ph ? hi_ : ph, q = hi_ < ph ? ph : hi_;
-      bj_rot(G[p][p], G[q][q], G[p][q], ch, sh);
+      bj_rot(G[p][p], G[q][q], G[p][q], floor2, ch, sh);
       sh = hi_ == p ? -sh : sh;
     }
     const double gn = cl * ch * G[lo_][hi_] + cl * sh * G[lo_][ph] + sl * ch * G[pl][hi_] + sl * sh * G[pl][ph];
     const int pj = j == lo_ ? pl : ph;
     const double cj = j == lo_ ? cl : ch, sj = j == lo_ ? sl : sh;
     const double jn = cj * Jc[i][j] + sj * Jc[i][pj];
-    sm.G[(r + 1) & 1][i][j] = gn; sm.Jm[(r + 1) & 1][i][j] = jn;
+    sm.G[(r - r0 + 1) & 1][i][j] = gn; sm.Jm[(r - r0 + 1) & 1][i][j] = jn;
     __syncthreads();
   }
+  BJ_MARK(2);
   // ---- 3. B <- B J, V <- V J ----
-  bj_apply(W, M, M, P, I, J, sm);
-  if (V != nullptr) bj_apply(V, P, P, P, I, J, sm);
+  const int buf = (BJ_N - 1 - r0) & 1;
+  bj_apply(W, M, M, P, I, J, sm, buf);
+  if (V != nullptr) bj_apply(V, P, P, P, I, J, sm, buf);
+  BJ_MARK(3);
 }
 
-// The whole block tournament in ONE cooperative launch: CTA b = block pair b of the round, grid barrier between rounds.
+// The whole block tournament in ONE cooperative launch (all CTAs co-resident): CTA b = block pair b of the round.  Between
+// rounds there is NO grid barrier: a pair (I, J) of round g only needs the two CTAs that held I and J in round g - 1, so
+// every block carries a round counter ver[b] (release store after the CTA's last write, acquire poll before its first
+// read).  One grid barrier per SWEEP remains, for the stop test.
+__device__ __forceinline__ void bj_wait(const unsigned int* ver, int b, unsigned int g) {
+  if (b < 0) return;
+  unsigned int v;
+  do { asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ver + b) : "memory"); } while (v < g);
+}
+__device__ __forceinline__ void bj_post(unsigned int* ver, int b, unsigned int g) {
+  if (b < 0) return;
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(ver + b), "r"(g) : "memory");
+}
+
 __global__ void __launch_bounds__(256) jacobi_block_kernel(double* __restrict__ W, double* __restrict__ V, int M, int P,
                                                            const int* __restrict__ sched, int rounds, int npairs,
-                                                           unsigned long long* conv, unsigned int* counter, int max_sweeps) {
+                                                           unsigned long long* conv, unsigned int* counter, unsigned int* ver,
+                                                           double floor2, int max_sweeps) {
   __shared__ BjSmem sm;
   bj_inner_schedule(sm);
-  unsigned int epoch = 0;
+  unsigned int epoch = 0, g = 0;
+  long long bj_t = clock64();
   for (int sweep = 0; sweep < max_sweeps; ++sweep) {
-    for (int r = 0; r < rounds; ++r) {
+    for (int r = 0; r < rounds; ++r, ++g) {
       const int I = sched[((size_t)r * npairs + blockIdx.x) * 2], J = sched[((size_t)r * npairs + blockIdx.x) * 2 + 1];
-      if (I >= 0) bj_block_pair(W, V, M, P, I, J, conv + sweep, sm);
-      grid_barrier(counter, epoch);
+      if (I >= 0) {
+        if (threadIdx.x == 0) { bj_wait(ver, I, g); bj_wait(ver, J, g); }
+        __syncthreads();
+        bj_block_pair(W, V, M, P, I, J, conv + sweep, floor2, r == 0, sm, bj_t);
+        __syncthreads();                      // every thread's stores are issued ...
+        if (threadIdx.x == 0) { __threadfence(); bj_post(ver, I, g + 1); bj_post(ver, J, g + 1); }   // ... and visible before the counters move
+      }
     }
+    grid_barrier(counter, epoch);
     if (*((volatile unsigned long long*)(conv + sweep)) == 0ull) break;
   }
+  (void)bj_t;
 }
 
 __global__ void set_identity_kernel(double* V, int P) {

@@ -7,7 +7,7 @@ W=$1; K=$2; TAG=$3; shift 3
 mkdir -p gpurun_out
 CMD="python bench.py --workload $W --steps 3 --warmup 3 --no-cpu --no-ess --e2e-steps 1 $*"
 $CMD > gpurun_out/plain_$TAG.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none -k regex:'stb|tri|ortho|gram' -c 2000 --csv --log-file gpurun_out/launches_$TAG.csv $CMD > gpurun_out/ncu_launches_$TAG.log 2>&1
+ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file gpurun_out/launches_$TAG.csv $CMD > gpurun_out/ncu_launches_$TAG.log 2>&1
 $CMD > gpurun_out/plain2_$TAG.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:$K -s 4 -c 1 -o /tmp/prof_$TAG $CMD > gpurun_out/ncu_full_$TAG.log 2>&1
 if [ -f /tmp/prof_$TAG.ncu-rep ]; then

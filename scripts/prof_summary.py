@@ -39,7 +39,7 @@ try:
         a = agg.setdefault(r[ki].split("(")[0][:70], [0, 0.0])
         a[0] += 1; a[1] += v
     tot = sum(a[1] for a in agg.values()) or 1
-    lines += ["", "## Launch list (`--metrics gpu__time_duration.sum`, sweep/precompute kernels of the whole bench command)", "",
+    lines += ["", "## Launch list (`--metrics gpu__time_duration.sum`, every kernel of the whole bench command)", "",
               "| kernel | launches | total ms | share |", "|---|---|---|---|"]
     for k, a in sorted(agg.items(), key=lambda x: -x[1][1]):
         lines.append(f"| `{k}` | {a[0]} | {a[1] / 1e6:.3f} | {a[1] / tot:.3f} |")
