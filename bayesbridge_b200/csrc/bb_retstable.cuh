@@ -233,6 +233,13 @@ __device__ __forceinline__ int rs_levels(int G) {       // longest walk through 
   return G >= 32 ? 13 : G >= 16 ? 9 : G >= 8 ? 7 : G >= 4 ? 4 : G >= 2 ? 2 : 1;
 }
 
+#ifdef BB_PHASES
+__device__ unsigned long long bb_phase_cyc[16];   // development: [0..7] stb64 phases, [8..11] lambda stage: round, walk, queue, passes
+#define BB_LAM_MARK(k) do { if (blockIdx.x == 0 && threadIdx.x == 0) { const long long now_ = clock64(); bb_phase_cyc[8 + k] += (unsigned long long)(now_ - lam_t); lam_t = now_; } } while (0)
+#else
+#define BB_LAM_MARK(k) do { } while (0)
+#endif
+
 // NT: threads serving one chain (multiple of 32); every thread of the CTA must call.  beta: per-item
 // coordinate values (shared or global), lam_out: where 2*draw goes (shared or global).
 // q_s: [2][qld] ints, qn_s: [2] ints (both zero on entry and on exit), kk_s: [P] block positions.
@@ -251,8 +258,21 @@ __device__ inline void lambda_stage_cta(const int tid, int P, const double* beta
     return;
   }
   RetAlpha A; A.init(alpha_half);
+  // the two offset tables as shared-memory bytes: the walk below is a chain of dependent look-ups (13 levels at G = 32), and
+  // unpacking a 6-bit field of a 64-bit constant costs ~300 cycles per level against ~80 for a shared-memory load
+  __shared__ unsigned char lut_slot[64], lut_reach[32];
+  if (threadIdx.x < 64) lut_slot[threadIdx.x] = (unsigned char)rs_slot_of((int)threadIdx.x);
+  if (threadIdx.x < 32) lut_reach[threadIdx.x] = (unsigned char)rs_reach((int)threadIdx.x);
+  __syncthreads();
   bool any = true;
+#ifdef BB_PHASES
+  long long lam_t = clock64();
+#endif
   while (any) {
+    BB_LAM_MARK(3);
+#ifdef BB_PHASES
+    if (blockIdx.x == 0 && threadIdx.x == 0) bb_phase_cyc[12] += 1;
+#endif
     int G = 1;
     while (G < 32 && n_act * (G * 2) <= NT) G *= 2;
     const int per_pass = NT / G;
@@ -273,12 +293,13 @@ __device__ inline void lambda_stage_cta(const int tid, int P, const double* beta
           if (rc_s && sub == 0) rc_s[j] = rc;
         }
         Stream s(key, gch, t, ST_LAMBDA, (uint32_t)j);
-        code = retstable_round_at(A, rc, s, k0 + (uint32_t)rs_reach(sub), out);
+        code = retstable_round_at(A, rc, s, k0 + (uint32_t)lut_reach[sub], out);
       }
+      BB_LAM_MARK(0);
       // walk the sequential path through the G evaluated offsets (uniform trip count: shuffles)
       int pos = 0, res = -1;
       for (int lvl = 0; lvl < nlvl; ++lvl) {
-        const int idx = rs_slot_of(pos);
+        const int idx = lut_slot[pos < 63 ? pos : 63];
         const bool covered = idx < G;
         const int c = __shfl_sync(0xffffffffu, code, covered ? idx : 0, G);
         if (res == -1) {
@@ -287,6 +308,7 @@ __device__ inline void lambda_stage_cta(const int tid, int P, const double* beta
           else pos += (c == 0) ? 3 : 5;
         }
       }
+      BB_LAM_MARK(1);
       const double val = __shfl_sync(0xffffffffu, out, res >= 0 ? res : 0, G);
       if (valid && sub == 0) {
         if (res >= 0) lam_out[j] = 2 * val;
@@ -303,6 +325,7 @@ __device__ inline void lambda_stage_cta(const int tid, int P, const double* beta
     first = false;
     if (tid == 0) qn_s[cur_q ^ 1] = 0;   // the queue the next pass fills
     any = __syncthreads_or(n_act > 0);
+    BB_LAM_MARK(2);
   }
 }
 

@@ -27,9 +27,13 @@ void launch64(const StbLaunch& L, cudaStream_t st) {
   check_launch();
 #ifdef BB_PHASES
   BB_CUDA_CHECK(cudaStreamSynchronize(st));
-  unsigned long long h[8];
+  unsigned long long h[16];
   BB_CUDA_CHECK(cudaMemcpyFromSymbol(h, bb_phase_cyc, sizeof(h)));
-  static unsigned long long prev[8] = {0};
+  static unsigned long long prev[16] = {0};
+  std::printf("  [lambda stage, CTA 0 thread 0] passes/it %.2f; cycles/it: setup+round %.0f walk %.0f queue+barriers %.0f loop head %.0f\n",
+              (double)(h[12] - prev[12]) / L.niter, (double)(h[8] - prev[8]) / L.niter, (double)(h[9] - prev[9]) / L.niter,
+              (double)(h[10] - prev[10]) / L.niter, (double)(h[11] - prev[11]) / L.niter);
+  for (int k = 8; k < 16; ++k) prev[k] = h[k];
   const char* nm[8] = {"tau+sig2", "lambda", "tiles+normals", "factorisation", "solves", "alpha+store", "-", "loop head"};
   double tot = 0; for (int k = 0; k < 8; ++k) tot += (double)(h[k] - prev[k]);
   std::printf("  [stb64 phases, CTA 0, %d iterations]", L.niter);

@@ -76,7 +76,6 @@ __device__ __forceinline__ void chol8_inverse(const double* __restrict__ tile, d
 
 // Phase timing (development, -DBB_PHASES): thread 0 of CTA 0 accumulates the cycles between the phase marks of its chain.
 #ifdef BB_PHASES
-__device__ unsigned long long bb_phase_cyc[8];
 #define BB_PHASE_MARK(k) do { if (blockIdx.x == 0 && threadIdx.x == 0) { const long long now_ = clock64(); bb_phase_cyc[k] += (unsigned long long)(now_ - ph_t); ph_t = now_; } } while (0)
 #else
 #define BB_PHASE_MARK(k) do { } while (0)

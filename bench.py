@@ -282,16 +282,18 @@ def run_ours(args):
     # ---- roofline of the dominant kernel (the sweep kernel; one launch per step except the large-P stable path) ----
     flops_step = algorithmic_flops_per_chain_iter(method, P) * nch * ips
     achieved = flops_step * args.steps / T_local / 1e12
-    traffic = None
+    traffic, ncu_info = None, None
     tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
     if os.path.exists(tpath):
-        traffic = (json.load(open(tpath)).get(args.workload) or {}).get("bytes_per_launch")
+        ncu_info = json.load(open(tpath)).get(args.workload) or None
+        traffic = (ncu_info or {}).get("bytes_per_launch")
     store_bytes = 8.0 * P * nch * ips
     roofline = {"bound": "tensor", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak,
                 "traffic": traffic, "kernel": kernel_name(method, P),
                 "peak_source": "cuBLAS DGEMM 8192^3 measured in this run (FP64; MEASURED_PEAKS.json carries no FP64 figure)",
                 "algorithmic_flops_per_chain_iter": algorithmic_flops_per_chain_iter(method, P),
                 "hbm_store_GBs": store_bytes * args.steps / T_local / 1e9, "hbm_peak_GBs": measured_hbm(),
+                "ncu": ncu_info,   # committed capture of this kernel (profiles/): FP64-pipe and issue-slot utilisation, DRAM bytes per launch
                 "note": "FP64 path: no bf16/HBM roofline applies; the sweep kernels are issue/latency-bound (sequential Gibbs steps, "
                         "3.5 chains per SM), see profiles/*.md for fp64-pipe utilisation and stall breakdowns"}
 
