@@ -134,3 +134,40 @@ def test_wide_design_builds_svd_factors_on_demand():
     assert rel_err(f["d"][:40], sv) < 1e-6 and not f["d"][40:].any() and not np.abs(f["bhat"]).any()
     if fast_ms is not None:
         assert model.L.bb_model_precompute_ms(model.h) >= fast_ms
+
+
+def test_thinned_run_is_a_subsample_and_chunked_download_is_complete():
+    """draws are addressed by (chain, iteration): a thin = 3 run stores iterations 3, 6, ... of the thin = 1 run; the
+    drivers copy finished chunks to the host while the next chunk is sampled, so every slot must arrive (also the
+    unrequested outputs stay untouched and the ragged last chunk is not lost)."""
+    import bayesbridge_b200 as bb
+    X, y, _ = small_problem(120, 11, seed=4)
+    for method, aux in (("stable", "lambda"), ("triangle", "u")):
+        kw = dict(method=method, nchains=5, seed=31, burn=7, alpha=0.5)
+        full = bb.bridge_batched(y, X, 1 + 3 * 67, want=("beta", aux, "sig2", "tau"), **kw)
+        thin = bb.bridge_batched(y, X, 1 + 67, thin=3, want=("beta", aux, "sig2", "tau"), **kw)
+        for k in ("beta", aux, "sig2", "tau"):
+            assert np.array_equal(thin[k], full[k][:, ::3]), (method, k)
+        only = bb.bridge_batched(y, X, 1 + 67, thin=3, want=("beta",), **kw)
+        assert np.array_equal(only["beta"], thin["beta"]) and set(only) == {"beta", "status", "runtime"}
+
+
+def test_constructor_falls_back_for_ill_conditioned_and_rank_deficient_tall_designs():
+    """N >= 4P takes the Cholesky-preconditioned SVD only when X'X factors and the singular values span < 1e3; an
+    ill-conditioned or rank-deficient tall X must come out of the direct rotation of X with the same accuracy."""
+    import bayesbridge_b200 as bb
+    rng = np.random.default_rng(12)
+    N, P = 400, 24
+    Q, _ = np.linalg.qr(rng.standard_normal((N, P)))
+    W, _ = np.linalg.qr(rng.standard_normal((P, P)))
+    for sv in (np.logspace(0, -6, P), np.r_[np.linspace(2, 1, P - 2), 0.0, 0.0]):
+        X = (Q * sv) @ W.T
+        y = X[:, 0] + 0.1 * rng.standard_normal(N)
+        f = bb.Model(X, y).factors()
+        d = np.sort(sv)[::-1]
+        assert np.abs(f["d"] - d).max() < 1e-12 * d[0]
+        V = f["tV"].T
+        assert np.abs(V.T @ V - np.eye(P)).max() < 1e-12
+        assert rel_err(V @ np.diag(f["d"] ** 2) @ V.T, X.T @ X) < 1e-11
+        if sv.min() == 0.0:   # singular: the least-squares start is 0 (BridgeRegression.cpp:79-91)
+            assert not f["bhat"].any()
