@@ -127,18 +127,24 @@ __global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, double* 
     __syncthreads();
   }
   for (int e = tid; e < nb * nb; e += SL_T) { const int r = e % nb, c = e / nb; if (r >= c) A[(k0 + r) + (size_t)(k0 + c) * P] = S[r][c]; }
-  // W = L^-1 (lower), one thread per column: W(c,c) = 1/L(c,c), W(r,c) = -(sum_{m=c}^{r-1} L(r,m) W(m,c)) / L(r,r).
-  // The panel solve below the block is then a DMMA product with W' (stbl_trsm_kernel).
-  if (tid < SL_NB) {
-    const int c = tid;
-    for (int r = 0; r < SL_NB; ++r) Wm[r][c] = 0.0;
-    if (c < nb) {
-      Wm[c][c] = 1.0 / S[c][c];
-      for (int r = c + 1; r < nb; ++r) {
-        double sum = 0.0;
-        for (int m = c; m < r; ++m) sum = fma(S[r][m], Wm[m][c], sum);
-        Wm[r][c] = -sum / S[r][r];
+  // W = L^-1 (lower): W(c,c) = 1/L(c,c), W(r,c) = -(sum_{m=c}^{r-1} L(r,m) W(m,c)) / L(r,r), row by row.  FOUR lanes per column
+  // split the dot product of a row (one thread per column walked 2000 dependent shared-memory steps, the longest chain of
+  // the kernel); the panel solve below the block is then a DMMA product with W' (stbl_trsm_kernel).
+  __syncthreads();
+  for (int e = tid; e < SL_NB * SL_NB; e += SL_T) Wm[e / SL_NB][e % SL_NB] = 0.0;
+  __syncthreads();
+  {
+    const int c = tid >> 2, q = tid & 3;            // SL_T = 256 = 64 columns x 4 lanes; a column's lanes share a warp
+    for (int r = 0; r < nb; ++r) {                  // uniform trip count: the shuffles and __syncwarp need every lane
+      double part = 0.0;
+      if (c < r) for (int m = c + q; m < r; m += 4) part = fma(S[r][m], Wm[m][c], part);
+      part += __shfl_xor_sync(0xffffffffu, part, 1);
+      part += __shfl_xor_sync(0xffffffffu, part, 2);
+      if (q == 0 && c < nb) {
+        if (r == c) Wm[r][c] = 1.0 / S[c][c];
+        else if (r > c) Wm[r][c] = -part / S[r][r];
       }
+      __syncwarp();
     }
   }
   __syncthreads();
