@@ -229,8 +229,8 @@ struct bb_chains {
   long long nslots = 0; int out_mask = 0;
   double *o_beta = nullptr, *o_u = nullptr, *o_omega = nullptr, *o_shape = nullptr, *o_lambda = nullptr;
   double *o_sig2 = nullptr, *o_tau = nullptr, *o_alpha = nullptr;
-  cudaStream_t stream = nullptr, stream2 = nullptr;   // stream2: second half-batch of the large-P stable path
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr, ev_join = nullptr;
+  cudaStream_t stream = nullptr, stream2 = nullptr, xs[3] = {nullptr, nullptr, nullptr};   // xs: the other sub-batches of the large-P stable path
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr, ev_join = nullptr, xj[3] = {nullptr, nullptr, nullptr};
 
   void free_draws() { dfree(o_beta); dfree(o_u); dfree(o_omega); dfree(o_shape); dfree(o_lambda); dfree(o_sig2); dfree(o_tau); dfree(o_alpha); nslots = 0; out_mask = 0; }
   ~bb_chains() {
@@ -242,6 +242,7 @@ struct bb_chains {
     if (ev_fork) cudaEventDestroy(ev_fork);
     if (ev_join) cudaEventDestroy(ev_join);
     if (stream2) cudaStreamDestroy(stream2);
+    for (int i = 0; i < 3; ++i) { if (xj[i]) cudaEventDestroy(xj[i]); if (xs[i]) cudaStreamDestroy(xs[i]); }
     if (stream) cudaStreamDestroy(stream);
   }
 };
@@ -337,23 +338,28 @@ void chains_run(bb_chains* c, const bb_hyper* hh, unsigned iter0, int niter, int
     L.beta = c->beta; L.lambda = c->aux; L.sig2 = c->sig2; L.tau = c->tau; L.alpha = c->alpha; L.status = c->status;
     L.A = c->A; L.W = c->W; L.sink = make_sink(c, thin, slot0);
     bb::stb_large_prepare(P);
-    // Two half-batches on two streams: the low-parallelism kernels of one half (diagonal-block factorisation, panel
-    // solve, substitution: one CTA per chain) run while the other half's update kernel fills the SMs.  The halves
-    // are independent chains, so they only meet again at the end of the call.
-    const int nhalf = c->nchains >= 16 ? 2 : 1;
-    if (nhalf == 2 && !c->stream2) {
-      BB_CUDA_CHECK(cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking));
-      BB_CUDA_CHECK(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
-      BB_CUDA_CHECK(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
+    // Sub-batches on their own streams: the low-parallelism kernels of one sub-batch (diagonal-block factorisation, panel
+    // solve, substitution: one CTA per chain) run while another sub-batch's update kernel fills the SMs.  The sub-batches
+    // are independent chains, so they only meet again at the end of the call.  BB_STBL_SPLIT overrides the count (1..4).
+    static const int split_env = std::getenv("BB_STBL_SPLIT") ? std::atoi(std::getenv("BB_STBL_SPLIT")) : 0;
+    int nsub = c->nchains >= 64 ? 4 : (c->nchains >= 16 ? 2 : 1);   // measured: c4 (128 chains) 9.2 -> 9.4 M, c5s (256 chains) 68.6 -> 71.5 M draws/s from 2 to 4
+    if (split_env >= 1 && split_env <= 4) nsub = std::min(split_env, c->nchains);
+    if (nsub > 1 && !c->ev_fork) BB_CUDA_CHECK(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    for (int i = 0; i + 1 < nsub; ++i)
+      if (!c->xs[i]) {
+        BB_CUDA_CHECK(cudaStreamCreateWithFlags(&c->xs[i], cudaStreamNonBlocking));
+        BB_CUDA_CHECK(cudaEventCreateWithFlags(&c->xj[i], cudaEventDisableTiming));
+      }
+    cudaStream_t sts[4] = {st, c->xs[0], c->xs[1], c->xs[2]};
+    if (nsub > 1) {
+      BB_CUDA_CHECK(cudaEventRecord(c->ev_fork, st));
+      for (int i = 1; i < nsub; ++i) BB_CUDA_CHECK(cudaStreamWaitEvent(sts[i], c->ev_fork, 0));
     }
-    cudaStream_t sts[2] = {st, c->stream2};
-    if (nhalf == 2) { BB_CUDA_CHECK(cudaEventRecord(c->ev_fork, st)); BB_CUDA_CHECK(cudaStreamWaitEvent(c->stream2, c->ev_fork, 0)); }
-    auto half = [&](int h) {
+    auto sub = [&](int h) {
       bb::StbLargeLaunch H = L;
-      const int h0 = h == 0 ? 0 : c->nchains / 2;
-      const int n = nhalf == 1 ? c->nchains : (h == 0 ? c->nchains / 2 : c->nchains - c->nchains / 2);
+      const int h0 = (int)((long long)c->nchains * h / nsub), h1 = (int)((long long)c->nchains * (h + 1) / nsub);
       const size_t o1 = (size_t)h0, oP = (size_t)h0 * P;
-      H.nchains = n; H.chain0 = L.chain0 + (uint32_t)h0;
+      H.nchains = h1 - h0; H.chain0 = L.chain0 + (uint32_t)h0;
       H.beta += oP; H.lambda += oP; H.sig2 += o1; H.tau += o1; H.alpha += o1; H.status += o1;
       H.A += oP * P; H.W += o1 * 64 * 64;
       const size_t os = o1 * (size_t)H.sink.chain_stride;
@@ -369,12 +375,12 @@ void chains_run(bb_chains* c, const bb_hyper* hh, unsigned iter0, int niter, int
       L.pre = it < 0; L.iter = iter0 + (it < 0 ? 0 : it);
       const bool store = c->nslots > 0 && thin > 0 && it >= 0 && ((it + 1) % thin) == 0;
       L.slot = store ? slot0 + (it + 1) / thin - 1 : -1;
-      for (int h = 0; h < nhalf; ++h) {
-        bb::StbLargeLaunch H = half(h);
+      for (int h = 0; h < nsub; ++h) {
+        bb::StbLargeLaunch H = sub(h);
         launched(bb::launch_stb_large_iter(H, (stages & BB_ST_BETA) != 0, sts[h]));
       }
     }
-    if (nhalf == 2) { BB_CUDA_CHECK(cudaEventRecord(c->ev_join, c->stream2)); BB_CUDA_CHECK(cudaStreamWaitEvent(st, c->ev_join, 0)); }
+    for (int i = 1; i < nsub; ++i) { BB_CUDA_CHECK(cudaEventRecord(c->xj[i - 1], sts[i])); BB_CUDA_CHECK(cudaStreamWaitEvent(st, c->xj[i - 1], 0)); }
     check_launch();
   }
   BB_CUDA_CHECK(cudaEventRecord(c->ev1, st));

@@ -1,5 +1,6 @@
 // bb_stb_large.cu -- host side of the large-P stable sweep (bb_stb_large.cuh): one Gibbs iteration =
 // scalar stage, build, blocked left-looking Cholesky (DMMA update / potrf / trsm per block column), solve.
+#include <cstdlib>
 #include "bb_stb_large.cuh"
 
 namespace bb {
@@ -14,6 +15,19 @@ void stb_large_prepare(int P) {
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_trsm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
+  BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_update2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stbl_update2_smem()));
+}
+
+// block column kb > 0 brought up to date: the diagonal tile by the 64 x 64 kernel, the row tiles below it in pairs by the
+// 128 x 64 kernel (BB_STBL_TILE64=1: everything by the 64 x 64 kernel)
+static int launch_update(double* A, int P, int kb, int nblk, int nch, cudaStream_t st) {
+  static const bool tile64 = std::getenv("BB_STBL_TILE64") != nullptr;
+  const size_t smem_sy = (size_t)2 * SL_NB * SL_LD * sizeof(double);
+  const int below = nblk - kb - 1;
+  if (tile64 || below < 2) { stbl_update_kernel<<<dim3(nblk - kb, nch), 256, smem_sy, st>>>(A, P, kb); return 1; }
+  stbl_update_kernel<<<dim3(1, nch), 256, smem_sy, st>>>(A, P, kb);
+  stbl_update2_kernel<<<dim3((below + 1) / 2, nch), 256, stbl_update2_smem(), st>>>(A, P, kb, kb + 1);
+  return 2;
 }
 
 int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
@@ -31,7 +45,7 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
   }
   stbl_build_kernel<<<dim3(64, nch), 256, 0, st>>>(L); ++n;
   for (int kb = 0; kb < nblk; ++kb) {   // left-looking: bring block column kb up to date, factor its diagonal block, solve its panel
-    if (kb > 0) { stbl_update_kernel<<<dim3(nblk - kb, nch), 256, smem_sy, st>>>(L.A, P, kb); ++n; }
+    if (kb > 0) n += launch_update(L.A, P, kb, nblk, nch, st);
     stbl_potrf_kernel<<<nch, SL_T, (size_t)2 * SL_NB * (SL_NB + 1) * sizeof(double), st>>>(L.A, L.W, P, kb, L.status); ++n;
     const int rem = nblk - kb - 1;
     if (rem > 0) { stbl_trsm_kernel<<<dim3(rem, nch), 256, smem_sy, st>>>(L.A, L.W, P, kb); ++n; }
@@ -50,7 +64,7 @@ int chol_lower_device(double* A, int P, double* Winv, uint32_t* status, cudaStre
   const int nblk = (P + SL_NB - 1) / SL_NB;
   int n = 0;
   for (int kb = 0; kb < nblk; ++kb) {
-    if (kb > 0) { stbl_update_kernel<<<dim3(nblk - kb, 1), 256, smem_sy, st>>>(A, P, kb); ++n; }
+    if (kb > 0) n += launch_update(A, P, kb, nblk, 1, st);
     stbl_potrf_kernel<<<1, SL_T, (size_t)2 * SL_NB * (SL_NB + 1) * sizeof(double), st>>>(A, Winv, P, kb, status); ++n;
     const int rem = nblk - kb - 1;
     if (rem > 0) { stbl_trsm_kernel<<<dim3(rem, 1), 256, smem_sy, st>>>(A, Winv, P, kb); ++n; }

@@ -16,7 +16,7 @@ namespace bb {
 
 constexpr int SL_NB = 64;
 constexpr int SL_T = 256;
-constexpr int SL_LD = 72;    // smem row stride of a staged 64 x 64 tile (k-major; minimal 2-way pattern)
+constexpr int SL_LD = 68;    // smem row stride of a staged 64 x 64 tile (k-major; 68 = 4 mod 16: the DMMA fragment loads of a half-warp hit 16 distinct 8-byte banks)
 
 // acc(64 x 64, 8 warps x 8 rows) += A(64 x 64) B(64 x 64)' with As[k][r] = A(r,k), Bs[k][c] = B(c,k) staged in smem
 __device__ __forceinline__ void tile_mma(const double* As, const double* Bs, double (&acc)[8][2], int lane, int warp) {
@@ -234,6 +234,70 @@ __global__ void __launch_bounds__(256, 2) stbl_update_kernel(double* Aall, int P
       if (c + 1 < P && (ti > jb || rr >= c + 1)) A[rr + (size_t)(c + 1) * P] -= acc[t][1];
     }
   }
+}
+
+// ---- the same update with a 128 x 64 CTA tile: every B fragment (the L(jb,k) panel, shared by all row tiles) feeds TWO
+// DMMAs, so the shared-memory loads per tensor instruction drop from 9/8 to 10/16 -- the 64 x 64 form is bound by them.
+// Warp w owns rows 16 w .. 16 w + 15 of the tile.  Launched for the row-tile PAIRS below the diagonal tile; the diagonal
+// tile itself (lower triangle only) stays with the 64 x 64 kernel.
+constexpr int SL_LDA = 132;  // row stride of the staged 128-row A panel (132 = 4 mod 16)
+inline size_t stbl_update2_smem() { return (size_t)(SL_NB * SL_LDA + SL_NB * SL_LD) * sizeof(double); }
+__global__ void __launch_bounds__(256, 2) stbl_update2_kernel(double* Aall, int P, int jb, int t0) {
+  extern __shared__ double smem[];
+  double* As = smem;                       // [64][SL_LDA]
+  double* Bs = smem + SL_NB * SL_LDA;      // [64][SL_LD]
+  const int ch = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double* A = Aall + (size_t)ch * P * P;
+  const int i0 = (t0 + 2 * blockIdx.x) * SL_NB, j0 = jb * SL_NB;
+  double acc[2][8][2];
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int t = 0; t < 8; ++t) { acc[a][t][0] = 0.0; acc[a][t][1] = 0.0; }
+  // thread -> A panel: row r2 = tid & 127, columns k = (tid >> 7) + 2 q (32 elements);  B panel: row r = tid & 63, k = (tid >> 6) + 4 q (16)
+  const int r2 = tid & 127, kh = tid >> 7, r = tid & (SL_NB - 1), kq = tid >> 6;
+  const bool ra = i0 + r2 < P, rb = j0 + r < P;
+  const double* pa_src = A + (i0 + r2) + (size_t)kh * P;
+  const double* pb_src = A + (j0 + r) + (size_t)kq * P;
+  for (int kb = 0; kb < jb; ++kb) {
+    const size_t off = (size_t)kb * SL_NB * P;
+    // staged in two halves (24 loads in flight per thread): the 64 accumulator registers leave no room for all 48
+#pragma unroll
+    for (int hf = 0; hf < 2; ++hf) {
+      double pa[16], pb[8];
+#pragma unroll
+      for (int q = 0; q < 16; ++q) pa[q] = ra ? pa_src[off + (size_t)(2 * (16 * hf + q)) * P] : 0.0;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) pb[q] = rb ? pb_src[off + (size_t)(4 * (8 * hf + q)) * P] : 0.0;
+      if (hf == 0) __syncthreads();        // the previous product is done with the panels
+#pragma unroll
+      for (int q = 0; q < 16; ++q) As[(kh + 2 * (16 * hf + q)) * SL_LDA + r2] = pa[q];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) Bs[(kq + 4 * (8 * hf + q)) * SL_LD + r] = pb[q];
+    }
+    __syncthreads();
+#pragma unroll 4
+    for (int kk = 0; kk < SL_NB; kk += 4) {
+      const double a0 = As[(kk + (lane & 3)) * SL_LDA + warp * 16 + (lane >> 2)];
+      const double a1 = As[(kk + (lane & 3)) * SL_LDA + warp * 16 + 8 + (lane >> 2)];
+#pragma unroll
+      for (int t = 0; t < 8; ++t) {
+        const double b = Bs[(kk + (lane & 3)) * SL_LD + t * 8 + (lane >> 2)];
+        dmma_m8n8k4(acc[0][t][0], acc[0][t][1], a0, b);
+        dmma_m8n8k4(acc[1][t][0], acc[1][t][1], a1, b);
+      }
+    }
+  }
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+      const int rr = i0 + warp * 16 + 8 * a + (lane >> 2), c = j0 + t * 8 + 2 * (lane & 3);
+      if (rr < P) {
+        if (c < P) A[rr + (size_t)c * P] -= acc[a][t][0];
+        if (c + 1 < P) A[rr + (size_t)(c + 1) * P] -= acc[a][t][1];
+      }
+    }
 }
 
 // ---- beta = L^-T (L^-1 Xy + sig eps): one CTA per chain, blocked substitution ----
