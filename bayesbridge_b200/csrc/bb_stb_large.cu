@@ -18,10 +18,11 @@ void stb_large_prepare(int P) {
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_update2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stbl_update2_smem()));
 }
 
-// block column kb > 0 brought up to date: the diagonal tile by the 64 x 64 kernel, the row tiles below it in pairs by the
-// 128 x 64 kernel (BB_STBL_TILE64=1: everything by the 64 x 64 kernel)
+// block column kb > 0 brought up to date by the 64 x 64 kernel.  BB_STBL_TILE128=1: the row tiles below the diagonal tile in
+// pairs by the 128 x 64 kernel instead -- measured SLOWER at c4 (9.8 M against 10.3 M draws/s): its 64 accumulator registers
+// leave no room to keep the next panels' global loads in flight during the tile product, which the 64 x 64 kernel does.
 static int launch_update(double* A, int P, int kb, int nblk, int nch, cudaStream_t st) {
-  static const bool tile64 = std::getenv("BB_STBL_TILE64") != nullptr;
+  static const bool tile64 = std::getenv("BB_STBL_TILE128") == nullptr;
   const size_t smem_sy = (size_t)2 * SL_NB * SL_LD * sizeof(double);
   const int below = nblk - kb - 1;
   if (tile64 || below < 2) { stbl_update_kernel<<<dim3(nblk - kb, nch), 256, smem_sy, st>>>(A, P, kb); return 1; }
