@@ -112,18 +112,34 @@ __global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, double* 
   const int k0 = kb * SL_NB, nb = min(SL_NB, P - k0);
   for (int e = tid; e < nb * nb; e += SL_T) { const int r = e % nb, c = e / nb; S[r][c] = A[(k0 + r) + (size_t)(k0 + c) * P]; }
   __syncthreads();
-  for (int k = 0; k < nb; ++k) {
-    const double piv = S[k][k];
-    __syncthreads();
-    if (tid == 0) { if (!(piv > 0.0)) atomicOr(status + ch, (uint32_t)ST_CHOL_FAIL); S[k][k] = sqrt(piv); }
-    const double rs = rsqrt(piv);
-    for (int r = k + 1 + tid; r < nb; r += SL_T) S[r][k] *= rs;
-    __syncthreads();
-    const int rem = nb - k - 1;
-    for (int e = tid; e < rem * rem; e += SL_T) {
-      const int r = k + 1 + e % rem, c = k + 1 + e / rem;
-      if (r >= c) S[r][c] = fma(-S[r][k], S[c][k], S[r][c]);
+  // Right-looking Cholesky with UNSCALED columns and ONE barrier per column (the form validated in stb64_kernel's scalar
+  // path): S(t,k) holds L(t,k) L(k,k) until the end, so a step needs 1 / pivot only, which the thread that finishes the next
+  // pivot publishes before the barrier.  Thread = (row t, column class h = j mod 4).  (The scaled form with a CTA-wide
+  // trailing update took three barriers and a libm rsqrt on every thread per column: 87 us per 64 x 64 block.)
+  __shared__ double ip_s[SL_NB], rs_s[SL_NB];
+  {
+    const int t = tid & (SL_NB - 1), h = tid >> 6;
+    if (tid == 0) {
+      const double piv = S[0][0];
+      if (!(piv > 0.0)) atomicOr(status + ch, (uint32_t)ST_CHOL_FAIL);
+      ip_s[0] = 1.0 / piv; rs_s[0] = rsqrt(piv);
     }
+    __syncthreads();
+    for (int k = 0; k < nb - 1; ++k) {
+      if (t > k && t < nb) {
+        const double lip = S[t][k] * ip_s[k];
+        int j = k + 1 + ((h - (k + 1)) & 3);
+#pragma unroll 4
+        for (; j <= t; j += 4) S[t][j] = fma(-lip, S[j][k], S[t][j]);
+        if (t == k + 1 && h == ((k + 1) & 3)) {
+          const double piv = S[t][t];
+          if (!(piv > 0.0)) atomicOr(status + ch, (uint32_t)ST_CHOL_FAIL);
+          ip_s[k + 1] = 1.0 / piv; rs_s[k + 1] = rsqrt(piv);
+        }
+      }
+      __syncthreads();
+    }
+    for (int e = tid; e < nb * nb; e += SL_T) { const int r = e % nb, c = e / nb; if (r >= c) S[r][c] *= rs_s[c]; }
     __syncthreads();
   }
   for (int e = tid; e < nb * nb; e += SL_T) { const int r = e % nb, c = e / nb; if (r >= c) A[(k0 + r) + (size_t)(k0 + c) * P] = S[r][c]; }
