@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, double* 
     if (tid == 0) {
       const double piv = S[0][0];
       if (!(piv > 0.0)) atomicOr(status + ch, (uint32_t)ST_CHOL_FAIL);
-      ip_s[0] = 1.0 / piv; rs_s[0] = rsqrt(piv);
+      ip_s[0] = piv > 0.0 ? x_rcp(piv) : 1.0 / piv; rs_s[0] = piv > 0.0 ? x_rsqrt(piv) : rsqrt(piv);
     }
     __syncthreads();
     for (int k = 0; k < nb - 1; ++k) {
@@ -134,7 +134,7 @@ __global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, double* 
         if (t == k + 1 && h == ((k + 1) & 3)) {
           const double piv = S[t][t];
           if (!(piv > 0.0)) atomicOr(status + ch, (uint32_t)ST_CHOL_FAIL);
-          ip_s[k + 1] = 1.0 / piv; rs_s[k + 1] = rsqrt(piv);
+          ip_s[k + 1] = piv > 0.0 ? x_rcp(piv) : 1.0 / piv; rs_s[k + 1] = piv > 0.0 ? x_rsqrt(piv) : rsqrt(piv);
         }
       }
       __syncthreads();
@@ -143,27 +143,57 @@ __global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, double* 
     __syncthreads();
   }
   for (int e = tid; e < nb * nb; e += SL_T) { const int r = e % nb, c = e / nb; if (r >= c) A[(k0 + r) + (size_t)(k0 + c) * P] = S[r][c]; }
-  // W = L^-1 (lower): W(c,c) = 1/L(c,c), W(r,c) = -(sum_{m=c}^{r-1} L(r,m) W(m,c)) / L(r,r), row by row.  FOUR lanes per column
-  // split the dot product of a row (one thread per column walked 2000 dependent shared-memory steps, the longest chain of
-  // the kernel); the panel solve below the block is then a DMMA product with W' (stbl_trsm_kernel).
+  // W = L^-1 (lower), by 8 x 8 blocks: the eight diagonal blocks are inverted independently (one thread per column, 1 / L(r,r) is
+  // the rs of the factorisation: no division), then block row i = 1..7:  T(i,j) = sum_{k=j}^{i-1} L(i,k) W(k,j)  for all j < i
+  // (one output element per thread), W(i,j) = -W(i,i) T(i,j).  Depth 8 x (a 56-term dot product + an 8-term one) instead of the
+  // 64 dependent rows of a plain forward substitution.  The panel solve below the block is a DMMA product with W' (stbl_trsm_kernel).
+  __shared__ double Tt[8][SL_NB];
   __syncthreads();
   for (int e = tid; e < SL_NB * SL_NB; e += SL_T) Wm[e / SL_NB][e % SL_NB] = 0.0;
   __syncthreads();
-  {
-    const int c = tid >> 2, q = tid & 3;            // SL_T = 256 = 64 columns x 4 lanes; a column's lanes share a warp
-    for (int r = 0; r < nb; ++r) {                  // uniform trip count: the shuffles and __syncwarp need every lane
-      double part = 0.0;
-      if (c < r) for (int m = c + q; m < r; m += 4) part = fma(S[r][m], Wm[m][c], part);
-      part += __shfl_xor_sync(0xffffffffu, part, 1);
-      part += __shfl_xor_sync(0xffffffffu, part, 2);
-      if (q == 0 && c < nb) {
-        if (r == c) Wm[r][c] = 1.0 / S[c][c];
-        else if (r > c) Wm[r][c] = -part / S[r][r];
+  if (tid < SL_NB) {
+    const int base = tid & ~7, c = tid & 7;
+    if (base + c < nb) {
+      double w[8];
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        w[r] = 0.0;
+        if (r == c) w[r] = rs_s[base + c];
+        else if (r > c && base + r < nb) {
+          double sum = 0.0;
+#pragma unroll
+          for (int m = 0; m < 8; ++m) if (m >= c && m < r) sum = fma(S[base + r][base + m], w[m], sum);
+          w[r] = -sum * rs_s[base + r];
+        }
       }
-      __syncwarp();
+#pragma unroll
+      for (int r = 0; r < 8; ++r) if (r >= c && base + r < nb) Wm[base + r][base + c] = w[r];
     }
   }
   __syncthreads();
+  for (int i = 1; 8 * i < nb; ++i) {
+    for (int e = tid; e < 64 * i; e += SL_T) {
+      const int r = e & 7, cc = e >> 3;              // row 8 i + r of L, column cc < 8 i of W
+      double sum = 0.0;
+      if (8 * i + r < nb) {
+        const double* lrow = &S[8 * i + r][0];
+#pragma unroll 4
+        for (int m = cc; m < 8 * i; ++m) sum = fma(lrow[m], Wm[m][cc], sum);   // W(m,cc) = 0 for m < cc
+      }
+      Tt[r][cc] = sum;
+    }
+    __syncthreads();
+    for (int e = tid; e < 64 * i; e += SL_T) {
+      const int r = e & 7, cc = e >> 3;
+      if (8 * i + r < nb) {
+        double sum = 0.0;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) if (q <= r) sum = fma(Wm[8 * i + r][8 * i + q], Tt[q][cc], sum);
+        Wm[8 * i + r][cc] = -sum;
+      }
+    }
+    __syncthreads();
+  }
   double* W = Wall + (size_t)ch * SL_NB * SL_NB;
   for (int e = tid; e < SL_NB * SL_NB; e += SL_T) { const int r = e % SL_NB, c = e / SL_NB; W[e] = Wm[r][c]; }
 }
