@@ -139,7 +139,7 @@ bool model_factor_chol(bb_model* m) {
   const char* env = std::getenv("BB_SVD_DIRECT");
   if (env && env[0] == '1') return false;
   double* W = dalloc<double>((size_t)P * P);
-  double* Winv = dalloc<double>(64 * 64);
+  double* Winv = dalloc<double>((size_t)((P + 63) / 64) * 64 * 64);
   uint32_t* d_status = dalloc<uint32_t>(1);
   double* nrm = dalloc<double>(P);
   int* d_perm = dalloc<int>(P);
@@ -332,7 +332,7 @@ void chains_run(bb_chains* c, const bb_hyper* hh, unsigned iter0, int niter, int
     L.sink = make_sink(c, thin, slot0);
     launched(bb::launch_stb_small(L, st));
   } else {
-    if (!c->A) { c->A = dalloc<double>((size_t)c->nchains * P * P); c->W = dalloc<double>((size_t)c->nchains * 64 * 64); }
+    if (!c->A) { c->A = dalloc<double>((size_t)c->nchains * P * P); c->W = dalloc<double>((size_t)c->nchains * ((P + 63) / 64) * 64 * 64); }
     bb::StbLargeLaunch L;
     L.m = m->view(); L.h = h; L.key = key; L.nchains = c->nchains; L.chain0 = c->chain0; L.stages = stages;
     L.beta = c->beta; L.lambda = c->aux; L.sig2 = c->sig2; L.tau = c->tau; L.alpha = c->alpha; L.status = c->status;
@@ -361,7 +361,7 @@ void chains_run(bb_chains* c, const bb_hyper* hh, unsigned iter0, int niter, int
       const size_t o1 = (size_t)h0, oP = (size_t)h0 * P;
       H.nchains = h1 - h0; H.chain0 = L.chain0 + (uint32_t)h0;
       H.beta += oP; H.lambda += oP; H.sig2 += o1; H.tau += o1; H.alpha += o1; H.status += o1;
-      H.A += oP * P; H.W += o1 * 64 * 64;
+      H.A += oP * P; H.W += o1 * ((P + 63) / 64) * 64 * 64;
       const size_t os = o1 * (size_t)H.sink.chain_stride;
       if (H.sink.beta) H.sink.beta += os * P;
       if (H.sink.lambda) H.sink.lambda += os * P;

@@ -7,7 +7,7 @@ namespace bb {
 
 void stb_large_prepare(int P) {
   const size_t smem_sc = ((size_t)P + 26) * sizeof(double) + ((size_t)3 * P + 2) * sizeof(int);
-  const size_t smem_sv = ((size_t)P + SL_NB * (SL_NB + 1) + SL_NB) * sizeof(double);
+  const size_t smem_sv = ((size_t)P + SL_NB * (SL_NB + 1) + 16 * SL_NB) * sizeof(double);
   const size_t smem_sy = (size_t)2 * SL_NB * SL_LD * sizeof(double);
   const size_t smem_pf = (size_t)2 * SL_NB * (SL_NB + 1) * sizeof(double);
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_potrf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pf));
@@ -34,7 +34,7 @@ static int launch_update(double* A, int P, int kb, int nblk, int nch, cudaStream
 int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
   const int P = L.m.P, nch = L.nchains;
   const size_t smem_sc = ((size_t)P + 26) * sizeof(double) + ((size_t)3 * P + 2) * sizeof(int);
-  const size_t smem_sv = ((size_t)P + SL_NB * (SL_NB + 1) + SL_NB) * sizeof(double);
+  const size_t smem_sv = ((size_t)P + SL_NB * (SL_NB + 1) + 16 * SL_NB) * sizeof(double);
   const size_t smem_sy = (size_t)2 * SL_NB * SL_LD * sizeof(double);
   const int nblk = (P + SL_NB - 1) / SL_NB;
   int n = 0;
@@ -59,6 +59,7 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
 // Cholesky of ONE P x P matrix with the same kernels (a batch of one chain): on return the lower triangle of A
 // holds L (A = L L'), the strict upper triangle still holds the input.  Winv: 64 x 64 scratch, status: one word,
 // ST_CHOL_FAIL is set when a pivot is not positive.  Used by the Cholesky-preconditioned SVD of the constructor.
+// Winv: ceil(P / 64) x 64 x 64 scratch (the inverses of all diagonal blocks of the factor are kept)
 int chol_lower_device(double* A, int P, double* Winv, uint32_t* status, cudaStream_t st) {
   stb_large_prepare(P);
   const size_t smem_sy = (size_t)2 * SL_NB * SL_LD * sizeof(double);

@@ -194,7 +194,7 @@ __global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, double* 
     }
     __syncthreads();
   }
-  double* W = Wall + (size_t)ch * SL_NB * SL_NB;
+  double* W = Wall + ((size_t)ch * ((P + SL_NB - 1) / SL_NB) + kb) * SL_NB * SL_NB;   // kept per block column: the solve kernel uses them all
   for (int e = tid; e < SL_NB * SL_NB; e += SL_T) { const int r = e % SL_NB, c = e / SL_NB; W[e] = Wm[r][c]; }
 }
 
@@ -207,7 +207,7 @@ __global__ void __launch_bounds__(256) stbl_trsm_kernel(double* Aall, const doub
   double* Bs = smem + SL_NB * SL_LD;
   const int ch = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   double* A = Aall + (size_t)ch * P * P;
-  const double* W = Wall + (size_t)ch * SL_NB * SL_NB;
+  const double* W = Wall + ((size_t)ch * ((P + SL_NB - 1) / SL_NB) + kb) * SL_NB * SL_NB;
   const int k0 = kb * SL_NB, nb = min(SL_NB, P - k0);
   const int i0 = k0 + SL_NB + blockIdx.x * SL_NB;
   for (int e = tid; e < SL_NB * SL_NB; e += 256) {
@@ -353,29 +353,39 @@ __global__ void __launch_bounds__(SV_T) stbl_solve_kernel(const StbLargeLaunch L
   const int P = L.m.P, tid = threadIdx.x, ch = blockIdx.x;
   if (ch >= L.nchains) return;
   double* x = smem;                 // [P]
-  double* D = x + P;                // [64][65] diagonal block of the factor, staged so that the 64 dependent
-  double* ps = D + SL_NB * (SL_NB + 1);   // pivot steps read shared memory, not HBM;  [64] partial dot products
+  double* D = x + P;                // [64][65] inverse W = L_kk^-1 of the current diagonal block (from stbl_potrf_kernel)
+  double* ps = D + SL_NB * (SL_NB + 1);   // [16][64] partial sums of the 64 x 64 matrix-vector products
   const double* A = L.A + (size_t)ch * P * P;
+  const int nblk = (P + SL_NB - 1) / SL_NB;
+  const double* Wg = L.W + (size_t)ch * nblk * SL_NB * SL_NB;
   const uint32_t gch = L.chain0 + (uint32_t)ch;
   const int lane = tid & 31, warp = tid >> 5;
+  const int vr = tid & (SL_NB - 1), vp = tid >> 6;     // matrix-vector product: index vr, 16 parts of 4 terms (SV_T = 1024)
   const double sig = sqrt(L.sig2[ch]);
   for (int j = tid; j < P; j += SV_T) x[j] = __ldg(L.m.Xy + j);
-  auto stage_diag = [&](int k0, int nb) {
-    for (int e = tid; e < nb * nb; e += SV_T) { const int r = e % nb, c = e / nb; D[r * (SL_NB + 1) + c] = A[(k0 + r) + (size_t)(k0 + c) * P]; }
+  // The diagonal blocks are applied as products with their inverses (rows / columns beyond the matrix are zero in W): a 64-term
+  // dot product per unknown, all unknowns of the block at once, instead of 64 dependent substitution steps with a division each.
+  auto stage_w = [&](int kb) {
+    const double* W = Wg + (size_t)kb * SL_NB * SL_NB;
+    for (int e = tid; e < SL_NB * SL_NB; e += SV_T) D[(e & (SL_NB - 1)) * (SL_NB + 1) + (e >> 6)] = W[e];   // W[e] = W(e % 64, e / 64)
   };
   // forward: L w = Xy, column-oriented
   for (int k0 = 0; k0 < P; k0 += SL_NB) {
     const int nb = min(SL_NB, P - k0);
-    stage_diag(k0, nb);
+    stage_w(k0 / SL_NB);
     __syncthreads();
-    if (tid < 32) {   // diagonal block by one warp
-      for (int k = 0; k < nb; ++k) {
-        const double xk = x[k0 + k] / D[k * (SL_NB + 1) + k];
-        __syncwarp();
-        if (tid == 0) x[k0 + k] = xk;
-        for (int r = k + 1 + tid; r < nb; r += 32) x[k0 + r] = fma(-D[r * (SL_NB + 1) + k], xk, x[k0 + r]);
-        __syncwarp();
-      }
+    {   // w_blk = W x_blk
+      double s = 0.0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) { const int c = 4 * vp + q; if (c < nb) s = fma(D[vr * (SL_NB + 1) + c], x[k0 + c], s); }
+      ps[vp * SL_NB + vr] = s;
+    }
+    __syncthreads();
+    if (tid < nb) {
+      double s = 0.0;
+#pragma unroll
+      for (int q = 0; q < 16; ++q) s += ps[q * SL_NB + tid];
+      x[k0 + tid] = s;
     }
     __syncthreads();
     for (int r = k0 + nb + tid; r < P; r += SV_T) {   // rows below: coalesced along r
@@ -389,10 +399,10 @@ __global__ void __launch_bounds__(SV_T) stbl_solve_kernel(const StbLargeLaunch L
   for (int j = tid; j < P; j += SV_T) { Stream s(L.key, gch, L.iter, ST_BETA_STB, (uint32_t)j); x[j] = fma(sig, s.norm(0), x[j]); }
   __syncthreads();
   // backward: L' b = x over the stored lower triangle: column k of L is contiguous, one warp per column, lanes along r
-  const int nblk = (P + SL_NB - 1) / SL_NB;
+  double* pk = ps + 15 * SL_NB;     // [64] column sums (the last part of ps is free until the product below)
   for (int kbk = nblk - 1; kbk >= 0; --kbk) {
     const int k0 = kbk * SL_NB, nb = min(SL_NB, P - k0);
-    stage_diag(k0, nb);
+    stage_w(kbk);
     for (int kk = warp; kk < nb; kk += SV_T / 32) {
       const double* col = A + (size_t)(k0 + kk) * P;
       double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
@@ -403,19 +413,24 @@ __global__ void __launch_bounds__(SV_T) stbl_solve_kernel(const StbLargeLaunch L
       }
       for (; r < P; r += 32) s0 = fma(col[r], x[r], s0);
       const double sum = warp_sum((s0 + s1) + (s2 + s3));
-      if (lane == 0) ps[kk] = sum;
+      if (lane == 0) pk[kk] = sum;
     }
     __syncthreads();
-    if (tid < nb) x[k0 + tid] -= ps[tid];
+    if (tid < nb) x[k0 + tid] -= pk[tid];
     __syncthreads();
-    if (tid < 32) {
-      for (int k = nb - 1; k >= 0; --k) {
-        const double xk = x[k0 + k] / D[k * (SL_NB + 1) + k];
-        __syncwarp();
-        if (tid == 0) x[k0 + k] = xk;
-        for (int r = tid; r < k; r += 32) x[k0 + r] = fma(-D[k * (SL_NB + 1) + r], xk, x[k0 + r]);
-        __syncwarp();
-      }
+    {   // b_blk = W' x_blk
+      double s = 0.0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) { const int r = 4 * vp + q; if (r < nb) s = fma(D[r * (SL_NB + 1) + vr], x[k0 + r], s); }
+      __syncthreads();               // pk (inside ps) has been read by everyone
+      ps[vp * SL_NB + vr] = s;
+    }
+    __syncthreads();
+    if (tid < nb) {
+      double s = 0.0;
+#pragma unroll
+      for (int q = 0; q < 16; ++q) s += ps[q * SL_NB + tid];
+      x[k0 + tid] = s;
     }
     __syncthreads();
   }
