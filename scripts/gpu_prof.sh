@@ -9,7 +9,7 @@ CMD="python bench.py --workload $W --steps 3 --warmup 3 --no-cpu --no-ess --e2e-
 $CMD > gpurun_out/plain_$TAG.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file gpurun_out/launches_$TAG.csv $CMD > gpurun_out/ncu_launches_$TAG.log 2>&1
 $CMD > gpurun_out/plain2_$TAG.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:$K -s 4 -c 1 -o /tmp/prof_$TAG $CMD > gpurun_out/ncu_full_$TAG.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:$K -s ${SKIP:-4} -c 1 -o /tmp/prof_$TAG $CMD > gpurun_out/ncu_full_$TAG.log 2>&1
 if [ -f /tmp/prof_$TAG.ncu-rep ]; then
   ncu -i /tmp/prof_$TAG.ncu-rep --page raw --csv > gpurun_out/raw_$TAG.csv 2>/dev/null
   ncu -i /tmp/prof_$TAG.ncu-rep --page details --csv > gpurun_out/details_$TAG.csv 2>/dev/null
