@@ -38,6 +38,9 @@ def _worker(rank, world, port, q):
     Zf = np.column_stack([X, y])
     ok_gram = np.allclose(G.numpy(), Zf.T @ Zf)
     t = bdist.max_over_ranks(1.0 + r)
+    # per-coefficient ESS of sharded chains adds up over the ranks (bench.py's ESS/sec)
+    e = bdist.sum_over_ranks(np.arange(5, dtype=np.float64) * (1 + r))
+    ok_gram = ok_gram and np.allclose(e, np.arange(5) * 3.0)
     bdist.barrier()
     q.put((rank, lo, hi, ok_bcast, ok_gram, t))
     dist.destroy_process_group()
