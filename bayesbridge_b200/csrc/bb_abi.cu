@@ -224,7 +224,7 @@ struct bb_chains {
   double *beta = nullptr, *u = nullptr, *aux = nullptr, *shape = nullptr, *z = nullptr;
   double *sig2 = nullptr, *tau = nullptr, *alpha = nullptr;
   uint32_t* status = nullptr;
-  double *A = nullptr, *W = nullptr;        // large-P stable workspace: factors, inverse diagonal blocks
+  double *A = nullptr, *W = nullptr, *Q = nullptr;   // large-P stable workspace: factors, inverse diagonal blocks, partial sums of d'X'Xd
   // draw buffer
   long long nslots = 0; int out_mask = 0;
   double *o_beta = nullptr, *o_u = nullptr, *o_omega = nullptr, *o_shape = nullptr, *o_lambda = nullptr;
@@ -235,7 +235,7 @@ struct bb_chains {
   void free_draws() { dfree(o_beta); dfree(o_u); dfree(o_omega); dfree(o_shape); dfree(o_lambda); dfree(o_sig2); dfree(o_tau); dfree(o_alpha); nslots = 0; out_mask = 0; }
   ~bb_chains() {
     cudaSetDevice(device);
-    dfree(beta); dfree(u); dfree(aux); dfree(shape); dfree(z); dfree(sig2); dfree(tau); dfree(alpha); dfree(status); dfree(A); dfree(W);
+    dfree(beta); dfree(u); dfree(aux); dfree(shape); dfree(z); dfree(sig2); dfree(tau); dfree(alpha); dfree(status); dfree(A); dfree(W); dfree(Q);
     free_draws();
     if (ev0) cudaEventDestroy(ev0);
     if (ev1) cudaEventDestroy(ev1);
@@ -332,11 +332,12 @@ void chains_run(bb_chains* c, const bb_hyper* hh, unsigned iter0, int niter, int
     L.sink = make_sink(c, thin, slot0);
     launched(bb::launch_stb_small(L, st));
   } else {
-    if (!c->A) { c->A = dalloc<double>((size_t)c->nchains * P * P); c->W = dalloc<double>((size_t)c->nchains * ((P + 63) / 64) * 64 * 64); }
+    if (!c->A) { c->A = dalloc<double>((size_t)c->nchains * P * P); c->W = dalloc<double>((size_t)c->nchains * ((P + 63) / 64) * 64 * 64); if (P >= 512) c->Q = dalloc<double>((size_t)c->nchains * ((P + 31) / 32)); }
+    // (Q: the batched d'X'Xd kernel pays from P = 512 on; at P = 256 the extra launch costs more than the per-chain loop: c5s 112 -> 109 M)
     bb::StbLargeLaunch L;
     L.m = m->view(); L.h = h; L.key = key; L.nchains = c->nchains; L.chain0 = c->chain0; L.stages = stages;
     L.beta = c->beta; L.lambda = c->aux; L.sig2 = c->sig2; L.tau = c->tau; L.alpha = c->alpha; L.status = c->status;
-    L.A = c->A; L.W = c->W; L.sink = make_sink(c, thin, slot0);
+    L.A = c->A; L.W = c->W; L.Q = c->Q; L.sink = make_sink(c, thin, slot0);
     bb::stb_large_prepare(P);
     // Sub-batches on their own streams: the low-parallelism kernels of one sub-batch (diagonal-block factorisation, panel
     // solve, substitution: one CTA per chain) run while another sub-batch's update kernel fills the SMs.  The sub-batches
@@ -361,7 +362,7 @@ void chains_run(bb_chains* c, const bb_hyper* hh, unsigned iter0, int niter, int
       const size_t o1 = (size_t)h0, oP = (size_t)h0 * P;
       H.nchains = h1 - h0; H.chain0 = L.chain0 + (uint32_t)h0;
       H.beta += oP; H.lambda += oP; H.sig2 += o1; H.tau += o1; H.alpha += o1; H.status += o1;
-      H.A += oP * P; H.W += o1 * ((P + 63) / 64) * 64 * 64;
+      H.A += oP * P; H.W += o1 * ((P + 63) / 64) * 64 * 64; if (H.Q) H.Q += o1 * ((P + 31) / 32);
       const size_t os = o1 * (size_t)H.sink.chain_stride;
       if (H.sink.beta) H.sink.beta += os * P;
       if (H.sink.lambda) H.sink.lambda += os * P;

@@ -64,7 +64,8 @@ struct StbLargeLaunch {
   double *beta, *lambda, *sig2, *tau, *alpha;
   uint32_t* status;
   double* A;               // [nchains][P][P] column-major workspace (lower triangle holds L)
-  double* W;               // [nchains][64][64] inverse of the current diagonal block of the factor (column-major)
+  double* W;               // [nchains][P/64][64][64] inverses of the diagonal blocks of the factor (column-major)
+  double* Q;               // [nchains][ceil(P/32)] partial sums of d'X'Xd, d = beta - bc (stbl_quad_kernel), or null
   DrawSink sink;
   long long slot;          // sink slot for this iteration, -1 = do not store
 };

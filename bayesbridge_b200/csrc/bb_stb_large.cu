@@ -39,6 +39,10 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
   const int nblk = (P + SL_NB - 1) / SL_NB;
   int n = 0;
   const bool do_alpha = (L.stages & 64) && !(L.h.true_alpha > 0) && !L.pre;
+  if (L.Q != nullptr && (L.stages & 2) && !(L.h.true_sig2 > 0) && !L.pre) {
+    const int nstrips = (P + QD_R - 1) / QD_R;
+    stbl_quad_kernel<<<dim3(nstrips, (nch + 31) / 32), 256, 0, st>>>(L, nstrips); ++n;
+  }
   stbl_scalar_kernel<<<nch, SL_T, smem_sc, st>>>(L); ++n;
   if (L.pre || !beta_stage) {
     if (do_alpha) { stbl_alpha_kernel<<<(nch + 7) / 8, 256, 0, st>>>(L); ++n; }
