@@ -175,34 +175,49 @@ __global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, double* 
   const int k0 = kb * SL_NB, nb = min(SL_NB, P - k0);
   for (int e = tid; e < nb * nb; e += SL_T) { const int r = e % nb, c = e / nb; S[r][c] = A[(k0 + r) + (size_t)(k0 + c) * P]; }
   __syncthreads();
-  // Right-looking Cholesky with UNSCALED columns and ONE barrier per column (the form validated in stb64_kernel's scalar
-  // path): S(t,k) holds L(t,k) L(k,k) until the end, so a step needs 1 / pivot only, which the thread that finishes the next
-  // pivot publishes before the barrier.  Thread = (row t, column class h = j mod 4).  (The scaled form with a CTA-wide
-  // trailing update took three barriers and a libm rsqrt on every thread per column: 87 us per 64 x 64 block.)
-  __shared__ double ip_s[SL_NB], rs_s[SL_NB];
+  // Right-looking Cholesky with UNSCALED columns, ONE barrier per column and the matrix in REGISTERS: thread (row t, class h)
+  // owns S(t,j) for j = h, h + 4, ... (16 values, static indices: the 64 steps are unrolled).  Step k: the owners of column k
+  // publish it (64 values, double-buffered), barrier, every thread takes 1 / pivot and its multiplier from the published column
+  // and updates its own entries -- no read-modify-write through shared memory, no single thread computing the pivot for all.
+  // (History: a scaled form with a CTA-wide trailing update, three barriers and a libm rsqrt per column: 87 us per 64 x 64
+  // block; unscaled columns through shared memory, one barrier: 50 us, bound by dependent shared-memory round trips.)
+  // Rows / columns beyond the matrix are padded with the identity.
+  __shared__ double rs_s[SL_NB], colbuf[2][SL_NB];
   {
     const int t = tid & (SL_NB - 1), h = tid >> 6;
-    if (tid == 0) {
-      const double piv = S[0][0];
-      if (!(piv > 0.0)) atomicOr(status + ch, (uint32_t)ST_CHOL_FAIL);
-      ip_s[0] = piv > 0.0 ? x_rcp(piv) : 1.0 / piv; rs_s[0] = piv > 0.0 ? x_rsqrt(piv) : rsqrt(piv);
+    double rv[16];
+#pragma unroll
+    for (int v = 0; v < 16; ++v) {
+      const int j = h + 4 * v;
+      rv[v] = (t < nb && j < nb) ? S[t][j] : (t == j ? 1.0 : 0.0);
     }
-    __syncthreads();
-    for (int k = 0; k < nb - 1; ++k) {
-      if (t > k && t < nb) {
-        const double lip = S[t][k] * ip_s[k];
-        int j = k + 1 + ((h - (k + 1)) & 3);
-#pragma unroll 4
-        for (; j <= t; j += 4) S[t][j] = fma(-lip, S[j][k], S[t][j]);
-        if (t == k + 1 && h == ((k + 1) & 3)) {
-          const double piv = S[t][t];
-          if (!(piv > 0.0)) atomicOr(status + ch, (uint32_t)ST_CHOL_FAIL);
-          ip_s[k + 1] = piv > 0.0 ? x_rcp(piv) : 1.0 / piv; rs_s[k + 1] = piv > 0.0 ? x_rsqrt(piv) : rsqrt(piv);
+    bool bad = false;
+#pragma unroll
+    for (int u = 0; u < 16; ++u) {
+#pragma unroll
+      for (int hh = 0; hh < 4; ++hh) {
+        const int k = 4 * u + hh;
+        if (h == hh) colbuf[k & 1][t] = rv[u];          // column k: S(t,k) L-unscaled, S(k,k) = pivot
+        __syncthreads();
+        const double piv = colbuf[k & 1][k];
+        if (t == k && h == hh) { rs_s[k] = piv > 0.0 ? x_rsqrt(piv) : rsqrt(piv); bad = bad || !(piv > 0.0); }
+        if (t > k) {
+          const double lip = colbuf[k & 1][t] * (piv > 0.0 ? x_rcp(piv) : 1.0 / piv);
+#pragma unroll
+          for (int v = u; v < 16; ++v) {
+            const int j = h + 4 * v;
+            if (j > k && j <= t) rv[v] = fma(-lip, colbuf[k & 1][j], rv[v]);
+          }
         }
       }
-      __syncthreads();
     }
-    for (int e = tid; e < nb * nb; e += SL_T) { const int r = e % nb, c = e / nb; if (r >= c) S[r][c] *= rs_s[c]; }
+    if (bad) atomicOr(status + ch, (uint32_t)ST_CHOL_FAIL);
+    __syncthreads();
+#pragma unroll
+    for (int v = 0; v < 16; ++v) {
+      const int j = h + 4 * v;
+      if (t < nb && j <= t) S[t][j] = rv[v] * rs_s[j];
+    }
     __syncthreads();
   }
   for (int e = tid; e < nb * nb; e += SL_T) { const int r = e % nb, c = e / nb; if (r >= c) A[(k0 + r) + (size_t)(k0 + c) * P] = S[r][c]; }
