@@ -39,7 +39,7 @@ WORKLOADS = {
     "c1": dict(desc="bridge.reg.tri n=442 p=64 alpha=0.5, 1 chain", chains=1, iters=2000),
     "c2": dict(desc="bridge.reg.stb n=442 p=64 alpha=0.5, 512 chains/GPU", chains=512, iters=200),
     "c3": dict(desc="bridge.reg.tri n=10000 p=1000 alpha=0.5, 512 chains/GPU (4096 on 8)", chains=512, iters=40),
-    "c4": dict(desc="bridge.reg.stb n=500 p=2000 alpha=0.25 (p>n), 128 chains/GPU (1024 on 8)", chains=128, iters=2),
+    "c4": dict(desc="bridge.reg.stb n=500 p=2000 alpha=0.25 (p>n), 128 chains/GPU (1024 on 8)", chains=128, iters=4),
     "c5": dict(desc="bridge.reg.tri n=100000 p=256 alpha=0.5 row-sharded Gram, 256 chains/GPU", chains=256, iters=100),
     "c5s": dict(desc="bridge.reg.stb n=100000 p=256 alpha=0.5 row-sharded Gram, 256 chains/GPU", chains=256, iters=20),
 }
