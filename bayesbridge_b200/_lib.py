@@ -23,7 +23,7 @@ OUT_BETA, OUT_U, OUT_OMEGA, OUT_SHAPE, OUT_LAMBDA, OUT_SIG2, OUT_TAU, OUT_ALPHA 
 # every symbol include/bayesbridge_b200.h declares
 EXPORTS = [
     "bridge_regression", "bridge_reg_stable", "bb_set_seed", "bb_set_device", "bb_set_verbose",
-    "bb_last_error", "bb_device_count", "bb_model_create", "bb_model_create_factors", "bb_gram",
+    "bb_last_error", "bb_device_count", "bb_model_create", "bb_model_create_factors", "bb_gram", "bb_gram_noalloc",
     "bb_model_create_gram", "bb_model_resid_partial", "bb_model_set_r0", "bb_model_free", "bb_model_get",
     "bb_model_precompute_ms", "bb_chains_create", "bb_chains_free", "bb_chains_set", "bb_chains_get", "bb_chains_alpha",
     "bb_chains_reserve", "bb_chains_run", "bb_chains_store_state", "bb_chains_fetch", "bb_chains_summary", "bb_launch_count",
@@ -67,6 +67,7 @@ def load():
     L.bb_model_create_factors.restype = vp
     L.bb_model_create_factors.argtypes = [vp, vp, C.c_int, C.c_int, dp, dp, dp, dp, C.c_int, C.c_int]
     L.bb_gram.argtypes = [vp, vp, C.c_int, C.c_int, vp, C.c_int]
+    L.bb_gram_noalloc.argtypes = [vp, vp, C.c_int, C.c_int, vp, C.c_int]
     L.bb_model_create_gram.restype = vp
     L.bb_model_create_gram.argtypes = [vp, C.c_int, C.c_int, C.c_int]
     L.bb_model_resid_partial.argtypes = [vp, vp, vp, C.c_int, vp]

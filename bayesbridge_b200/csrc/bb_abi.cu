@@ -503,6 +503,17 @@ int bb_gram(const double* X_dev, const double* y_dev, int n_rows, int P, double*
   });
 }
 
+// No counterpart in the reference: bb_gram for callers that must not allocate (see include/bayesbridge_b200.h).
+// Size checks come first (no CUDA call is made for a refused size); no cudaMalloc / cudaFree / pool call on this path.
+int bb_gram_noalloc(const double* X_dev, const double* y_dev, int n_rows, int P, double* G_dev, int device) {
+  return guarded([&] {
+    if (n_rows < 1 || P < 1) throw std::string("bb_gram_noalloc: n_rows and P must be positive");
+    if (P > 3071) throw std::string("bb_gram_noalloc: P = ") + std::to_string(P) + " exceeds the static scratch (P <= 3071); use bb_gram";
+    BB_CUDA_CHECK(cudaSetDevice(device));
+    launched(bb::gram_device_noalloc(X_dev, y_dev, n_rows, P, G_dev, nullptr));
+  });
+}
+
 bb_model* bb_model_create_gram(const double* G_dev, int N, int P, int device) {
   bb_model* m = nullptr;
   const int rc = guarded([&] {

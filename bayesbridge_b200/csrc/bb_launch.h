@@ -90,6 +90,7 @@ int summary_device(const double* draws, int P, long long chain_stride, long long
 
 // ---- one-time precompute (bb_pre.cu) ----
 int gram_device(const double* X, const double* y, int N, int P, double* G, cudaStream_t st);   // G = [X y]'[X y]
+int gram_device_noalloc(const double* X, const double* y, int N, int P, double* G, cudaStream_t st);   // same, partial tiles in a static __device__ array
 int gram_unpack(const double* G, int P, double* XX, double* Xy, double* yy_dev, cudaStream_t st);
 int jacobi_device(double* W, double* V, int M, int P, cudaStream_t st);
 double resid_device(const double* X, const double* y, const double* b, int N, int P, cudaStream_t st, int* launches);

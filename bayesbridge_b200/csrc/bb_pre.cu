@@ -5,7 +5,17 @@
 #include <cstdlib>
 #include <cstring>
 #include <vector>
+#include <mutex>
+#include <string>
 #include "bb_pre.cuh"
+
+// Scratch of bb_gram_noalloc (the split-K partial tiles of gram_kernel): one file-scope array per GPU that loads this
+// library, held until the process exits.  1184 tiles of 64 x 64 doubles = 37 MiB: enough for every P <= 3071 at any
+// number of rows (slots = tiles x row splits <= 591 + tiles while the grid is being filled, = tiles beyond that).
+// In HOST code this name is only a stand-in for the symbol -- the device address comes from cudaGetSymbolAddress, below.
+constexpr int BB_GRAM_NOALLOC_MAX_P = 3071;
+constexpr size_t BB_GRAM_NOALLOC_SLOTS = 1184;
+static __device__ __align__(256) double g_gram_noalloc_scratch[BB_GRAM_NOALLOC_SLOTS * bb::GR_T * bb::GR_T];
 
 namespace bb {
 
@@ -27,6 +37,51 @@ int gram_device(const double* X, const double* y, int N, int P, double* G, cudaS
   check_launch();
   BB_CUDA_CHECK(cudaStreamSynchronize(st));
   dfree(part);
+  return 2;
+}
+
+// Device address of g_gram_noalloc_scratch on the CURRENT device, looked up once per device.
+static double* gram_noalloc_scratch_ptr() {
+  static std::mutex mu;
+  static double* ptr[64] = {};
+  int dev = -1;
+  BB_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) throw std::string("bb_gram_noalloc: device index out of range");
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptr[dev]) {
+    double* p = nullptr;
+    BB_CUDA_CHECK(cudaGetSymbolAddress((void**)&p, g_gram_noalloc_scratch));
+    if (!p) throw std::string("bb_gram_noalloc: cudaGetSymbolAddress returned a null address");
+    ptr[dev] = p;
+  }
+  return ptr[dev];
+}
+
+// gram_device without any allocation: the same two kernels with the same row split (so the result is bit-identical),
+// the partial tiles in the static scratch.  gram_kernel writes every entry of every slot it is given before
+// gram_reduce_kernel reads them, so nothing has to be cleared between calls; two calls that overlap on one GPU would race
+// on the scratch.  The device must be current.
+int gram_device_noalloc(const double* X, const double* y, int N, int P, double* G, cudaStream_t st) {
+  if (N < 1 || P < 1) throw std::string("bb_gram_noalloc: n_rows and P must be positive");
+  if (P > BB_GRAM_NOALLOC_MAX_P)
+    throw std::string("bb_gram_noalloc: P = ") + std::to_string(P) + " exceeds the static scratch (P <= " +
+        std::to_string(BB_GRAM_NOALLOC_MAX_P) + "); use bb_gram";
+  // the split of gram_device (keep in step: tests/test_zz_no_alloc.py compares the two bit for bit)
+  const int PA = P + 1;
+  const int nt = (PA + GR_T - 1) / GR_T;
+  const int ntile = nt * (nt + 1) / 2;
+  int nsplit = std::max(1, std::min((N + 4 * GR_K - 1) / (4 * GR_K), (148 * 4 + ntile - 1) / ntile));
+  int rows = (N + nsplit - 1) / nsplit;
+  rows = (rows + GR_K - 1) / GR_K * GR_K;
+  nsplit = (N + rows - 1) / rows;
+  if (nsplit < 1) nsplit = 1;
+  if ((size_t)nsplit * ntile > BB_GRAM_NOALLOC_SLOTS) throw std::string("bb_gram_noalloc: problem exceeds the static scratch; use bb_gram");
+  double* part = gram_noalloc_scratch_ptr();
+  gram_kernel<<<dim3(ntile, 1, nsplit), 256, 0, st>>>(X, y, N, P, rows, part);
+  check_launch();
+  gram_reduce_kernel<<<296, 256, 0, st>>>(part, P, nsplit, G);
+  check_launch();
+  BB_CUDA_CHECK(cudaStreamSynchronize(st));
   return 2;
 }
 

@@ -128,6 +128,16 @@ bb_model *bb_model_create_factors(const double *X, const double *y, int N, int P
  * bb_model_create_gram builds the model from the reduced G (device memory), N = total rows. */
 int bb_gram(const double *X_dev, const double *y_dev, int n_rows, int P, double *G_dev, int device);
 bb_model *bb_model_create_gram(const double *G_dev, int N, int P, int device);
+/* bb_gram for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * No counterpart in the reference.  Same arguments, same kernels, same
+ * result bit for bit, but the split-K partial tiles live in a file-scope `static __device__` array of 37 MiB (1184
+ * tiles of 64 x 64 doubles) that every GPU loading the library holds until the process exits.  LIMIT: P <= 3071 (any
+ * n_rows); larger P returns 1 with bb_last_error() saying so, before any CUDA call.  The call makes no cudaMalloc /
+ * cudaFree / allocating library call; inputs and the output G are the caller's device buffers.  Every call on a GPU
+ * shares the one scratch array, which keeps the previous call's contents (every slot a call reads is rewritten by that
+ * call first, so nothing needs clearing): calls that overlap in time on the same GPU race -- serialise them.  The first
+ * call on a device also looks the array's address up (cudaGetSymbolAddress, once per device). */
+int bb_gram_noalloc(const double *X_dev, const double *y_dev, int n_rows, int P, double *G_dev, int device);
 /* residual sums of squares of a row shard at the two expansion centres -> out_dev[0..1] (device);
  * after the all-reduce, bb_model_set_r0 installs the totals. */
 int bb_model_resid_partial(const bb_model *m, const double *X_dev, const double *y_dev, int n_rows, double *out_dev);
