@@ -25,3 +25,26 @@ def ref():
     if not bb_oracle.ref_available() and not os.path.isdir("/root/reference/Code/C"):
         pytest.skip("oracle/_ref/libbb_ref.so not built (reference sources absent)")
     return bb_oracle.Ref()
+
+
+def pytest_sessionfinish(session, exitstatus):
+    """achieved parity errors of this session -> gpurun_out/parity_errors.json (merged with what is there)"""
+    import json
+    try:
+        from helpers import PARITY
+    except ImportError:
+        return
+    if not PARITY:
+        return
+    out = os.path.join(ROOT, "gpurun_out")
+    os.makedirs(out, exist_ok=True)
+    path = os.path.join(out, "parity_errors.json")
+    rows = {}
+    if os.path.exists(path):
+        try:
+            rows = {(r["row"], r["config"], r["against"]): r for r in json.load(open(path))}
+        except (ValueError, KeyError):
+            rows = {}
+    for (row, config, against), v in PARITY.items():
+        rows[(row, config, against)] = {"row": row, "config": config, "against": against, **v}   # the latest session wins
+    json.dump(sorted(rows.values(), key=lambda r: (r["row"], r["config"], r["against"])), open(path, "w"), indent=1)

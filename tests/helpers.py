@@ -1,5 +1,22 @@
 """Shared test helpers: small synthetic problems and state generators."""
+import os
+
 import numpy as np
+
+# Achieved parity errors of this pytest session: (row, config, against) -> max error seen.  tests/conftest.py writes them to
+# gpurun_out/parity_errors.json at the end of the session; scripts/make_parity_md.py turns that file into PARITY.md.
+PARITY = {}
+
+
+def check(row, config, err, tol, against="port"):
+    """Record the achieved error of one SURVEY section-8 row and assert it against `tol`.
+    BB_PARITY_RECORD_ONLY=1 records without asserting (used once to calibrate the tolerances)."""
+    err = float(err)
+    key = (row, str(config), against)
+    old = PARITY.get(key)
+    PARITY[key] = {"err": max(err, old["err"]) if old else err, "tol": tol, "n": (old["n"] + 1) if old else 1}
+    if not os.environ.get("BB_PARITY_RECORD_ONLY"):
+        assert err < tol, f"{row} [{config}] vs {against}: {err:.3e} >= {tol:.1e}"
 
 
 def small_problem(N, P, seed=0, rho=0.4, nnz=3, noise=0.3):
@@ -51,3 +68,16 @@ def teacher_forced_sweep_error(f, beta0, b, sig2, seed, chain, it, beta_dev):
         cur += v * (zdev[i] - z[i])
         z[i] = zdev[i]
     return worst
+
+
+def engines(port, X, y):
+    """(reference model | None, port model, factors): the reference's LAPACK factors when oracle/_ref is built, otherwise
+    the port's Jacobi factors; the port model always runs on the same factors as the device."""
+    import bb_oracle
+    if bb_oracle.ref_available():
+        rm = bb_oracle.Ref().model(X, y)
+        f = rm.factors()
+    else:
+        rm, f = None, port.model(X, y).factors()
+    pm = port.model(X, y, (f["tV"], f["d"], f["a"], f["bhat"]))
+    return rm, pm, f

@@ -63,8 +63,12 @@ def test_dropin_tri_posterior_vs_reference_golden():
     for j in range(b.shape[1]):
         se = np.hypot(_mcse(b[:, j]), g["drv_tri_sd"][j] / np.sqrt(200.0))
         assert abs(b[:, j].mean() - g["drv_tri_mean"][j]) < 4 * se + 1e-3 * g["drv_tri_sd"][j], j
-    assert abs(out["sig2"][1:].mean() / g["drv_tri_sig2"] - 1) < 0.05
-    assert abs(out["tau"][1:].mean() / g["drv_tri_tau"] - 1) < 0.15
+    # sig2 and tau: one reference run of 5000 draws is the only golden value for this 150 x 24 problem, so both sides carry
+    # Monte-Carlo error: 4 MCSE of the difference, the reference's MCSE taken equal to ours (same law, same run length).
+    # (The criterion proper -- means AND quantiles of beta, sig2, tau, replicated reference runs on the c1/c2 shape -- is
+    # test_posterior_means_and_quantiles_vs_reference_golden below.)
+    for k, gk in (("sig2", "drv_tri_sig2"), ("tau", "drv_tri_tau")):
+        assert abs(out[k][1:].mean() - g[gk]) < 4 * np.sqrt(2.0) * _mcse(out[k][1:]), k
     # layout of the .C arrays: sample 0 is the state after burn-in, shape in {1,2}, u in (0,1)
     assert set(np.unique(out["shape"][1:])) <= {1.0, 2.0}
     assert (out["u"][1:] >= 0).all() and (out["u"][1:] < 1).all()
@@ -79,8 +83,36 @@ def test_dropin_stb_posterior_vs_reference_golden():
     for j in range(b.shape[1]):
         se = np.hypot(_mcse(b[:, j]), g["drv_stb_sd"][j] / np.sqrt(1000.0))
         assert abs(b[:, j].mean() - g["drv_stb_mean"][j]) < 4 * se + 1e-3 * g["drv_stb_sd"][j], j
-    assert abs(out["sig2"][1:].mean() / g["drv_stb_sig2"] - 1) < 0.05
-    assert abs(out["tau"][1:].mean() / g["drv_stb_tau"] - 1) < 0.15
+    for k, gk in (("sig2", "drv_stb_sig2"), ("tau", "drv_stb_tau")):
+        assert abs(out[k][1:].mean() - g[gk]) < 4 * np.sqrt(2.0) * _mcse(out[k][1:]), k
+
+
+@pytest.mark.parametrize("method", ["triangle", "stable"])
+def test_posterior_means_and_quantiles_vs_reference_golden(method):
+    """north_star's end-to-end criterion as written: posterior means AND quantiles (Q.1, Q.9, the quantiles of sum.stat,
+    Code/R/PublicBenchmark.R:120-128) of every beta_j, of sig2 and of tau agree with the reference within 4 Monte-Carlo
+    standard errors, on the diabetes-shaped 442 x 64 design of configs c1 / c2.  Reference side: 32 independent runs of the
+    compiled reference drivers (tests/golden/posterior_c2.npz, made by make_posterior_golden.py); GPU side: 128 chains of
+    the batched driver (same schedule per chain).  Both standard errors come from the spread over independent chains, so
+    no autocorrelation model enters the test."""
+    import bayesbridge_b200 as bb
+    from bayesbridge_b200 import synth
+    g = np.load(os.path.join(os.path.dirname(GOLD), "posterior_c2.npz"))
+    ref = g["tri" if method == "triangle" else "stb"]                       # [nrep, 3, P + 2]
+    X, y, _ = synth.make("c2")
+    nch, nsamp = 128, 2501
+    out = bb.bridge_batched(y, X, nsamp, method=method, nchains=nch, seed=2024, burn=int(g["burn"]), alpha=float(g["alpha"]),
+                            want=("beta", "sig2", "tau"))
+    assert not out["status"].any()
+    M = np.concatenate([out["beta"][:, 1:], out["sig2"][:, 1:, None], out["tau"][:, 1:, None]], axis=2)   # [chain, sample, P + 2]
+    ours = np.stack([M.mean(1), np.quantile(M, 0.1, axis=1), np.quantile(M, 0.9, axis=1)], axis=1)      # [chain, 3, P + 2]
+    se = lambda a: a.std(0, ddof=1) / np.sqrt(a.shape[0])
+    z = np.abs(ours.mean(0) - ref.mean(0)) / np.hypot(se(ours), se(ref))
+    P = X.shape[1]
+    for k, name in enumerate(("mean", "Q.1", "Q.9")):
+        assert z[k, :P].max() < 4.0, (name, "beta", int(z[k, :P].argmax()), z[k, :P].max())
+        assert z[k, P] < 4.0, (name, "sig2", z[k, P])
+        assert z[k, P + 1] < 4.0, (name, "tau", z[k, P + 1])
 
 
 def test_device_factors_match_oracle(port):

@@ -10,7 +10,7 @@ c3 / c4 shapes, conditional by conditional), plus size-independent properties of
 import numpy as np
 import pytest
 
-from helpers import rel_err, teacher_forced_sweep_error
+from helpers import check, engines, rel_err, teacher_forced_sweep_error
 
 pytestmark = pytest.mark.gpu
 
@@ -18,18 +18,24 @@ SEED = 0xBADC0FFEE
 
 
 def test_c3_shape_tri_conditionals(port):
-    """n=10000, p=1000 (config c3): device factors (Jacobi SVD on the GPU) feed the oracle, then every
-    conditional of one iteration is compared for two chains; the sweep is checked draw by draw."""
+    """n=10000, p=1000 (config c3).  (1) The device's own factors (Gram on DMMA + Jacobi SVD) against LAPACK; (2) every
+    conditional of one iteration for two chains against the port AND the compiled reference (oracle/_ref) on the
+    reference's LAPACK factors; the sweep is checked draw by draw (teacher-forced)."""
     import bayesbridge_b200 as bb
     from bayesbridge_b200 import synth
     from bayesbridge_b200._lib import ST_BETA, ST_OMEGA, ST_SIG2, ST_TAU, ST_U
     X, y, _ = synth.make("c3")
     N, P = X.shape
-    model = bb.Model(X, y)
-    f = model.factors()
+    own = bb.Model(X, y)
+    fo = own.factors()
     sv = np.linalg.svd(X, compute_uv=False)
-    assert rel_err(f["d"], sv) < 1e-10
-    pm = port.model(X, y, (f["tV"], f["d"], f["a"], f["bhat"]))
+    check("a1 constructor: singular values", "c3 10000x1000", rel_err(fo["d"], sv), 1e-12, "LAPACK")
+    V = fo["tV"].T
+    check("a1 constructor: V diag(d^2) V' = X'X", "c3 10000x1000", rel_err((V * fo["d"] ** 2) @ V.T, X.T @ X), 1e-12, "LAPACK")
+    own.close()
+    rm, pm, f = engines(port, X, y)
+    engs = [(e, n) for e, n in ((pm, "port"), (rm, "reference")) if e is not None]
+    model = bb.Model(X, y, factors=f)
     nch, alpha, it = 2, 0.5, 7
     rng = np.random.default_rng(3)
     beta0 = f["bhat"][None, :] * (1 + 0.05 * rng.standard_normal((nch, P))) + 0.01 * rng.standard_normal((nch, P))
@@ -42,21 +48,25 @@ def test_c3_shape_tri_conditionals(port):
     ch.run(hyp, 1, it, ST_OMEGA); st = ch.get(); om, sh = st["aux"], st["shape"]
     ch.run(hyp, 1, it, ST_U); u1 = ch.get()["u"]
     ch.run(hyp, 1, it, ST_BETA); b1 = ch.get()["beta"]
+    cfg = "c3 tri 10000x1000 a=0.5"
     for c in range(nch):
-        assert rel_err(tau[c], pm.sample_tau_marg(beta0[c], alpha, 2.0, 2.0, SEED, 11 + c, it)) < 1e-10
-        assert rel_err(sig2[c], pm.sample_sig2(beta0[c], 0.0, 0.0, SEED, 11 + c, it)) < 1e-8
-        o, s = pm.sample_omega(beta0[c], u0[c], tau[c], alpha, SEED, 11 + c, it)
-        assert rel_err(om[c], o) < 1e-10 and np.array_equal(sh[c], s)
-        assert np.abs(u1[c] - pm.sample_u(beta0[c], om[c], tau[c], alpha, SEED, 11 + c, it)).max() < 1e-10
+        for eng, en in engs:
+            check("a3 sample_tau_marg", cfg, rel_err(tau[c], eng.sample_tau_marg(beta0[c], alpha, 2.0, 2.0, SEED, 11 + c, it)), 1e-12, en)
+            check("a4 sample_sig2", cfg, rel_err(sig2[c], eng.sample_sig2(beta0[c], 0.0, 0.0, SEED, 11 + c, it)), 1e-12, en)
+            o, s = eng.sample_omega(beta0[c], u0[c], tau[c], alpha, SEED, 11 + c, it)
+            check("a5 sample_omega", cfg, rel_err(om[c], o), 1e-12, en)
+            assert np.array_equal(sh[c], s)
+            check("a6 sample_u", cfg, np.abs(u1[c] - eng.sample_u(beta0[c], om[c], tau[c], alpha, SEED, 11 + c, it)).max(), 1e-12, en)
         bbox = (1.0 - u1[c]) * np.exp(np.log(om[c]) / alpha) * tau[c]
-        assert teacher_forced_sweep_error(f, beta0[c], bbox, sig2[c], SEED, 11 + c, it, b1[c]) < 1e-10
+        check("a7 sample_beta (per draw)", cfg, teacher_forced_sweep_error(f, beta0[c], bbox, sig2[c], SEED, 11 + c, it, b1[c]), 1e-11, "port draws")
     assert not ch.get()["status"].any()
 
 
 def test_c4_shape_stb_conditionals(port):
-    """n=500, p=2000, alpha=0.25 (config c4, p > n): tau, sig2, lambda and the 2000 x 2000 Cholesky draw of
-    beta (blocked DMMA factorisation in HBM) against the oracle for one chain."""
+    """n=500, p=2000, alpha=0.25 (config c4, p > n): tau, sig2, lambda and the 2000 x 2000 Cholesky draw of beta (blocked
+    DMMA factorisation in HBM) for one chain against the port and the compiled reference (its own chol / trsm)."""
     import bayesbridge_b200 as bb
+    import bb_oracle
     from bayesbridge_b200 import synth
     from bayesbridge_b200._lib import ST_BETA, ST_LAMBDA, ST_SIG2, ST_TAU
     X, y, _ = synth.make("c4")
@@ -65,6 +75,7 @@ def test_c4_shape_stb_conditionals(port):
     f = model.factors()
     assert not np.abs(f["bhat"]).any()          # singular X'X: least squares start is 0 (BridgeRegression.cpp:79-91)
     pm = port.model(X, y, (f["tV"], f["d"], f["a"], f["bhat"]))
+    rm = bb_oracle.Ref().model(X, y) if bb_oracle.ref_available() else None
     alpha, it = 0.25, 4
     rng = np.random.default_rng(4)
     beta0 = 0.05 * rng.standard_normal((1, P))
@@ -76,11 +87,18 @@ def test_c4_shape_stb_conditionals(port):
     ch.run(hyp, 1, it, ST_LAMBDA); lam = ch.get()["aux"]
     ch.run(hyp, 1, it, ST_BETA); st = ch.get()
     assert not st["status"].any()
-    assert rel_err(tau[0], pm.sample_tau_marg(beta0[0], alpha, 2.0, 2.0, SEED, 5, it)) < 1e-10
-    assert rel_err(sig2[0], pm.sample_sig2(beta0[0], 0.0, 0.0, SEED, 5, it)) < 1e-8
-    want = pm.sample_lambda(beta0[0], alpha, tau[0], SEED, 5, it)
-    assert np.abs(lam[0] / want - 1).max() < 1e-9
-    assert rel_err(st["beta"][0], pm.sample_beta_stable(lam[0], sig2[0], tau[0], SEED, 5, it)) < 1e-7
+    cfg = "c4 stb 500x2000 a=0.25"
+    kappa = np.linalg.cond(f["XX"] + np.diag(lam[0] * sig2[0] / tau[0] ** 2))
+    EPS = np.finfo(float).eps
+    for eng, en in ((e, n) for e, n in ((pm, "port"), (rm, "reference")) if e is not None):
+        check("a3 sample_tau_marg", cfg, rel_err(tau[0], eng.sample_tau_marg(beta0[0], alpha, 2.0, 2.0, SEED, 5, it)), 1e-12, en)
+        check("a4 sample_sig2", cfg, rel_err(sig2[0], eng.sample_sig2(beta0[0], 0.0, 0.0, SEED, 5, it)), 1e-12, en)
+        want = eng.sample_lambda(beta0[0], alpha, tau[0], SEED, 5, it)
+        check("a9 sample_lambda", cfg, np.abs(lam[0] / want - 1).max(), 1e-12, en)
+        kw = {"alpha": alpha} if en == "reference" else {}
+        err = rel_err(st["beta"][0], eng.sample_beta_stable(lam[0], sig2[0], tau[0], SEED, 5, it, **kw))
+        check("a10 sample_beta_stable", cfg, err, 1e-12, en)
+        check("a10 sample_beta_stable: err / (kappa eps)", cfg, err / (kappa * EPS), 8.0, en)
 
 
 @pytest.mark.parametrize("method,cfg", [("stable", "c2"), ("triangle", "c1")])
@@ -129,7 +147,7 @@ def test_tri_invariants_after_many_sweeps():
     b1 = ch.get()["beta"]
     for c in range(nch):
         bbox = (1.0 - u0[c]) * om0[c] ** 2.0 * st["tau"][c]
-        assert teacher_forced_sweep_error(f, beta0[c], bbox, st["sig2"][c], SEED, c, 300, b1[c]) < 1e-8
+        check("a7 sample_beta (per draw, after 300 incremental sweeps)", "tri 3000x256", teacher_forced_sweep_error(f, beta0[c], bbox, st["sig2"][c], SEED, c, 300, b1[c]), 1e-8, "port draws")
 
 
 def test_tri_vs_stb_posterior_means_agree():
