@@ -22,12 +22,12 @@ OUT_BETA, OUT_U, OUT_OMEGA, OUT_SHAPE, OUT_LAMBDA, OUT_SIG2, OUT_TAU, OUT_ALPHA 
 
 # every symbol include/bayesbridge_b200.h declares
 EXPORTS = [
-    "bridge_regression", "bridge_reg_stable", "bb_set_seed", "bb_set_device", "bb_set_verbose",
+    "bridge_regression", "bridge_reg_stable", "bb_set_seed", "bb_set_device", "bb_set_verbose", "bb_set_interrupt", "bb_scalar_status",
     "bb_last_error", "bb_device_count", "bb_model_create", "bb_model_create_factors", "bb_gram", "bb_gram_noalloc",
-    "bb_model_create_gram", "bb_model_resid_partial", "bb_model_set_r0", "bb_model_free", "bb_model_get",
+    "bb_model_create_gram", "bb_model_resid_partial", "bb_model_set_r0", "bb_model_free", "bb_model_clone", "bb_model_status", "bb_model_get",
     "bb_model_precompute_ms", "bb_chains_create", "bb_chains_free", "bb_chains_set", "bb_chains_get", "bb_chains_alpha",
-    "bb_chains_reserve", "bb_chains_run", "bb_chains_store_state", "bb_chains_fetch", "bb_chains_summary", "bb_launch_count",
-    "bb_bridge_batched", "bb_bridge_batched_summary",
+    "bb_chains_reserve", "bb_chains_run", "bb_chains_store_state", "bb_chains_fetch", "bb_chains_summary", "bb_launch_count", "bb_measure_fp64_fma",
+    "bb_bridge_batched", "bb_bridge_batched_multi", "bb_bridge_batched_summary",
     "rtexpon_rate_left", "rtexpon_rate_both", "rtexpon_rate", "rtnorm_left", "rtnorm_both", "rtnorm", "rrtgamma_rate", "retstable_LD",
 ]
 
@@ -89,8 +89,17 @@ def load():
     L.bb_chains_store_state.argtypes = [vp, C.c_longlong]
     L.bb_chains_fetch.argtypes = [vp, C.c_int, C.c_longlong, C.c_longlong, vp]
     L.bb_chains_summary.argtypes = [vp, C.c_int, C.c_longlong, C.c_longlong, C.c_double, vp, vp]
+    L.bb_measure_fp64_fma.argtypes = [C.c_int, dp]
     L.bb_bridge_batched.argtypes = [C.c_int, C.c_int, dp, dp, C.c_int, C.c_int, C.POINTER(Hyper), C.c_int, C.c_ulonglong,
                                     C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int] + [dp] * 7 + [up, dp]
+    L.bb_bridge_batched_multi.argtypes = [C.c_int, C.c_int, dp, dp, C.c_int, C.c_int, C.POINTER(Hyper), C.c_int, C.c_ulonglong,
+                                          C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int, ip] + [dp] * 7 + [up, dp]
+    L.bb_set_interrupt.argtypes = [C.c_void_p]
+    L.bb_set_interrupt.restype = None
+    L.bb_scalar_status.restype = C.c_uint
+    L.bb_model_clone.restype = vp
+    L.bb_model_clone.argtypes = [vp, C.c_int]
+    L.bb_model_status.argtypes = [vp]
     L.bb_bridge_batched_summary.argtypes = [C.c_int, C.c_int, dp, dp, C.c_int, C.c_int, C.POINTER(Hyper), C.c_int, C.c_ulonglong,
                                             C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int] + [dp] * 4 + [up, dp]
     for name, nd in (("rtexpon_rate_left", 3), ("rtexpon_rate_both", 4), ("rtexpon_rate", 4), ("rtnorm_left", 4),

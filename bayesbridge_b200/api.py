@@ -295,11 +295,15 @@ class Chains:
     def store_state(self, slot):
         self._ck(self.L.bb_chains_store_state(self.h, slot))
 
-    def fetch(self, name, slot0=0, nslots=None):
+    def fetch(self, name, slot0=0, nslots=None, out=None):
+        """stored draws [chain, slot, P] (or [chain, slot]); `out`: a host buffer to fill instead of a new numpy array --
+        anything with .ctypes.data or .data_ptr() (e.g. a pinned torch tensor: the copy then runs at full PCIe speed)."""
         nslots = self.nslots - slot0 if nslots is None else nslots
         w = 1 if name in ("sig2", "tau", "alpha") else self.P
-        out = np.zeros((self.nchains, nslots, w)) if w > 1 else np.zeros((self.nchains, nslots))
-        self._ck(self.L.bb_chains_fetch(self.h, _OUT[name], slot0, nslots, out.ctypes.data))
+        if out is None:
+            out = np.zeros((self.nchains, nslots, w)) if w > 1 else np.zeros((self.nchains, nslots))
+        ptr = out.data_ptr() if hasattr(out, "data_ptr") else out.ctypes.data
+        self._ck(self.L.bb_chains_fetch(self.h, _OUT[name], slot0, nslots, ptr))
         return out
 
     def summary(self, name="beta", slot0=0, nslots=None, runtime=None, per_chain=False):

@@ -6,12 +6,15 @@
 //   BridgeWrapper.cpp:80-537 (the four Gibbs drivers)     -> run_driver()
 //   BridgeRegression.h:81-166 (class BridgeRegression)    -> struct bb_model + struct bb_chains
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include <limits>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/bayesbridge_b200.h"
@@ -20,11 +23,13 @@
 namespace {
 
 thread_local std::string g_err;
-long long g_launches = 0;
+std::atomic<long long> g_launches{0};
 unsigned long long g_seed = 20121027ULL;
-unsigned g_scalar_calls = 0;   // Philox `iter` word of the stand-alone scalar samplers: one per call since bb_set_seed
+std::atomic<unsigned> g_scalar_calls{0};   // Philox `iter` word of the stand-alone scalar samplers: one per call since bb_set_seed
 int g_device = 0;
 int g_verbose = 0;
+std::atomic<unsigned> g_scalar_status{0};  // status word (bb::Status bits) of the last stand-alone sampler call
+int (*g_interrupt)(void) = nullptr;        // bb_set_interrupt: polled between chunks of the sampling loop on the calling thread
 
 void set_err(const std::string& s) { g_err = s; }
 
@@ -32,7 +37,18 @@ using bb::dalloc;
 using bb::dfree;
 using bb::check_launch;
 
-inline void launched(int n = 1) { g_launches += n; }
+inline void launched(int n = 1) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+// scratch device buffer that is released on every exit path (an exception between dalloc and dfree used to leak it)
+template <typename T>
+struct DBuf {
+  T* p = nullptr;
+  explicit DBuf(size_t n) : p(bb::dalloc<T>(n)) {}
+  ~DBuf() { bb::dfree(p); }
+  DBuf(const DBuf&) = delete;
+  DBuf& operator=(const DBuf&) = delete;
+  operator T*() const { return p; }
+};
 
 }  // namespace
 
@@ -48,6 +64,8 @@ struct bb_model {
   double r0z = 0, r0b = 0, yy = 0;
   bool singular = false;
   bool lazy_svd = false;   // P > N: the SVD factors (triangle sampler only) are built on first use, see ensure_svd
+  std::mutex svd_mu;       // ensure_svd may be reached from several threads creating chains on one model
+  int zeroed_by_gram_cut = 0;   // singular values dropped by the 1e-7 d_max cut of the Gram-eigen path although above eps d_max
   double precompute_ms = 0;
   cudaStream_t stream = nullptr;
 
@@ -96,9 +114,9 @@ void model_finish(bb_model* m, bool have_rows, bool stable_only = false) {
 // singular values / vectors from the Jacobi result; sorts descending; fills every derived array.
 void model_factor(bb_model* m, double* W, int M, bool w_is_gram) {
   const int P = m->P; cudaStream_t st = m->stream;
-  double* V = dalloc<double>((size_t)P * P);
+  DBuf<double> V((size_t)P * P);
   launched(bb::jacobi_device(W, V, M, P, st));
-  double* nrm = dalloc<double>(P);
+  DBuf<double> nrm(P);
   launched(bb::colnorm_device(W, M, P, nrm, st));
   std::vector<double> h(P);
   BB_CUDA_CHECK(cudaMemcpyAsync(h.data(), nrm, P * sizeof(double), cudaMemcpyDeviceToHost, st));
@@ -110,12 +128,28 @@ void model_factor(bb_model* m, double* W, int M, bool w_is_gram) {
   std::vector<int> perm(P);
   for (int i = 0; i < P; ++i) perm[i] = i;
   std::stable_sort(perm.begin(), perm.end(), [&](int x, int y) { return h[x] > h[y]; });
-  // numerically zero directions are exactly zero (the reference takes the flat branch when d <= 1e-16, :272-281)
+  // numerically zero directions are exactly zero (the reference takes the flat branch when d <= 1e-16, :272-281).
+  // On the Gram-eigen path singular values are only resolved to sqrt(eps) d_max: everything below 1e-7 d_max is cut.  For
+  // cond(X) >= 1e7 the reference (SVD of X itself) would still draw tnorm(a_i/d_i^2, sig/d_i) in those directions; the
+  // model records how many such values were cut so that the caller is told (stderr + bb_model_status) instead of
+  // diverging silently -- build the model from the rows (bb_model_create, N >= P) to keep them.
   const double tol = w_is_gram ? 1e-7 * dmax : 1e-13 * dmax;
   double dmin = dmax;
-  for (int i = 0; i < P; ++i) { if (i >= rank_cap || h[perm[i]] <= tol) h[perm[i]] = 0.0; dmin = std::min(dmin, h[perm[i]]); }
+  int cut = 0;
+  for (int i = 0; i < P; ++i) {
+    const bool beyond_rank = i >= rank_cap;
+    if (beyond_rank || h[perm[i]] <= tol) {
+      if (w_is_gram && !beyond_rank && h[perm[i]] > 1e-13 * dmax) ++cut;
+      h[perm[i]] = 0.0;
+    }
+    dmin = std::min(dmin, h[perm[i]]);
+  }
+  m->zeroed_by_gram_cut = cut;
+  if (cut > 0)
+    std::fprintf(stderr, "bayesbridge_b200: warning: %d singular value(s) between 1e-13 and 1e-7 of the largest were set to zero "
+                         "(factors taken from X'X, cond(X) >= 1e7); the reference's SVD of X would keep them.\n", cut);
   m->singular = !(dmin > 0.0);
-  int* d_perm = dalloc<int>(P);
+  DBuf<int> d_perm(P);
   BB_CUDA_CHECK(cudaMemcpyAsync(d_perm, perm.data(), P * sizeof(int), cudaMemcpyHostToDevice, st));
   BB_CUDA_CHECK(cudaMemcpyAsync(nrm, h.data(), P * sizeof(double), cudaMemcpyHostToDevice, st));
   launched(bb::derive_device(V, d_perm, nrm, m->Xy, P, m->ldv, m->tV, m->Vc, m->VQ, m->d, m->a, m->mean, m->d2, m->zc, st));
@@ -123,7 +157,6 @@ void model_factor(bb_model* m, double* W, int M, bool w_is_gram) {
   if (m->singular) BB_CUDA_CHECK(cudaMemsetAsync(m->bhat, 0, P * sizeof(double), st));
   else launched(bb::vz_device(m->Vc, m->zc, P, m->ldv, m->bhat, st));
   BB_CUDA_CHECK(cudaStreamSynchronize(st));
-  dfree(V); dfree(nrm); dfree(d_perm);
 }
 
 // Tall designs (N >= 4 P): the factors from the Cholesky factor of the Gram matrix instead of from X itself.
@@ -138,11 +171,11 @@ bool model_factor_chol(bb_model* m) {
   const int P = m->P; cudaStream_t st = m->stream;
   const char* env = std::getenv("BB_SVD_DIRECT");
   if (env && env[0] == '1') return false;
-  double* W = dalloc<double>((size_t)P * P);
-  double* Winv = dalloc<double>((size_t)((P + 63) / 64) * 64 * 64);
-  uint32_t* d_status = dalloc<uint32_t>(1);
-  double* nrm = dalloc<double>(P);
-  int* d_perm = dalloc<int>(P);
+  DBuf<double> W((size_t)P * P);
+  DBuf<double> Winv((size_t)((P + 63) / 64) * 64 * 64);
+  DBuf<uint32_t> d_status(1);
+  DBuf<double> nrm(P);
+  DBuf<int> d_perm(P);
   bool ok = false;
   BB_CUDA_CHECK(cudaMemcpyAsync(W, m->XX, (size_t)P * P * sizeof(double), cudaMemcpyDeviceToDevice, st));
   BB_CUDA_CHECK(cudaMemsetAsync(d_status, 0, sizeof(uint32_t), st));
@@ -173,7 +206,6 @@ bool model_factor_chol(bb_model* m) {
       ok = true;
     }
   }
-  dfree(W); dfree(Winv); dfree(d_status); dfree(nrm); dfree(d_perm);
   return ok;
 }
 
@@ -200,13 +232,12 @@ void model_take_rows(bb_model* m, const double* X, const double* y, int mem) {
 
 void model_gram(bb_model* m) {
   const int P = m->P;
-  double* G = dalloc<double>((size_t)(P + 1) * (P + 1));
+  DBuf<double> G((size_t)(P + 1) * (P + 1));
   launched(bb::gram_device(m->X, m->y, m->N, P, G, m->stream));
-  double* d_yy = dalloc<double>(1);
+  DBuf<double> d_yy(1);
   launched(bb::gram_unpack(G, P, m->XX, m->Xy, d_yy, m->stream));
   BB_CUDA_CHECK(cudaMemcpyAsync(&m->yy, d_yy, sizeof(double), cudaMemcpyDeviceToHost, m->stream));
   BB_CUDA_CHECK(cudaStreamSynchronize(m->stream));
-  dfree(G); dfree(d_yy);
 }
 
 }  // namespace
@@ -285,6 +316,21 @@ __global__ void gather_kernel(const double* src, double* dst, int width, long lo
     const size_t c = e / per, r = e % per;
     dst[e] = src[(c * stride + slot0) * width + r];
   }
+}
+
+// FP64 vector-pipe peak: 16 independent DFMA chains per thread, all SMs full (bb_measure_fp64_fma)
+__global__ void __launch_bounds__(256) dfma_peak_kernel(double* out, int iters, double a, double b) {
+  double x[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) x[k] = 1e-3 * (threadIdx.x + k);
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int k = 0; k < 16; ++k) x[k] = fma(x[k], a, b);
+  }
+  double s = 0.0;
+#pragma unroll
+  for (int k = 0; k < 16; ++k) s += x[k];
+  if (s == 123.456) out[0] = s;   // keeps the chains alive
 }
 
 void fill(double* p, size_t n, double v, cudaStream_t st) { fill_kernel<<<296, 256, 0, st>>>(p, n, v); check_launch(); launched(); }
@@ -402,13 +448,15 @@ int guarded(F&& f) {
 
 void ensure_svd(const bb_model* cm) {
   bb_model* m = const_cast<bb_model*>(cm);
+  std::lock_guard<std::mutex> lock(m->svd_mu);   // two threads creating triangle chains on one model build the factors once
   if (!m->lazy_svd) return;
   auto t0 = std::chrono::steady_clock::now();
   const int P = m->P;
-  double* W = dalloc<double>((size_t)P * P);
-  BB_CUDA_CHECK(cudaMemcpyAsync(W, m->XX, (size_t)P * P * sizeof(double), cudaMemcpyDeviceToDevice, m->stream));
-  model_factor(m, W, P, true);
-  dfree(W);
+  {
+    DBuf<double> W((size_t)P * P);
+    BB_CUDA_CHECK(cudaMemcpyAsync(W, m->XX, (size_t)P * P * sizeof(double), cudaMemcpyDeviceToDevice, m->stream));
+    model_factor(m, W, P, true);
+  }
   model_finish(m, m->X != nullptr);
   BB_CUDA_CHECK(cudaStreamSynchronize(m->stream));
   m->lazy_svd = false;
@@ -424,10 +472,39 @@ extern "C" {
 
 const char* bb_last_error(void) { return g_err.c_str(); }
 int bb_device_count(void) { int n = 0; if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; } return n; }
-long long bb_launch_count(void) { return g_launches; }
-void bb_set_seed(unsigned long long seed) { g_seed = seed; g_scalar_calls = 0; }
+long long bb_launch_count(void) { return g_launches.load(); }
+void bb_set_seed(unsigned long long seed) { g_seed = seed; g_scalar_calls.store(0); }
+void bb_set_interrupt(int (*fn)(void)) { g_interrupt = fn; }
+unsigned int bb_scalar_status(void) { return g_scalar_status.load(); }
+int bb_model_status(const bb_model* m) { return m ? m->zeroed_by_gram_cut : -1; }
 void bb_set_device(int device) { g_device = device; }
 void bb_set_verbose(int v) { g_verbose = v; }
+
+// Measurement aid (no counterpart in the reference): peak of the FP64 vector pipe of `device` in TFLOP/s (2 flops per
+// DFMA), best of 5 launches timed with CUDA events.  bench.py uses it as the roofline denominator of the triangle sweep.
+int bb_measure_fp64_fma(int device, double* tflops) {
+  return guarded([&] {
+    BB_CUDA_CHECK(cudaSetDevice(device));
+    int nsm = 0;
+    BB_CUDA_CHECK(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, device));
+    double* d_out = dalloc<double>(1);
+    cudaEvent_t e0, e1;
+    BB_CUDA_CHECK(cudaEventCreate(&e0)); BB_CUDA_CHECK(cudaEventCreate(&e1));
+    const int iters = 8192, grid = nsm * 8;
+    double best = 1e30;
+    for (int r = 0; r < 6; ++r) {
+      BB_CUDA_CHECK(cudaEventRecord(e0, cudaStreamPerThread));
+      dfma_peak_kernel<<<grid, 256, 0, cudaStreamPerThread>>>(d_out, iters, 0.999999, 1e-9);
+      BB_CUDA_CHECK(cudaEventRecord(e1, cudaStreamPerThread));
+      BB_CUDA_CHECK(cudaEventSynchronize(e1));
+      check_launch(); launched();
+      float ms = 0; BB_CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+      if (r > 0) best = std::min(best, (double)ms);
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); dfree(d_out);
+    *tflops = 2.0 * 16.0 * iters * 256.0 * grid / (best * 1e-3) / 1e12;
+  });
+}
 
 bb_model* bb_model_create(const double* X, const double* y, int N, int P, int device, int mem) {
   bb_model* m = nullptr;
@@ -454,10 +531,11 @@ bb_model* bb_model_create(const double* X, const double* y, int N, int P, int de
       model_finish(m, true);
       lap("centres, residuals");
     } else if (N >= P) {
-      double* W = dalloc<double>((size_t)N * P);
-      BB_CUDA_CHECK(cudaMemcpyAsync(W, m->X, (size_t)N * P * sizeof(double), cudaMemcpyDeviceToDevice, m->stream));
-      model_factor(m, W, N, false);
-      dfree(W);
+      {
+        DBuf<double> W((size_t)N * P);
+        BB_CUDA_CHECK(cudaMemcpyAsync(W, m->X, (size_t)N * P * sizeof(double), cudaMemcpyDeviceToDevice, m->stream));
+        model_factor(m, W, N, false);
+      }
       model_finish(m, true);
     } else {
       // P > N: X'X is singular by rank, so the least-squares start is 0 (BridgeRegression.cpp:79-91) and the stable
@@ -520,16 +598,14 @@ bb_model* bb_model_create_gram(const double* G_dev, int N, int P, int device) {
     auto t0 = std::chrono::steady_clock::now();
     m = model_new(N, P, device);
     if (!m) throw std::string(g_err);
-    double* d_yy = dalloc<double>(1);
+    DBuf<double> d_yy(1);
     launched(bb::gram_unpack(G_dev, P, m->XX, m->Xy, d_yy, m->stream));
     BB_CUDA_CHECK(cudaMemcpyAsync(&m->yy, d_yy, sizeof(double), cudaMemcpyDeviceToHost, m->stream));
     if (!(N >= 4 * (long long)P && model_factor_chol(m))) {
-      double* W = dalloc<double>((size_t)P * P);
+      DBuf<double> W((size_t)P * P);
       BB_CUDA_CHECK(cudaMemcpyAsync(W, m->XX, (size_t)P * P * sizeof(double), cudaMemcpyDeviceToDevice, m->stream));
       model_factor(m, W, P, true);
-      dfree(W);
     }
-    dfree(d_yy);
     model_finish(m, false);
     // without the rows: r0 from the normal equations (replaced by bb_model_set_r0 after the shard all-reduce)
     BB_CUDA_CHECK(cudaStreamSynchronize(m->stream));
@@ -546,7 +622,8 @@ int bb_model_resid_partial(const bb_model* m, const double* X_dev, const double*
     int nl = 0;
     const double r[2] = {bb::resid_device(X_dev, y_dev, m->bz, n_rows, m->P, m->stream, &nl), bb::resid_device(X_dev, y_dev, m->bc, n_rows, m->P, m->stream, &nl)};
     launched(nl);
-    BB_CUDA_CHECK(cudaMemcpy(out_dev, r, 2 * sizeof(double), cudaMemcpyHostToDevice));
+    BB_CUDA_CHECK(cudaMemcpyAsync(out_dev, r, 2 * sizeof(double), cudaMemcpyHostToDevice, m->stream));
+    BB_CUDA_CHECK(cudaStreamSynchronize(m->stream));   // r lives on this stack frame
   });
 }
 int bb_model_set_r0(bb_model* m, double r0z, double r0b) { m->r0z = r0z; m->r0b = r0b; return 0; }
@@ -683,13 +760,12 @@ int bb_chains_summary(const bb_chains* c, int which, long long slot0, long long 
     if (slot0 < 0 || nslots < 2 || slot0 + nslots > c->nslots) throw std::string("bb_chains_summary: slot range out of bounds");
     if (nslots > 16384) throw std::string("bb_chains_summary: at most 16384 stored draws per chain (thin the run or fetch the draws)");
     const size_t P = c->m->P, n1 = (size_t)c->nchains * 5 * P, n2 = 7 * P;
-    double* d_pc = dalloc<double>(n1);
-    double* d_po = dalloc<double>(n2);
+    DBuf<double> d_pc(n1);
+    DBuf<double> d_po(n2);
     launched(bb::summary_device(src, (int)P, c->nslots, slot0, (int)nslots, c->nchains, runtime_sec, d_pc, d_po, c->stream));
     if (per_chain) BB_CUDA_CHECK(cudaMemcpyAsync(per_chain, d_pc, n1 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     if (pooled) BB_CUDA_CHECK(cudaMemcpyAsync(pooled, d_po, n2 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     BB_CUDA_CHECK(cudaStreamSynchronize(c->stream));
-    dfree(d_pc); dfree(d_po);
   });
 }
 
@@ -712,11 +788,10 @@ int bb_chains_fetch(const bb_chains* c, int which, long long slot0, long long ns
     if (slot0 < 0 || slot0 + nslots > c->nslots) throw std::string("bb_chains_fetch: slot range out of bounds");
     const size_t n = (size_t)c->nchains * nslots * w;
     if (slot0 == 0 && nslots == c->nslots) { BB_CUDA_CHECK(cudaMemcpy(out, src, n * sizeof(double), cudaMemcpyDeviceToHost)); return; }
-    double* tmp = dalloc<double>(n);
+    DBuf<double> tmp(n);
     gather_kernel<<<296, 256, 0, c->stream>>>(src, tmp, w, c->nslots, slot0, nslots, c->nchains); check_launch(); launched();
     BB_CUDA_CHECK(cudaStreamSynchronize(c->stream));
     BB_CUDA_CHECK(cudaMemcpy(out, tmp, n * sizeof(double), cudaMemcpyDeviceToHost));
-    dfree(tmp);
   });
 }
 
@@ -729,32 +804,60 @@ namespace {
 
 void nan_fill(double* p, size_t n) { if (p) for (size_t i = 0; i < n; ++i) p[i] = std::numeric_limits<double>::quiet_NaN(); }
 
-void run_driver(int method, int ortho, const double* X, const double* y, int N, int P, const bb_hyper* h,
-                int nchains, unsigned long long seed, unsigned int chain0, int burn, int nsamp, int thin, int device,
-                double* beta, double* aux1, double* aux2, double* aux3, double* sig2, double* tau, double* alpha,
-                unsigned int* status, double* runtime, double* sum_pooled = nullptr, double* sum_chain = nullptr) {
+// a bit-for-bit copy of a model on another device (peer copies; X, y stay behind: no kernel of the sweep reads them)
+bb_model* model_clone(const bb_model* src, int device) {
+  bb_model* m = model_new(src->N, src->P, device);
+  if (!m) throw std::string(g_err);
+  try {
+    if (src->lazy_svd) throw std::string("bb_model_clone: the source model's SVD factors are not built yet");
+    const size_t P = src->P, ldv = src->ldv;
+    cudaStream_t st = m->stream;
+    auto cp = [&](double* dst, const double* from, size_t n) {
+      BB_CUDA_CHECK(cudaMemcpyPeerAsync(dst, device, from, src->device, n * sizeof(double), st));
+    };
+    cp(m->XX, src->XX, P * P); cp(m->Xy, src->Xy, P); cp(m->bhat, src->bhat, P); cp(m->tV, src->tV, P * P);
+    cp(m->Vc, src->Vc, P * ldv); cp(m->VQ, src->VQ, 2 * P * (ldv + 2)); cp(m->d, src->d, P); cp(m->a, src->a, P);
+    cp(m->mean, src->mean, P); cp(m->zc, src->zc, P); cp(m->d2, src->d2, P); cp(m->gc, src->gc, P); cp(m->bc, src->bc, P);
+    cp(m->bz, src->bz, P);
+    m->r0z = src->r0z; m->r0b = src->r0b; m->yy = src->yy; m->singular = src->singular; m->lazy_svd = false;
+    m->zeroed_by_gram_cut = src->zeroed_by_gram_cut; m->precompute_ms = 0;
+    BB_CUDA_CHECK(cudaStreamSynchronize(st));
+  } catch (...) { delete m; throw; }
+  return m;
+}
+
+struct DriverOut {   // host outputs of one driver call, [nchains][nsamp][w] / [nchains][nsamp]; any may be null
+  double *beta = nullptr, *aux1 = nullptr, *aux2 = nullptr, *aux3 = nullptr, *sig2 = nullptr, *tau = nullptr, *alpha = nullptr;
+  unsigned int* status = nullptr;
+  double *sum_pooled = nullptr, *sum_chain = nullptr;
+};
+
+// The drivers' schedule on an existing model, for chains [chain0, chain0 + nchains).  Returns the seconds of the
+// post-burn-in loop INCLUDING the arrival of the last draws on the host (the reference's clock stops when its samples are
+// in memory, BridgeWrapper.cpp:197-202).  poll: the calling thread polls the interrupt hook between chunks.
+double run_driver_on_model(const bb_model* m, int method, int ortho, const bb_hyper* h, int nchains, unsigned long long seed,
+                           unsigned int chain0, int burn, int nsamp, int thin, const DriverOut& out, bool poll) {
   if (nsamp < 1 || burn < 0 || nchains < 1) throw std::string("bridge driver: need nsamp >= 1, burn >= 0, nchains >= 1");
   if (thin < 1) thin = 1;
-  struct Guard { bb_model* m = nullptr; bb_chains* c = nullptr; ~Guard() { delete c; delete m; } } g;
+  const int P = m->P;
+  BB_CUDA_CHECK(cudaSetDevice(m->device));
+  struct Guard { bb_chains* c = nullptr; ~Guard() { delete c; } } g;
   auto tp0 = std::chrono::steady_clock::now();
   auto lap = [&](const char* what) {
     if (g_verbose >= 2) { auto n = std::chrono::steady_clock::now(); std::printf("  [driver] %-22s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(n - tp0).count()); tp0 = n; }
   };
-  g.m = bb_model_create(X, y, N, P, device, BB_MEM_HOST);
-  if (!g.m) throw std::string(g_err);
-  lap("model (upload+factors)");
-  g.c = bb_chains_create(g.m, method, ortho, nchains, seed, chain0);
+  g.c = bb_chains_create(m, method, ortho, nchains, seed, chain0);
   if (!g.c) throw std::string(g_err);
   // only the outputs the caller asked for are stored by the kernels (8 P bytes per chain-iteration each)
   struct Out { int which; double* host; const double* dev; int w; };
-  Out outs[8] = {{BB_OUT_BETA, beta, nullptr, P},
-                 {method == BB_TRI ? BB_OUT_U : BB_OUT_LAMBDA, aux1, nullptr, P},
-                 {BB_OUT_OMEGA, method == BB_TRI ? aux2 : nullptr, nullptr, P},
-                 {BB_OUT_SHAPE, method == BB_TRI ? aux3 : nullptr, nullptr, P},
-                 {BB_OUT_SIG2, sig2, nullptr, 1}, {BB_OUT_TAU, tau, nullptr, 1}, {BB_OUT_ALPHA, alpha, nullptr, 1}, {0, nullptr, nullptr, 0}};
+  Out outs[8] = {{BB_OUT_BETA, out.beta, nullptr, P},
+                 {method == BB_TRI ? BB_OUT_U : BB_OUT_LAMBDA, out.aux1, nullptr, P},
+                 {BB_OUT_OMEGA, method == BB_TRI ? out.aux2 : nullptr, nullptr, P},
+                 {BB_OUT_SHAPE, method == BB_TRI ? out.aux3 : nullptr, nullptr, P},
+                 {BB_OUT_SIG2, out.sig2, nullptr, 1}, {BB_OUT_TAU, out.tau, nullptr, 1}, {BB_OUT_ALPHA, out.alpha, nullptr, 1}, {0, nullptr, nullptr, 0}};
   int mask = 0;
   for (const Out& o : outs) if (o.host) mask |= o.which;
-  if (mask == 0 || sum_pooled || sum_chain) mask |= BB_OUT_BETA;
+  if (mask == 0 || out.sum_pooled || out.sum_chain) mask |= BB_OUT_BETA;
   if (bb_chains_reserve(g.c, nsamp, mask)) throw std::string(g_err);
   for (Out& o : outs) {
     switch (o.host ? o.which : 0) {
@@ -781,27 +884,44 @@ void run_driver(int method, int ortho, const double* X, const double* y, int N, 
                                       cudaMemcpyDeviceToHost, cps.s));
     }
   };
+  auto interrupted = [&]() { return poll && g_interrupt && g_interrupt() != 0; };
   lap("chains + draw buffer");
-  if (g_verbose) {
+  if (g_verbose && poll) {
     std::printf("Bridge Regression (%s):", method == BB_TRI ? "mix. of triangles" : "mix. of normals");
     if (h->true_alpha > 0) std::printf(" known alpha=%g", h->true_alpha);
     if (h->true_sig2 > 0) std::printf(", sig2=%g", h->true_sig2);
     if (h->true_tau > 0) std::printf(", tau=%g", h->true_tau);
     std::printf("\nBurn-in: %i, Num. Samples: %i, Chains: %i\n", burn, nsamp, nchains);
   }
-  // burn-in, in place (tri: burn iterations, :145 ; stb: burn+1, :266), preceded by the pre-draws
+  // burn-in, in place (tri: burn iterations, :145 ; stb: burn+1, :266), preceded by the pre-draws.  With an interrupt hook
+  // the burn-in runs in slices so that the hook is polled about five times a second (the reference polls
+  // R_CheckUserInterrupt every 10 iterations, BridgeWrapper.cpp:154-156,186-188).
   const int nburn = method == BB_TRI ? burn : burn + 1;
   int pre = 0;
   if (method == BB_TRI) pre = ortho ? 3 : 1;          // :142 / :379-380
   else pre = ortho ? 0 : 1;                           // :262 / none (:490)
-  chains_run(g.c, h, 0u, nburn, BB_ST_ALL, pre & 1, (pre >> 1) & 1, 0, 0, nullptr);
+  {
+    long long done_b = 0, slice = (poll && g_interrupt) ? 16 : nburn;
+    bool first = true;
+    do {
+      const long long n = std::min(slice, (long long)nburn - done_b);
+      auto ts = std::chrono::steady_clock::now();
+      chains_run(g.c, h, (unsigned)done_b, (int)n, BB_ST_ALL, first ? (pre & 1) : 0, first ? ((pre >> 1) & 1) : 0, 0, 0, nullptr);
+      first = false; done_b += n;
+      if (interrupted()) throw std::string("interrupted by the caller's hook (bb_set_interrupt) during burn-in");
+      const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - ts).count();
+      if (poll && g_interrupt && sec > 0) slice = std::max(16LL, std::min(1LL << 20, (long long)(slice * 0.2 / sec)));
+    } while (done_b < nburn);
+  }
   if (bb_chains_store_state(g.c, 0)) throw std::string(g_err);     // sample 0 = state after burn-in
   lap("burn-in");
   auto t0 = std::chrono::steady_clock::now();
   const long long total = (long long)(nsamp - 1) * thin;
   long long done = 0;
-  // chunks: at most 8192 stored iterations between two polls, and about four chunks per call so that the download overlaps
-  const long long chunk = std::min(8192LL, std::max(16LL, (total / thin + 3) / 4)) * thin;
+  // chunks: at most 8192 stored iterations between two polls, and about four chunks per call so that the download overlaps;
+  // with an interrupt hook the chunk adapts to about 0.2 s of sampling
+  long long chunk = std::min(8192LL, std::max(16LL, (total / thin + 3) / 4)) * thin;
+  if (poll && g_interrupt) chunk = std::min(chunk, 16LL * thin);
   long long copied = 0;   // slots [0, copied) are on their way to the host
   // the sampling loop of the non-orthogonal stable driver hands (alpha_b, alpha_b) to the alpha step
   // (BridgeWrapper.cpp:294; its burn-in :272 and the other three drivers pass (alpha_a, alpha_b)): kept as written
@@ -809,21 +929,97 @@ void run_driver(int method, int ortho, const double* X, const double* y, int N, 
   if (method != BB_TRI && !ortho) hs.alpha_a = hs.alpha_b;
   while (done < total) {
     const long long n = std::min(chunk, total - done);
+    auto ts = std::chrono::steady_clock::now();
     chains_run(g.c, &hs, (unsigned)(nburn + done), (int)n, BB_ST_ALL, 0, 0, thin, 1 + done / thin, nullptr);
     done += n;
     const long long have = 1 + done / thin;
     download(copied, have - copied); copied = have;
+    if (interrupted()) {
+      BB_CUDA_CHECK(cudaStreamSynchronize(cps.s));
+      throw std::string("interrupted by the caller's hook (bb_set_interrupt) after ") + std::to_string(have) + " of " + std::to_string(nsamp) + " samples";
+    }
+    if (poll && g_interrupt) {
+      const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - ts).count();
+      if (sec > 0) chunk = std::max(16LL, std::min(8192LL, (long long)((chunk / thin) * 0.2 / sec))) * thin;
+    }
   }
   download(copied, nsamp - copied);
+  BB_CUDA_CHECK(cudaStreamSynchronize(cps.s));    // the clock stops when the last draws are in host memory
   const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-  if (runtime) *runtime = secs;
-  lap("sampling loop");
-  BB_CUDA_CHECK(cudaStreamSynchronize(cps.s));
+  lap("sampling loop + download");
   // summary mode: sum.stat of beta over the nsamp stored samples, on the device (the draws need not leave the GPU)
-  if ((sum_pooled || sum_chain) && bb_chains_summary(g.c, BB_OUT_BETA, 0, nsamp, secs, sum_chain, sum_pooled)) throw std::string(g_err);
-  if (status && bb_chains_get(g.c, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, status)) throw std::string(g_err);
-  lap("download");
-  if (g_verbose) std::printf("Sampling complete: %g sec. for %i iterations.\n", secs, nsamp);
+  if ((out.sum_pooled || out.sum_chain) && bb_chains_summary(g.c, BB_OUT_BETA, 0, nsamp, secs, out.sum_chain, out.sum_pooled)) throw std::string(g_err);
+  if (out.status && bb_chains_get(g.c, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, out.status)) throw std::string(g_err);
+  if (g_verbose && poll) std::printf("Sampling complete: %g sec. for %i iterations.\n", secs, nsamp);
+  return secs;
+}
+
+void run_driver(int method, int ortho, const double* X, const double* y, int N, int P, const bb_hyper* h,
+                int nchains, unsigned long long seed, unsigned int chain0, int burn, int nsamp, int thin, int device,
+                double* beta, double* aux1, double* aux2, double* aux3, double* sig2, double* tau, double* alpha,
+                unsigned int* status, double* runtime, double* sum_pooled = nullptr, double* sum_chain = nullptr) {
+  struct Guard { bb_model* m = nullptr; ~Guard() { delete m; } } g;
+  g.m = bb_model_create(X, y, N, P, device, BB_MEM_HOST);
+  if (!g.m) throw std::string(g_err);
+  DriverOut o;
+  o.beta = beta; o.aux1 = aux1; o.aux2 = aux2; o.aux3 = aux3; o.sig2 = sig2; o.tau = tau; o.alpha = alpha; o.status = status;
+  o.sum_pooled = sum_pooled; o.sum_chain = sum_chain;
+  const double secs = run_driver_on_model(g.m, method, ortho, h, nchains, seed, chain0, burn, nsamp, thin, o, true);
+  if (runtime) *runtime = secs;
+}
+
+// Device fan-out inside the library: the constructor runs once, on devices[0]; the other devices
+// receive a bit-for-bit copy of the factors over NVLink (peer copies); device k samples the k-th contiguous block of chains
+// on its own host thread.  Philox is keyed by the global chain id, so every draw equals the one-GPU run's.
+void run_driver_multi(int method, int ortho, const double* X, const double* y, int N, int P, const bb_hyper* h,
+                      int nchains, unsigned long long seed, unsigned int chain0, int burn, int nsamp, int thin,
+                      int ndevices, const int* devices, const DriverOut& out, double* runtime) {
+  int avail = 0;
+  if (cudaGetDeviceCount(&avail) != cudaSuccess || avail == 0) throw std::string("bb_bridge_batched_multi: no CUDA device (there is no CPU fallback)");
+  if (ndevices < 1 || ndevices > avail) throw std::string("bb_bridge_batched_multi: ndevices must be between 1 and the number of CUDA devices (") + std::to_string(avail) + ")";
+  if (nchains < ndevices) ndevices = nchains;
+  std::vector<int> devs(ndevices);
+  for (int k = 0; k < ndevices; ++k) {
+    devs[k] = devices ? devices[k] : k;
+    if (devs[k] < 0 || devs[k] >= avail) throw std::string("bb_bridge_batched_multi: bad device index");
+  }
+  if (out.sum_pooled || out.sum_chain) throw std::string("bb_bridge_batched_multi: summary mode runs on one device (bb_bridge_batched_summary)");
+  struct Models { std::vector<bb_model*> m; ~Models() { for (bb_model* x : m) delete x; } } ms;
+  ms.m.assign(ndevices, nullptr);
+  ms.m[0] = bb_model_create(X, y, N, P, devs[0], BB_MEM_HOST);
+  if (!ms.m[0]) throw std::string(g_err);
+  if (method == BB_TRI && !ortho) ensure_svd(ms.m[0]);
+  else if (ms.m[0]->lazy_svd && ndevices > 1) { /* P > N, stable sampler: the clone needs no SVD factors */ }
+  for (int k = 1; k < ndevices; ++k) {
+    if (ms.m[0]->lazy_svd) {   // copy what exists; the stable path never touches the missing factors
+      bb_model* src = ms.m[0];
+      const bool lazy = src->lazy_svd; src->lazy_svd = false;
+      try { ms.m[k] = model_clone(src, devs[k]); } catch (...) { src->lazy_svd = lazy; throw; }
+      src->lazy_svd = lazy; ms.m[k]->lazy_svd = false;
+    } else ms.m[k] = model_clone(ms.m[0], devs[k]);
+  }
+  std::vector<std::string> errs(ndevices);
+  std::vector<double> secs(ndevices, 0.0);
+  std::vector<std::thread> th;
+  auto block = [&](int k, int& lo, int& n) { lo = (int)((long long)nchains * k / ndevices); n = (int)((long long)nchains * (k + 1) / ndevices) - lo; };
+  auto work = [&](int k) {
+    int lo, n; block(k, lo, n);
+    DriverOut o = out;
+    const size_t ov = (size_t)lo * nsamp * P, os = (size_t)lo * nsamp;
+    if (o.beta) o.beta += ov; if (o.aux1) o.aux1 += ov; if (o.aux2) o.aux2 += ov; if (o.aux3) o.aux3 += ov;
+    if (o.sig2) o.sig2 += os; if (o.tau) o.tau += os; if (o.alpha) o.alpha += os; if (o.status) o.status += lo;
+    try { secs[k] = run_driver_on_model(ms.m[k], method, ortho, h, n, seed, chain0 + (unsigned)lo, burn, nsamp, thin, o, k == 0); }
+    catch (const bb::CudaError& e) { errs[k] = std::string("CUDA error: ") + cudaGetErrorString(e.code); }
+    catch (const std::string& e) { errs[k] = e.empty() ? std::string("error") : e; }
+    catch (const std::exception& e) { errs[k] = e.what(); }
+    catch (...) { errs[k] = "unknown error"; }
+  };
+  for (int k = 1; k < ndevices; ++k) th.emplace_back(work, k);
+  work(0);                                   // device 0's block on the calling thread (it is the one that may poll the hook)
+  for (std::thread& t : th) t.join();
+  for (int k = 0; k < ndevices; ++k)
+    if (!errs[k].empty()) throw std::string("device ") + std::to_string(devs[k]) + ": " + errs[k];
+  if (runtime) *runtime = *std::max_element(secs.begin(), secs.end());
 }
 
 }  // namespace
@@ -838,6 +1034,28 @@ int bb_bridge_batched(int method, int ortho, const double* X, const double* y, i
     run_driver(method, ortho, X, y, N, P, h, nchains, seed, chain0, burn, nsamp, thin, device, beta, aux1, aux2, aux3, sig2, tau,
                alpha, status, runtime);
   });
+}
+
+int bb_bridge_batched_multi(int method, int ortho, const double* X, const double* y, int N, int P, const bb_hyper* h,
+                            int nchains, unsigned long long seed, unsigned int chain0, int burn, int nsamp, int thin,
+                            int ndevices, const int* devices,
+                            double* beta, double* aux1, double* aux2, double* aux3, double* sig2, double* tau, double* alpha,
+                            unsigned int* status, double* runtime) {
+  return guarded([&] {
+    DriverOut o;
+    o.beta = beta; o.aux1 = aux1; o.aux2 = aux2; o.aux3 = aux3; o.sig2 = sig2; o.tau = tau; o.alpha = alpha; o.status = status;
+    run_driver_multi(method, ortho, X, y, N, P, h, nchains, seed, chain0, burn, nsamp, thin, ndevices, devices, o, runtime);
+  });
+}
+
+bb_model* bb_model_clone(const bb_model* src, int device) {
+  bb_model* m = nullptr;
+  const int rc = guarded([&] {
+    if (!src) throw std::string("bb_model_clone: null model");
+    ensure_svd(src);
+    m = model_clone(src, device);
+  });
+  return rc ? nullptr : m;
 }
 
 int bb_bridge_batched_summary(int method, int ortho, const double* X, const double* y, int N, int P, const bb_hyper* h,
@@ -903,10 +1121,17 @@ void scalar_call(const char* name, int kind, int n, const double* p0, const doub
     b.status = dalloc<uint32_t>(1);
     BB_CUDA_CHECK(cudaMemsetAsync(b.status, 0, sizeof(uint32_t), st));
     const bb::RngKey key{(uint32_t)g_seed, (uint32_t)(g_seed >> 32)};
-    launched(bb::launch_scalar(kind, n, b.d[0], b.d[1], b.d[2], b.d[3], b.d[4], key, g_scalar_calls++, b.status, st));
+    launched(bb::launch_scalar(kind, n, b.d[0], b.d[1], b.d[2], b.d[3], b.d[4], key, g_scalar_calls.fetch_add(1), b.status, st));
     check_launch();
+    uint32_t status = 0;
     BB_CUDA_CHECK(cudaMemcpyAsync(x, b.d[4], (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, st));
+    BB_CUDA_CHECK(cudaMemcpyAsync(&status, b.status, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     BB_CUDA_CHECK(cudaStreamSynchronize(st));
+    // the reference prints its own warnings (BridgeWrapper.cpp:899-934); a dropped status word would hand NaNs back silently
+    if (status & bb::ST_TRIAL_CAP) std::fprintf(stderr, "%s (bayesbridge_b200): warning: a rejection sampler reached its trial cap; the affected draws are NaN.\n", name);
+    if (status & bb::ST_EMPTY_INTERVAL) std::fprintf(stderr, "%s (bayesbridge_b200): warning: left > right for some items; the left bound was returned.\n", name);
+    if (status & bb::ST_NAN) std::fprintf(stderr, "%s (bayesbridge_b200): warning: NaN parameters for some items.\n", name);
+    g_scalar_status.store(status);
   });
   if (rc) {
     std::fprintf(stderr, "%s (bayesbridge_b200): %s\n", name, g_err.c_str());

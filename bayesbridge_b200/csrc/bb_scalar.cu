@@ -12,6 +12,10 @@
 
 namespace bb {
 
+// Trial cap of the right-truncated gamma (naive rejection from the untruncated law, Notes/bbnotes.tex:792-793): when
+// P(X <= right) is tiny a thread would otherwise spin through 2^24 Philox blocks (seconds).  The CPU checker carries the same cap.
+constexpr uint32_t RTG_CAP = 1u << 16;
+
 // sequential Gamma(shape, rate) starting at block k (advances k): the block order of the scalar draw spec
 __device__ inline double gamma_rate_seq(const Stream& s, uint32_t& k, double shape, double rate, uint32_t& status) {
   if (shape == 1.0) return -log(s.unif(k++)) / rate;
@@ -73,7 +77,7 @@ __global__ void __launch_bounds__(128) scalar_kernel(const int kind, const int n
       for (;;) {
         x = gamma_rate_seq(s, k, p0[i], p1[i], status);
         if (x <= p2[i] || x != x) break;
-        if (k >= K_CAP - 64) { x = nan(""); status |= ST_TRIAL_CAP; break; }
+        if (k >= RTG_CAP - 64) { x = nan(""); status |= ST_TRIAL_CAP; break; }   // bounded cost: NaN + a warning from the host
       }
       break;
     }

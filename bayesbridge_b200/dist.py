@@ -44,51 +44,81 @@ def row_range(N, rank, world):
     return chain_range(N, rank, world)
 
 
-def replicate(X, y, N, P, device, src=0):
+def _timed(fn, device, timing, key):
+    """run fn() between two CUDA events on torch's current stream; add the elapsed ms to timing[key]"""
+    if timing is None:
+        return fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    out = fn()
+    e1.record()
+    torch.cuda.synchronize(device)
+    timing[key] = timing.get(key, 0.0) + e0.elapsed_time(e1)
+    return out
+
+
+def replicate(X, y, N, P, device, src=0, timing=None):
     """One broadcast of the packed column-major [X | y] from `src`; returns device tensors (Xd, yd).
-    X, y are numpy arrays on `src` and may be None elsewhere."""
+    X, y are numpy arrays (or a pinned 1-D torch tensor holding the packed [X | y]) on `src` and may be None elsewhere.
+    timing (dict, optional) receives h2d_ms and comm_ms (the NCCL broadcast), timed with CUDA events."""
     buf = torch.empty((P + 1) * N, dtype=torch.float64, device=device)
     if not dist.is_initialized() or dist.get_rank() == src:
-        packed = np.concatenate([np.asfortranarray(X, dtype=np.float64).ravel(order="F"), np.asarray(y, dtype=np.float64)])
-        buf.copy_(torch.from_numpy(packed))
+        if torch.is_tensor(X):
+            host = X
+        else:
+            host = torch.from_numpy(np.concatenate([np.asfortranarray(X, dtype=np.float64).ravel(order="F"), np.asarray(y, dtype=np.float64)]))
+        _timed(lambda: buf.copy_(host, non_blocking=True), device, timing, "h2d_ms")
     if dist.is_initialized() and dist.get_world_size() > 1:
-        dist.broadcast(buf, src=src)
+        _timed(lambda: dist.broadcast(buf, src=src), device, timing, "comm_ms")
+        if timing is not None:
+            timing["collective"] = f"1 ncclBroadcast of [X|y] ({8 * (P + 1) * N / 1e6:.1f} MB) from rank {src}"
     return buf[: N * P], buf[N * P:], buf
 
 
-def replicated_model(X, y, N, P, local_device, src=0):
+def replicated_model(X, y, N, P, local_device, src=0, timing=None):
     """Model on this rank's GPU from data broadcast once over NCCL.  Keeps the device buffer alive."""
     dev = torch.device("cuda", local_device)
-    Xd, yd, buf = replicate(X, y, N, P, dev, src)
+    Xd, yd, buf = replicate(X, y, N, P, dev, src, timing)
     torch.cuda.synchronize(dev)
     m = Model.from_device(Xd.data_ptr(), yd.data_ptr(), N, P, local_device)
     m._keep = buf
     return m
 
 
-def sharded_model(X_rows, y_rows, N_total, P, local_device):
-    """Row-sharded construction: X_rows (n_local x P) and y_rows are this rank's rows (numpy)."""
+def sharded_model(X_rows, y_rows, N_total, P, local_device, timing=None):
+    """Row-sharded construction: X_rows (n_local x P) and y_rows are this rank's rows (numpy, or a pinned 1-D torch tensor
+    holding the packed column-major [X_rows | y_rows] with n_local = len / (P + 1)).
+    timing (dict, optional) receives h2d_ms and comm_ms (the two NCCL all-reduces), timed with CUDA events."""
     L = _lib.load()
     dev = torch.device("cuda", local_device)
-    n_local = X_rows.shape[0]
-    Xd = torch.from_numpy(np.asfortranarray(X_rows, dtype=np.float64).ravel(order="F").copy()).to(dev)
-    yd = torch.from_numpy(np.asarray(y_rows, dtype=np.float64).copy()).to(dev)
+    if torch.is_tensor(X_rows):
+        host = X_rows
+        n_local = host.numel() // (P + 1)
+    else:
+        n_local = X_rows.shape[0]
+        host = torch.from_numpy(np.concatenate([np.asfortranarray(X_rows, dtype=np.float64).ravel(order="F"), np.asarray(y_rows, dtype=np.float64)]))
+    buf = torch.empty((P + 1) * n_local, dtype=torch.float64, device=dev)
+    _timed(lambda: buf.copy_(host, non_blocking=True), dev, timing, "h2d_ms")
+    Xd, yd = buf[: n_local * P], buf[n_local * P:]
     G = torch.zeros((P + 1) * (P + 1), dtype=torch.float64, device=dev)
     torch.cuda.synchronize(dev)
     if L.bb_gram(Xd.data_ptr(), yd.data_ptr(), n_local, P, G.data_ptr(), local_device):
         raise RuntimeError(_lib.last_error())
-    if dist.is_initialized() and dist.get_world_size() > 1:
-        dist.all_reduce(G)          # the one all-reduce of the packed Gram matrix
+    multi = dist.is_initialized() and dist.get_world_size() > 1
+    if multi:
+        _timed(lambda: dist.all_reduce(G), dev, timing, "comm_ms")          # the one all-reduce of the packed Gram matrix
     torch.cuda.synchronize(dev)
     m = Model.from_gram(G.data_ptr(), N_total, P, local_device)
     r = torch.zeros(2, dtype=torch.float64, device=dev)
     if L.bb_model_resid_partial(m.h, Xd.data_ptr(), yd.data_ptr(), n_local, r.data_ptr()):
         raise RuntimeError(_lib.last_error())
-    if dist.is_initialized() and dist.get_world_size() > 1:
-        dist.all_reduce(r)
+    if multi:
+        _timed(lambda: dist.all_reduce(r), dev, timing, "comm_ms")
+        if timing is not None:
+            timing["collective"] = f"ncclAllReduce of the packed Gram [X'X X'y; y'X y'y] ({8 * (P + 1) ** 2 / 1e6:.2f} MB) + 16-byte all-reduce of the residual constants"
     r = r.cpu().numpy()
     L.bb_model_set_r0(m.h, float(r[0]), float(r[1]))
-    m._keep = (Xd, yd, G)
+    m._keep = (buf, G)
     return m
 
 

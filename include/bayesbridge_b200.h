@@ -64,6 +64,17 @@ void bb_set_seed(unsigned long long seed);
 void bb_set_device(int device);
 /* Banner printing of the reference drivers (BridgeWrapper.cpp:112-117,162-163,200): 0 = quiet (default). */
 void bb_set_verbose(int verbose);
+/* Interrupt hook, the role of R_CheckUserInterrupt() in the reference's loops (every 10 iterations, BridgeWrapper.cpp:154-156,
+ * 186-188; every 1000 rejection trials, retstable.cpp:158-166).  The sampling loop runs on the GPU in chunks; between chunks
+ * (sized to about 0.2 s of work while a hook is installed) the CALLING thread calls fn(); a non-zero return aborts the run:
+ * the entry point returns non-zero with bb_last_error() = "interrupted ...", the .C symbols print that and NaN-fill their
+ * outputs like any other failure.  An R binding installs a function that wraps R_ToplevelExec(R_CheckUserInterrupt) (see
+ * INTEGRATION.md).  NULL removes the hook. */
+void bb_set_interrupt(int (*fn)(void));
+/* Status word of the last stand-alone sampler call (rtnorm, rtexpon_rate, rrtgamma_rate, retstable_LD ...): bit 0 NaN
+ * parameters, bit 1 empty interval (left > right), bit 2 a rejection loop reached its trial cap (those draws are NaN).
+ * The same conditions are also printed to stderr, as the reference prints its own warnings (BridgeWrapper.cpp:899-934). */
+unsigned int bb_scalar_status(void);
 
 /* Stand-alone scalar samplers exported by the reference's shared object next to the two Gibbs entry points
  * (declarations BridgeWrapper.h:230-244, bodies BridgeWrapper.cpp:762-984; R callers BridgeWrapper.R:295-537).
@@ -143,6 +154,13 @@ int bb_gram_noalloc(const double *X_dev, const double *y_dev, int n_rows, int P,
 int bb_model_resid_partial(const bb_model *m, const double *X_dev, const double *y_dev, int n_rows, double *out_dev);
 int bb_model_set_r0(bb_model *m, double r0z, double r0b);
 void bb_model_free(bb_model *m);
+/* A bit-for-bit copy of the model's factors on another device (peer copies over NVLink; the rows X, y are not copied: the
+ * sweep never reads them).  Chains on the copy produce exactly the draws they would produce on the original. */
+bb_model *bb_model_clone(const bb_model *src, int device);
+/* 0 = clean; n > 0: n singular values between 1e-13 and 1e-7 of the largest were set to zero because the factors had to be
+ * taken from X'X (bb_model_create_gram, or P > N) -- for cond(X) >= 1e7 the reference's SVD of X would keep them (also
+ * printed to stderr when it happens).  Build the model from the rows (bb_model_create with N >= P) to avoid it. */
+int bb_model_status(const bb_model *m);
 /* copy factors to host (any pointer may be NULL) */
 int bb_model_get(const bb_model *m, double *XX, double *Xy, double *bhat, double *tV, double *d, double *a);
 double bb_model_precompute_ms(const bb_model *m);
@@ -185,6 +203,9 @@ int bb_chains_summary(const bb_chains *c, int which, long long slot0, long long 
                       double *per_chain, double *pooled);
 /* number of kernels launched by this library in this process so far */
 long long bb_launch_count(void);
+/* Measurement aid, no counterpart in the reference: measured peak of the FP64 vector pipe (DFMA) of `device` in
+ * TFLOP/s -- the roofline denominator of the triangle sweep, which has no contraction (bench.py). */
+int bb_measure_fp64_fma(int device, double *tflops);
 
 /* ---------------------------------------------------------------------------------------- */
 /* Part 3: batched extension                                                                 */
@@ -200,6 +221,19 @@ int bb_bridge_batched(int method, int ortho,
                       int burn, int nsamp, int thin, int device,
                       double *beta, double *aux1, double *aux2, double *aux3,
                       double *sig2, double *tau, double *alpha, unsigned int *status, double *runtime);
+
+/* bb_bridge_batched over several GPUs of one box, inside the library: the constructor (Gram, SVD
+ * factors) runs once on devices[0]; the other devices get a bit-for-bit copy of the factors by peer copies over NVLink
+ * (bb_model_clone); device k samples the k-th contiguous block of chains on its own host thread and streams its draws into
+ * its slice of the same host arrays.  devices: ndevices device indices, or NULL for 0 .. ndevices-1.  The Philox stream of
+ * a chain depends only on (seed, chain0 + index), so the outputs equal the one-GPU call's bit for bit.  There is no
+ * collective: nothing is exchanged during sampling.  runtime = the slowest device's post-burn-in loop. */
+int bb_bridge_batched_multi(int method, int ortho,
+                            const double *X, const double *y, int N, int P, const bb_hyper *h,
+                            int nchains, unsigned long long seed, unsigned int chain0,
+                            int burn, int nsamp, int thin, int ndevices, const int *devices,
+                            double *beta, double *aux1, double *aux2, double *aux3,
+                            double *sig2, double *tau, double *alpha, unsigned int *status, double *runtime);
 
 /* The same run in SUMMARY mode: the draws of beta stay in HBM and sum.stat is taken on the
  * device.  pooled: [7][P] (mean, sd, ESS, ESS.sec, t, Q.1, Q.9 over all chains, ESS.sec = ESS / runtime of the

@@ -48,6 +48,7 @@ enum {
 };
 
 #define BBO_K_CAP (1u << 24) /* trial cap: k must stay below 2^24 */
+#define BBO_RTG_CAP (1u << 16) /* trial cap of the right-truncated gamma's naive rejection */
 
 typedef struct {
   uint32_t seed_lo, seed_hi; /* key */
@@ -212,7 +213,7 @@ static inline double bbo_rtgamma_rate(bbo_rng *r, double shape, double rate, dou
   for (;;) {
     double x = bbo_gamma_rate(r, shape, rate);
     if (x <= right || x != x) return x;
-    if (r->k >= BBO_K_CAP - 64) return NAN;
+    if (r->k >= BBO_RTG_CAP - 64) return NAN;   /* bounded cost, same cap as the device (bb_scalar.cu RTG_CAP) */
   }
 }
 
