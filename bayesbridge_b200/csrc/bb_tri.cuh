@@ -107,6 +107,20 @@ __device__ __forceinline__ double reduce_minima(const double (&lmn)[C], const do
   }
 }
 
+// Phase timing (development, -DBB_TRI_PHASES): one thread of CTA 0 (BB_TRI_PHASE_TID, default 0) accumulates, in shared memory,
+// the cycles between the marks of the coordinate step; [0..7] steps in which its warp draws, [8..15] the other steps:
+// 7 = loop top + TMA issue, 0 = column wait + load, 1 = candidates + butterfly, 2 = barrier 1, 3 = draw (or RNG look-ahead),
+// 4 = barrier 2, 5 = axpy; [6] / [14] count the steps.  Each mark costs about 40 cycles itself.
+#ifdef BB_TRI_PHASES
+#ifndef BB_TRI_PHASE_TID
+#define BB_TRI_PHASE_TID 0
+#endif
+__device__ unsigned long long tri_phase_cyc[16];
+#define BB_TRI_MARK(k) do { if (ph_on) { const long long now_ = clock64(); ph_acc[ph_half + (k)] += (unsigned long long)(now_ - ph_t); ph_t = now_; } } while (0)
+#else
+#define BB_TRI_MARK(k) do { } while (0)
+#endif
+
 // shared-memory footprint of one CTA (bytes); mirrored by the host launcher
 __host__ __device__ inline size_t tri_smem_bytes(int P, int LD, int S, int NG, int W, int C) {
   const size_t CH = (size_t)NG * C;
@@ -217,8 +231,15 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
   // ring cursor
   int rs = 0; uint32_t ruse = 0; long long nstep = 0;
   double2 vq[J], dm, dm2;   // dm = {d_i, mean_i}, dm2 = {1/d_i, -}
+#ifdef BB_TRI_PHASES
+  bool ph_on = false; int ph_half = 0; long long ph_t = 0;
+  __shared__ unsigned long long ph_acc[16];
+  if (tid < 16) ph_acc[tid] = 0;
+  __syncthreads();
+#endif
   auto next_column = [&]() {   // wait for the column, copy this lane's slice into registers, release the stage
     if (issuer && inext < nload && inext <= nstep + S - D) issue_one();
+    BB_TRI_MARK(7);
     if (!resident || nstep < P) mbar_wait(&full[rs], ruse & 1);
     const double2* col = ring + (size_t)rs * LQ;
     dm = col[LD]; dm2 = col[LD + 1];
@@ -386,10 +407,17 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
     for (int sw = 0; do_beta && sw < nsweep; ++sw) {
       for (int i = 0; i < P; ++i) {
         const bool drawer = (W == 1) || (w == i % W);
+#ifdef BB_TRI_PHASES
+        ph_on = blockIdx.x == 0 && tid == BB_TRI_PHASE_TID;
+        ph_half = drawer ? 0 : 8;
+        ph_t = clock64();
+        if (ph_on) ph_acc[ph_half + 6] += 1;
+#endif
         Stream s(L.key, gch_d, t, ST_BETA, (uint32_t)(sw * P + i));
         if (drawer && !have_rng) { double ua, ub; s.block((uint32_t)sl, ua, ub); td.set(ua, ub); }
         have_rng = false;
         next_column();
+        BB_TRI_MARK(0);
         double di = 0.0, mean = 0.0, sd = 1.0, isd = 1.0;
         if (drawer) { di = dm.x; mean = dm.y; sd = sig_d * dm2.x; isd = di * isig_d; }   // sd = sig/d_i (:269) by reciprocals
         // ---- candidates: min_j fma(beta_j, q, b_j|q|) and min_j fma(-beta_j, q, b_j|q|) ----
@@ -408,9 +436,11 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
         }
         // after the transposed butterfly the first half of draw slice c holds L_c, the second half R_c
         double keep = reduce_minima<C>(lmn, rmn, lane);
+        BB_TRI_MARK(1);
         if (W > 1) {
           if ((sl & (SL / 2 - 1)) == 0) redg0[(w * C + dc) * 2 + (sl >= SL / 2 ? 1 : 0)] = keep;
           bar_sync(bar_id, bar_n);
+          BB_TRI_MARK(2);
           if (!drawer && i + 1 < P && w == (i + 1) % W) {   // idle until the draw is done: prepare the next step's trial
             Stream sn(L.key, gch_d, t, ST_BETA, (uint32_t)(sw * P + i + 1));
             double ua, ub; sn.block((uint32_t)sl, ua, ub); td.set(ua, ub);
@@ -460,7 +490,9 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
           }
           if (sl == 0) { zg[dc * P + i] = znew; bc[g * C + dc] = znew - zold; }
         }
+        BB_TRI_MARK(3);
         group_sync();
+        BB_TRI_MARK(4);
         // ---- beta += V[:,i] (z_i' - z_i) ----
 #pragma unroll
         for (int c = 0; c < C; ++c) {
@@ -469,6 +501,7 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
           for (int jj = 0; jj < J; ++jj) cur[c][jj] = fma(vq[jj].x, dl, cur[c][jj]);
         }
         if (W == 1) __syncwarp();   // bc is rewritten by the next step's draw
+        BB_TRI_MARK(5);
       }
     }
 
@@ -517,6 +550,9 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
     }
   }
 
+#ifdef BB_TRI_PHASES
+  if (blockIdx.x == 0 && tid == BB_TRI_PHASE_TID) for (int k = 0; k < 16; ++k) tri_phase_cyc[k] += ph_acc[k];
+#endif
   // ---------------- write state back ----------------
   group_sync();
 #pragma unroll
