@@ -67,6 +67,26 @@ __device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t
 __device__ __forceinline__ double dmin_keep(double m, double x) { return (x < m) ? x : m; }
 __device__ __forceinline__ double shfl_xor_d(double v, int o) { return __shfl_xor_sync(0xffffffffu, v, o); }
 
+// Warp-wide minimum of one double on the integer REDUX unit: the doubles are mapped to their order-preserving 64-bit
+// integer image, the high words are reduced (redux.sync.min.u32), then the low words among the lanes that tie on the high
+// word.  Two dependent REDUX instead of five shuffle rounds of (2 SHFL + DSETP + 2 SEL); every lane receives the result.
+// Inputs must not be NaN (the per-lane minima never are: dmin_keep drops NaN candidates, the start value is +inf).
+// -0.0 orders below +0.0 here; both bound the same interval.  Measured (scripts/mb/mb_reduce.cu): 4 values 126 cycles
+// against 230 for the transposed butterfly.
+__device__ __forceinline__ uint32_t redux_min_u32(uint32_t v) {
+  uint32_t r; asm volatile("redux.sync.min.u32 %0, %1, 0xffffffff;" : "=r"(r) : "r"(v)); return r;
+}
+__device__ __forceinline__ double warp_min_redux(double x) {
+  const long long b = __double_as_longlong(x);
+  const unsigned long long k = (unsigned long long)(b ^ ((b >> 63) | (long long)0x8000000000000000ULL));
+  const uint32_t hi = (uint32_t)(k >> 32), lo = (uint32_t)k;
+  const uint32_t mh = redux_min_u32(hi);
+  const uint32_t ml = redux_min_u32(hi == mh ? lo : 0xffffffffu);
+  const unsigned long long m = ((unsigned long long)mh << 32) | ml;
+  const long long r = (long long)(m ^ ((m >> 63) ? 0x8000000000000000ULL : 0xffffffffffffffffULL));
+  return __longlong_as_double(r);
+}
+
 // Reduce NV = 2C per-lane minima over the 32 lanes with a TRANSPOSED butterfly: at the first log2(NV)
 // levels a lane keeps one half of its values and hands the other half to its partner, so the number of
 // live values halves together with the distance; plain butterflies finish the last value.  On return
@@ -75,6 +95,15 @@ __device__ __forceinline__ double shfl_xor_d(double v, int o) { return __shfl_xo
 // 2C = 4: 7 shuffle rounds of one double instead of 20.
 template <int C>
 __device__ __forceinline__ double reduce_minima(const double (&lmn)[C], const double (&rmn)[C], int lane) {
+#ifndef BB_TRI_BUTTERFLY
+  if (C <= 2) {   // same lane layout as the butterflies below: value v = (L_0, R_0[, L_1, R_1]) in lanes [v 32/(2C), (v+1) 32/(2C))
+    double out = warp_min_redux(lmn[0]);
+    const double r0 = warp_min_redux(rmn[0]);
+    if (C == 1) return (lane & 16) ? r0 : out;
+    const double l1 = warp_min_redux(lmn[C - 1]), r1 = warp_min_redux(rmn[C - 1]);
+    return (lane & 16) ? ((lane & 8) ? r1 : l1) : ((lane & 8) ? r0 : out);
+  }
+#endif
   if (C == 1) {
     const bool hi = lane & 16;
     double keep = hi ? rmn[0] : lmn[0], send = hi ? lmn[0] : rmn[0];
@@ -115,7 +144,7 @@ __device__ __forceinline__ double reduce_minima(const double (&lmn)[C], const do
 #ifndef BB_TRI_PHASE_TID
 #define BB_TRI_PHASE_TID 0
 #endif
-__device__ unsigned long long tri_phase_cyc[16];
+__device__ unsigned long long tri_phase_cyc[32];
 #define BB_TRI_MARK(k) do { if (ph_on) { const long long now_ = clock64(); ph_acc[ph_half + (k)] += (unsigned long long)(now_ - ph_t); ph_t = now_; } } while (0)
 #else
 #define BB_TRI_MARK(k) do { } while (0)
@@ -233,14 +262,19 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
   double2 vq[J], dm, dm2;   // dm = {d_i, mean_i}, dm2 = {1/d_i, -}
 #ifdef BB_TRI_PHASES
   bool ph_on = false; int ph_half = 0; long long ph_t = 0;
-  __shared__ unsigned long long ph_acc[16];
-  if (tid < 16) ph_acc[tid] = 0;
+  __shared__ unsigned long long ph_acc[32];
+  if (tid < 32) ph_acc[tid] = 0;
   __syncthreads();
 #endif
-  auto next_column = [&]() {   // wait for the column, copy this lane's slice into registers, release the stage
-    if (issuer && inext < nload && inext <= nstep + S - D) issue_one();
+  // Thread 0 keeps the ring S - D columns ahead; called where warp 0 is idle (see the sweep), at most two copies per call.
+  auto maybe_issue = [&]() {
+    if (!issuer) return;
+    for (int k = 0; k < 2 && inext < nload && inext <= nstep + S - D; ++k) issue_one();
+  };
+  // `waited`: a warp of this group has already observed the column's barrier and a group barrier has passed since.
+  auto next_column = [&](bool waited) {   // wait for the column, copy this lane's slice into registers, release the stage
     BB_TRI_MARK(7);
-    if (!resident || nstep < P) mbar_wait(&full[rs], ruse & 1);
+    if (!waited && (!resident || nstep < P)) mbar_wait(&full[rs], ruse & 1);
     const double2* col = ring + (size_t)rs * LQ;
     dm = col[LD]; dm2 = col[LD + 1];
 #pragma unroll
@@ -256,7 +290,8 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
   // ---------------- z = V' beta (BridgeRegression.cpp:246) from the registers, or from the state ----------------
   if (L.init_z) {
     for (int i = 0; i < P; ++i) {
-      next_column();
+      maybe_issue();
+      next_column(false);
       double pz[C];
 #pragma unroll
       for (int c = 0; c < C; ++c) {
@@ -404,19 +439,22 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
     // bounds.  With W > 1 the warp that draws step i+1 prepares them while the drawer of step i is busy.
     TnDraw td; td.ua = 0.5; td.ub = 0.5; td.nlu = 0.0; td.lub = 0.0; td.xn = 0.0;
     bool have_rng = false;
+    bool col_waited = false;   // the next column's barrier was observed by the idle warps of this group during the last draw
     for (int sw = 0; do_beta && sw < nsweep; ++sw) {
       for (int i = 0; i < P; ++i) {
         const bool drawer = (W == 1) || (w == i % W);
 #ifdef BB_TRI_PHASES
         ph_on = blockIdx.x == 0 && tid == BB_TRI_PHASE_TID;
-        ph_half = drawer ? 0 : 8;
+        ph_half = drawer ? 0 : 16;
         ph_t = clock64();
         if (ph_on) ph_acc[ph_half + 6] += 1;
 #endif
         Stream s(L.key, gch_d, t, ST_BETA, (uint32_t)(sw * P + i));
         if (drawer && !have_rng) { double ua, ub; s.block((uint32_t)sl, ua, ub); td.set(ua, ub); }
         have_rng = false;
-        next_column();
+        if (W == 1) maybe_issue();
+        next_column(col_waited);
+        col_waited = false;
         BB_TRI_MARK(0);
         double di = 0.0, mean = 0.0, sd = 1.0, isd = 1.0;
         if (drawer) { di = dm.x; mean = dm.y; sd = sig_d * dm2.x; isd = di * isig_d; }   // sd = sig/d_i (:269) by reciprocals
@@ -434,6 +472,7 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
             rmn[c] = dmin_keep(rmn[c], fma(-cur[c][jj], q, gq));
           }
         }
+        BB_TRI_MARK(8);
         // after the transposed butterfly the first half of draw slice c holds L_c, the second half R_c
         double keep = reduce_minima<C>(lmn, rmn, lane);
         BB_TRI_MARK(1);
@@ -441,7 +480,15 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
           if ((sl & (SL / 2 - 1)) == 0) redg0[(w * C + dc) * 2 + (sl >= SL / 2 ? 1 : 0)] = keep;
           bar_sync(bar_id, bar_n);
           BB_TRI_MARK(2);
-          if (!drawer && i + 1 < P && w == (i + 1) % W) {   // idle until the draw is done: prepare the next step's trial
+          // Idle until the draw is done.  The idle warps service the column stream: thread 0 issues the TMA copies, and every
+          // idle warp waits for the NEXT column's barrier here (90 cycles even when the data has long landed), so that after
+          // the group barrier below nobody -- the drawer included -- has to wait for it at the top of the next step.
+          if (!drawer) {
+            maybe_issue();
+            if (nstep < total_steps && (!resident || nstep < P)) mbar_wait(&full[rs], ruse & 1);   // rs / nstep already point at the next step
+          }
+          col_waited = true;
+          if (!drawer && i + 1 < P && w == (i + 1) % W) {   // ... and the next drawer prepares its first trial
             Stream sn(L.key, gch_d, t, ST_BETA, (uint32_t)(sw * P + i + 1));
             double ua, ub; sn.block((uint32_t)sl, ua, ub); td.set(ua, ub);
             have_rng = true;
@@ -460,10 +507,12 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
           }
           const double zold = zg[dc * P + i];
           const double lm = zold - lq, rm = zold + rq;
+          BB_TRI_MARK(9);
           double znew;
           if (di > 1e-16) {   // BridgeRegression.cpp:268-273
             const double a = (lm - mean) * isd, b = (rm - mean) * isd;
             const TnPlan p = tn_setup_fast(a, b);
+            BB_TRI_MARK(10);
             double x = 0.0;
             bool fin = false;
             if (p.mode == 5) { status |= ST_NAN; x = a + b; fin = true; }
@@ -472,15 +521,20 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
             while (true) {
               double xt = 0.0;
               const bool acc_ = !fin && tn_eval_log(p, td, xt);
-              const uint32_t mine = __ballot_sync(0xffffffffu, acc_) & slmask;
+              const uint32_t all = __ballot_sync(0xffffffffu, acc_ || fin);   // a finished slice reports all its lanes
+              const uint32_t mine = all & slmask;
               const int src = mine ? (__ffs(mine) - 1) : lane;
               const double xs = __shfl_sync(0xffffffffu, xt, src);
               if (!fin && mine) { x = p.sgn * xs; fin = true; }
-              if (__ballot_sync(0xffffffffu, !fin) == 0u) break;
+              bool done = true;                                               // every slice has an accepting (or finished) lane
+#pragma unroll
+              for (int c = 0; c < C; ++c) done = done && ((all >> (c * SL)) & ((SL == 32) ? 0xffffffffu : ((1u << SL) - 1u))) != 0u;
+              if (done) break;
               base += SL;
               if (base >= K_CAP - 32) { if (!fin) { status |= ST_TRIAL_CAP; x = nan(""); fin = true; } break; }
               if (!fin) { double ua, ub; s.block(base + (uint32_t)sl, ua, ub); td.set(ua, ub); }
             }
+            BB_TRI_MARK(11);
             znew = mean + sd * x;
             if (znew < lm) znew = lm;
             if (znew > rm) znew = rm;
@@ -551,7 +605,7 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
   }
 
 #ifdef BB_TRI_PHASES
-  if (blockIdx.x == 0 && tid == BB_TRI_PHASE_TID) for (int k = 0; k < 16; ++k) tri_phase_cyc[k] += ph_acc[k];
+  if (blockIdx.x == 0 && tid == BB_TRI_PHASE_TID) for (int k = 0; k < 32; ++k) tri_phase_cyc[k] += ph_acc[k];
 #endif
   // ---------------- write state back ----------------
   group_sync();
