@@ -18,6 +18,7 @@ up = C.POINTER(C.c_uint)
 BB_TRI, BB_STB = 0, 1
 MEM_HOST, MEM_DEVICE = 0, 1
 ST_TAU, ST_SIG2, ST_OMEGA, ST_U, ST_BETA, ST_LAMBDA, ST_ALPHA, ST_ALL = 1, 2, 4, 8, 16, 32, 64, 127
+OPT_WIDE_GAUSSIAN = 1
 OUT_BETA, OUT_U, OUT_OMEGA, OUT_SHAPE, OUT_LAMBDA, OUT_SIG2, OUT_TAU, OUT_ALPHA = 1, 2, 4, 8, 16, 32, 64, 128
 
 # every symbol include/bayesbridge_b200.h declares
@@ -26,7 +27,7 @@ EXPORTS = [
     "bb_last_error", "bb_device_count", "bb_model_create", "bb_model_create_factors", "bb_gram", "bb_gram_noalloc",
     "bb_model_create_gram", "bb_model_resid_partial", "bb_model_set_r0", "bb_model_free", "bb_model_clone", "bb_model_status", "bb_model_get",
     "bb_model_precompute_ms", "bb_chains_create", "bb_chains_free", "bb_chains_set", "bb_chains_get", "bb_chains_alpha",
-    "bb_chains_reserve", "bb_chains_run", "bb_chains_store_state", "bb_chains_fetch", "bb_chains_summary", "bb_launch_count", "bb_measure_fp64_fma",
+    "bb_chains_option", "bb_set_wide_gaussian", "bb_chains_reserve", "bb_chains_run", "bb_chains_store_state", "bb_chains_fetch", "bb_chains_summary", "bb_launch_count", "bb_measure_fp64_fma",
     "bb_bridge_batched", "bb_bridge_batched_multi", "bb_bridge_batched_summary",
     "rtexpon_rate_left", "rtexpon_rate_both", "rtexpon_rate", "rtnorm_left", "rtnorm_both", "rtnorm", "rrtgamma_rate", "retstable_LD",
 ]
@@ -84,6 +85,9 @@ def load():
     L.bb_chains_set.argtypes = [vp] + [dp] * 5
     L.bb_chains_get.argtypes = [vp] + [dp] * 6 + [up]
     L.bb_chains_alpha.argtypes = [vp, dp, dp]
+    L.bb_chains_option.argtypes = [vp, C.c_int, C.c_int]
+    L.bb_set_wide_gaussian.argtypes = [C.c_int]
+    L.bb_set_wide_gaussian.restype = None
     L.bb_chains_reserve.argtypes = [vp, C.c_longlong, C.c_int]
     L.bb_chains_run.argtypes = [vp, C.POINTER(Hyper), C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int, C.c_longlong, dp]
     L.bb_chains_store_state.argtypes = [vp, C.c_longlong]

@@ -263,6 +263,12 @@ class Chains:
         if rc:
             raise RuntimeError(_lib.last_error())
 
+    def wide_gaussian(self, on=True):
+        """opt into the N x N form of the Gaussian draw of beta (stable sampler, P > N; bb_chains_option): same law as
+        sample_beta_stable (BridgeRegression.cpp:552-575), not the same draws"""
+        self._ck(self.L.bb_chains_option(self.h, _lib.OPT_WIDE_GAUSSIAN, int(bool(on))))
+        return self
+
     def set(self, beta=None, u=None, aux=None, sig2=None, tau=None, alpha=None):
         arrs = [None if a is None else _f(a) for a in (beta, u, aux, sig2, tau)]
         self._ck(self.L.bb_chains_set(self.h, *[_p(a) for a in arrs]))

@@ -29,6 +29,7 @@ std::atomic<unsigned> g_scalar_calls{0};   // Philox `iter` word of the stand-al
 int g_device = 0;
 int g_verbose = 0;
 std::atomic<unsigned> g_scalar_status{0};  // status word (bb::Status bits) of the last stand-alone sampler call
+int g_wide_default = 0;                    // bb_set_wide_gaussian: the drivers opt their chains into BB_OPT_WIDE_GAUSSIAN where it applies
 int (*g_interrupt)(void) = nullptr;        // bb_set_interrupt: polled between chunks of the sampling loop on the calling thread
 
 void set_err(const std::string& s) { g_err = s; }
@@ -256,18 +257,28 @@ struct bb_chains {
   double *sig2 = nullptr, *tau = nullptr, *alpha = nullptr;
   uint32_t* status = nullptr;
   double *A = nullptr, *W = nullptr, *Q = nullptr;   // large-P stable workspace: factors, inverse diagonal blocks, partial sums of d'X'Xd
+  int wide = 0;                                      // BB_OPT_WIDE_GAUSSIAN: the Gaussian draw through the N x N system (bb_stb_wide.cuh)
+  double *U = nullptr, *R = nullptr;                 // its workspace: u [nchains][P], right-hand side [nchains][N]
   // draw buffer
   long long nslots = 0; int out_mask = 0;
   double *o_beta = nullptr, *o_u = nullptr, *o_omega = nullptr, *o_shape = nullptr, *o_lambda = nullptr;
   double *o_sig2 = nullptr, *o_tau = nullptr, *o_alpha = nullptr;
+  // large-P stable path: one Gibbs iteration of a sub-batch (about 50 small launches at P = 256) captured once as a CUDA graph
+  // and replayed; gkey = the frozen launch parameters the graph was captured with, ctl = [sub-batch][2] iteration / slot offsets
+  cudaGraphExec_t gx[4] = {nullptr, nullptr, nullptr, nullptr};
+  std::vector<char> gkey[4];
+  int glaunches[4] = {0, 0, 0, 0};
+  long long* ctl = nullptr;
   cudaStream_t stream = nullptr, stream2 = nullptr, xs[3] = {nullptr, nullptr, nullptr};   // xs: the other sub-batches of the large-P stable path
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr, ev_join = nullptr, xj[3] = {nullptr, nullptr, nullptr};
 
   void free_draws() { dfree(o_beta); dfree(o_u); dfree(o_omega); dfree(o_shape); dfree(o_lambda); dfree(o_sig2); dfree(o_tau); dfree(o_alpha); nslots = 0; out_mask = 0; }
   ~bb_chains() {
     cudaSetDevice(device);
-    dfree(beta); dfree(u); dfree(aux); dfree(shape); dfree(z); dfree(sig2); dfree(tau); dfree(alpha); dfree(status); dfree(A); dfree(W); dfree(Q);
+    dfree(beta); dfree(u); dfree(aux); dfree(shape); dfree(z); dfree(sig2); dfree(tau); dfree(alpha); dfree(status); dfree(A); dfree(W); dfree(Q); dfree(U); dfree(R);
     free_draws();
+    for (int i = 0; i < 4; ++i) if (gx[i]) cudaGraphExecDestroy(gx[i]);
+    dfree(ctl);
     if (ev0) cudaEventDestroy(ev0);
     if (ev1) cudaEventDestroy(ev1);
     if (ev_fork) cudaEventDestroy(ev_fork);
@@ -378,12 +389,20 @@ void chains_run(bb_chains* c, const bb_hyper* hh, unsigned iter0, int niter, int
     L.sink = make_sink(c, thin, slot0);
     launched(bb::launch_stb_small(L, st));
   } else {
-    if (!c->A) { c->A = dalloc<double>((size_t)c->nchains * P * P); c->W = dalloc<double>((size_t)c->nchains * ((P + 63) / 64) * 64 * 64); if (P >= 512) c->Q = dalloc<double>((size_t)c->nchains * ((P + 31) / 32)); }
+    const int Nw = m->N;
+    const size_t dimA = c->wide ? (size_t)Nw : (size_t)P;               // order of the per-chain system that is factored
+    const size_t wblk = ((dimA + 63) / 64) * 64 * 64;
+    if (!c->A) {
+      c->A = dalloc<double>((size_t)c->nchains * dimA * dimA); c->W = dalloc<double>((size_t)c->nchains * wblk);
+      if (P >= 512 && !c->Q) c->Q = dalloc<double>((size_t)c->nchains * ((P + 31) / 32));
+      if (c->wide) { c->U = dalloc<double>((size_t)c->nchains * P); c->R = dalloc<double>((size_t)c->nchains * Nw); }
+    }
     // (Q: the batched d'X'Xd kernel pays from P = 512 on; at P = 256 the extra launch costs more than the per-chain loop: c5s 112 -> 109 M)
     bb::StbLargeLaunch L;
     L.m = m->view(); L.h = h; L.key = key; L.nchains = c->nchains; L.chain0 = c->chain0; L.stages = stages;
     L.beta = c->beta; L.lambda = c->aux; L.sig2 = c->sig2; L.tau = c->tau; L.alpha = c->alpha; L.status = c->status;
     L.A = c->A; L.W = c->W; L.Q = c->Q; L.sink = make_sink(c, thin, slot0);
+    L.wide = c->wide; L.U = c->U; L.R = c->R;
     bb::stb_large_prepare(P);
     // Sub-batches on their own streams: the low-parallelism kernels of one sub-batch (diagonal-block factorisation, panel
     // solve, substitution: one CTA per chain) run while another sub-batch's update kernel fills the SMs.  The sub-batches
@@ -408,7 +427,8 @@ void chains_run(bb_chains* c, const bb_hyper* hh, unsigned iter0, int niter, int
       const size_t o1 = (size_t)h0, oP = (size_t)h0 * P;
       H.nchains = h1 - h0; H.chain0 = L.chain0 + (uint32_t)h0;
       H.beta += oP; H.lambda += oP; H.sig2 += o1; H.tau += o1; H.alpha += o1; H.status += o1;
-      H.A += oP * P; H.W += o1 * ((P + 63) / 64) * 64 * 64; if (H.Q) H.Q += o1 * ((P + 31) / 32);
+      H.A += o1 * dimA * dimA; H.W += o1 * wblk; if (H.Q) H.Q += o1 * ((P + 31) / 32);
+      if (H.wide) { H.U += oP; H.R += o1 * (size_t)Nw; }
       const size_t os = o1 * (size_t)H.sink.chain_stride;
       if (H.sink.beta) H.sink.beta += os * P;
       if (H.sink.lambda) H.sink.lambda += os * P;
@@ -418,7 +438,56 @@ void chains_run(bb_chains* c, const bb_hyper* hh, unsigned iter0, int niter, int
       if (H.sink.sum) { H.sink.sum += oP; H.sink.sumsq += oP; }
       return H;
     };
-    for (int it = -pre_tau; it < niter; ++it) {
+    L.ctl = nullptr;
+    // Graph replay: every iteration of a run is the same sequence of launches; only the iteration index (RNG counter) and
+    // the sink slot move, and those come from device memory (StbLargeLaunch::ctl).  One iteration of one sub-batch is
+    // captured once -- and again whenever a frozen parameter (hyper-parameters, stages, store or not) changes -- then
+    // replayed niter times: one cudaGraphLaunch per sub-batch and iteration instead of ~50 launches, which at P = 256 took
+    // longer to issue from the host than to run.  thin > 1 (stores on some iterations only) and short runs launch directly.
+    static const bool graph_off = std::getenv("BB_STBL_NOGRAPH") != nullptr;
+    const bool storing = c->nslots > 0 && thin == 1;
+    const bool use_graph = !graph_off && niter >= 4 && (thin == 1 || thin == 0 || c->nslots == 0);
+    int it_first = -pre_tau;
+    if (use_graph) {
+      if (!c->ctl) c->ctl = dalloc<long long>(8);
+      for (int it = it_first; it < 0; ++it) {          // the tau pre-draw: plain launches
+        L.pre = true; L.iter = iter0; L.slot = -1;
+        for (int h = 0; h < nsub; ++h) { bb::StbLargeLaunch H = sub(h); launched(bb::launch_stb_large_iter(H, (stages & BB_ST_BETA) != 0, sts[h])); }
+      }
+      L.pre = false; L.iter = 0; L.slot = storing ? 0 : -1;
+      const long long init[2] = {(long long)iter0, storing ? slot0 : 0};
+      for (int h = 0; h < nsub; ++h) {
+        bb::StbLargeLaunch H = sub(h);
+        H.ctl = c->ctl + 2 * h;
+        // everything a later call may change under the same chains object: priors / switches, stage mask, the draw buffer
+        struct Key { bb::Hyper h; int stages, storing, nsub, pad; long long stride; double *b, *l, *s2, *ta, *al, *Q; } key;
+        std::memset(&key, 0, sizeof(key));
+        key.h.sig2_shape = H.h.sig2_shape; key.h.sig2_scale = H.h.sig2_scale; key.h.nu_shape = H.h.nu_shape; key.h.nu_rate = H.h.nu_rate;
+        key.h.alpha_a = H.h.alpha_a; key.h.alpha_b = H.h.alpha_b; key.h.true_sig2 = H.h.true_sig2; key.h.true_tau = H.h.true_tau;
+        key.h.true_alpha = H.h.true_alpha; key.h.betaburn = H.h.betaburn;
+        key.stages = stages; key.storing = storing ? 1 : 0; key.nsub = nsub; key.pad = c->wide; key.stride = H.sink.chain_stride;
+        key.b = H.sink.beta; key.l = H.sink.lambda; key.s2 = H.sink.sig2; key.ta = H.sink.tau; key.al = H.sink.alpha; key.Q = H.Q;
+        const char* kb = reinterpret_cast<const char*>(&key);
+        if (!c->gx[h] || c->gkey[h].size() != sizeof(key) || std::memcmp(c->gkey[h].data(), kb, sizeof(key)) != 0) {
+          if (c->gx[h]) { cudaGraphExecDestroy(c->gx[h]); c->gx[h] = nullptr; }
+          cudaGraph_t graph = nullptr;
+          BB_CUDA_CHECK(cudaStreamBeginCapture(sts[h], cudaStreamCaptureModeThreadLocal));
+          int nl = bb::launch_stb_large_iter(H, (stages & BB_ST_BETA) != 0, sts[h]);
+          nl += bb::stb_large_advance(c->ctl + 2 * h, storing ? 1 : 0, sts[h]);
+          BB_CUDA_CHECK(cudaStreamEndCapture(sts[h], &graph));
+          const cudaError_t ie = cudaGraphInstantiate(&c->gx[h], graph, 0);
+          cudaGraphDestroy(graph);
+          BB_CUDA_CHECK(ie);
+          c->gkey[h].assign(kb, kb + sizeof(key));
+          c->glaunches[h] = nl;
+        }
+        BB_CUDA_CHECK(cudaMemcpyAsync(c->ctl + 2 * h, init, sizeof(init), cudaMemcpyHostToDevice, sts[h]));
+      }
+      for (int it = 0; it < niter; ++it)
+        for (int h = 0; h < nsub; ++h) { BB_CUDA_CHECK(cudaGraphLaunch(c->gx[h], sts[h])); launched(c->glaunches[h]); }
+      it_first = niter;
+    }
+    for (int it = it_first; it < niter; ++it) {
       L.pre = it < 0; L.iter = iter0 + (it < 0 ? 0 : it);
       const bool store = c->nslots > 0 && thin > 0 && it >= 0 && ((it + 1) % thin) == 0;
       L.slot = store ? slot0 + (it + 1) / thin - 1 : -1;
@@ -475,6 +544,7 @@ int bb_device_count(void) { int n = 0; if (cudaGetDeviceCount(&n) != cudaSuccess
 long long bb_launch_count(void) { return g_launches.load(); }
 void bb_set_seed(unsigned long long seed) { g_seed = seed; g_scalar_calls.store(0); }
 void bb_set_interrupt(int (*fn)(void)) { g_interrupt = fn; }
+void bb_set_wide_gaussian(int on) { g_wide_default = on ? 1 : 0; }
 unsigned int bb_scalar_status(void) { return g_scalar_status.load(); }
 int bb_model_status(const bb_model* m) { return m ? m->zeroed_by_gram_cut : -1; }
 void bb_set_device(int device) { g_device = device; }
@@ -705,6 +775,25 @@ int bb_chains_alpha(bb_chains* c, const double* set, double* get) {
   });
 }
 
+int bb_chains_option(bb_chains* c, int option, int value) {
+  return guarded([&] {
+    if (!c) throw std::string("bb_chains_option: null chains");
+    if (option != BB_OPT_WIDE_GAUSSIAN) throw std::string("bb_chains_option: unknown option");
+    if (value) {
+      if (c->method != BB_STB || c->ortho) throw std::string("bb_chains_option: BB_OPT_WIDE_GAUSSIAN applies to the stable sampler (ortho = 0)");
+      if (c->m->P <= 128) throw std::string("bb_chains_option: BB_OPT_WIDE_GAUSSIAN needs P > 128 (below that the P x P system is factored on chip)");
+      if (!c->m->X) throw std::string("bb_chains_option: BB_OPT_WIDE_GAUSSIAN needs the rows of X on the device (a model built from a Gram matrix has none)");
+      if (c->m->N > c->m->P) throw std::string("bb_chains_option: BB_OPT_WIDE_GAUSSIAN is for wide designs (N <= P); for N > P the P x P system is the smaller one");
+    }
+    if ((value != 0) != (c->wide != 0)) {     // the workspace has another shape: rebuilt on the next run
+      BB_CUDA_CHECK(cudaSetDevice(c->device));
+      BB_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+      dfree(c->A); dfree(c->W); dfree(c->U); dfree(c->R);
+      c->wide = value ? 1 : 0;
+    }
+  });
+}
+
 int bb_chains_reserve(bb_chains* c, long long nslots, int out_mask) {
   return guarded([&] {
     BB_CUDA_CHECK(cudaSetDevice(c->m->device));
@@ -848,6 +937,8 @@ double run_driver_on_model(const bb_model* m, int method, int ortho, const bb_hy
   };
   g.c = bb_chains_create(m, method, ortho, nchains, seed, chain0);
   if (!g.c) throw std::string(g_err);
+  if (g_wide_default && method == BB_STB && !ortho && m->P > 128 && m->X && m->N <= m->P && bb_chains_option(g.c, BB_OPT_WIDE_GAUSSIAN, 1))
+    throw std::string(g_err);
   // only the outputs the caller asked for are stored by the kernels (8 P bytes per chain-iteration each)
   struct Out { int which; double* host; const double* dev; int w; };
   Out outs[8] = {{BB_OUT_BETA, out.beta, nullptr, P},

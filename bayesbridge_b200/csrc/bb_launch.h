@@ -68,7 +68,17 @@ struct StbLargeLaunch {
   double* Q;               // [nchains][ceil(P/32)] partial sums of d'X'Xd, d = beta - bc (stbl_quad_kernel), or null
   DrawSink sink;
   long long slot;          // sink slot for this iteration, -1 = do not store
+  // Replayed as a CUDA graph the launch parameters are frozen, so what changes from one iteration to the next comes from
+  // device memory: ctl[0] is added to `iter`, ctl[1] to `slot` (when slot >= 0); stbl_advance_kernel moves both at the end
+  // of the iteration.  null: plain launches, iter / slot as given.
+  const long long* ctl;
+  // wide designs, opt-in (bb_stb_wide.cuh): the Gaussian draw through the N x N system; A is then [nchains][N][N],
+  // W [nchains][ceil(N/64)][64][64], U [nchains][P] (the draw u ~ N(0, D^-1)), R [nchains][N] (right-hand side)
+  int wide;
+  double* U;
+  double* R;
 };
+int stb_large_advance(long long* ctl, int stored, cudaStream_t st);   // ctl[0] += 1, ctl[1] += stored
 
 // the reference's stand-alone scalar samplers (BridgeWrapper.h:230-244), bb_scalar.cu
 enum ScalarKind { SC_TEXPON_LEFT = 0, SC_TEXPON_BOTH, SC_TEXPON, SC_TNORM_LEFT, SC_TNORM_BOTH, SC_TNORM, SC_RTGAMMA, SC_RETSTABLE };

@@ -186,6 +186,12 @@ __device__ __forceinline__ int retstable_round_at(const RetAlpha& A, const RetCo
   return retstable_round_libm(A, c, s, k, out);
 }
 
+// Trial cap of the double rejection: 2^18 Philox blocks = at least 52000 rounds.  A round is accepted with probability >= 0.15
+// for every (h, alpha) the algorithm is meant for, so the cap is only reached when the constants have degenerated (NaN / inf
+// from a collapsed chain); the draw then comes back NaN with ST_TRIAL_CAP after about 0.1 s instead of spinning through the
+// 2^24 blocks of the counter space for minutes (the reference loops for ever there, polling the interrupt, retstable.cpp:158-166).
+constexpr uint32_t RET_CAP = 1u << 18;
+
 // sequential form, one thread per item
 __device__ inline double retstable_scalar(const Stream& s, double h, double alpha, uint32_t& status, double V0 = 1.0) {
   if (alpha == 1.) return V0;  // point mass at V0 (retstable.cpp:104-110)
@@ -193,7 +199,7 @@ __device__ inline double retstable_scalar(const Stream& s, double h, double alph
   const double log_v0 = V0 == 1.0 ? 0.0 : log(V0);
   RetConst c; c.init(h, A, log_v0);
   uint32_t k = 0; double out = 0.;
-  while (k < K_CAP - 8) {
+  while (k < RET_CAP - 8) {
     const int r = retstable_round_at(A, c, s, k, out);
     if (r == 2) return V0 == 1.0 ? out : exp(log_v0 * A.inv_alpha) * out;   // V0^(1/alpha) X^-b (retstable.cpp:270)
     k += r == 0 ? 3u : 5u;
@@ -257,6 +263,11 @@ __device__ inline void lambda_stage_cta(const int tid, int P, const double* beta
     __syncthreads();
     return;
   }
+  if (!(tau > 0.0) || !(tau < 1e300)) {   // a chain that has already broken down (NaN / zero / infinite tau): no trials, flag it
+    for (int j = tid; j < P; j += NT) lam_out[j] = nan("");
+    status |= ST_NAN;
+    n_act = 0;                            // (no early return: other chains of the CTA still need this chain at the barriers)
+  }
   RetAlpha A; A.init(alpha_half);
   // the two offset tables as shared-memory bytes: the walk below is a chain of dependent look-ups (13 levels at G = 32), and
   // unpacking a 6-bit field of a 64-bit constant costs ~300 cycles per level against ~80 for a shared-memory load
@@ -312,7 +323,7 @@ __device__ inline void lambda_stage_cta(const int tid, int P, const double* beta
       const double val = __shfl_sync(0xffffffffu, out, res >= 0 ? res : 0, G);
       if (valid && sub == 0) {
         if (res >= 0) lam_out[j] = 2 * val;
-        else if (k0 + (uint32_t)pos >= K_CAP - 64) { lam_out[j] = nan(""); status |= ST_TRIAL_CAP; }
+        else if (k0 + (uint32_t)pos >= RET_CAP - 64) { lam_out[j] = nan(""); status |= ST_TRIAL_CAP; }
         else {
           kk_s[j] = k0 + (uint32_t)pos;
           q_s[(cur_q ^ 1) * qld + atomicAdd(&qn_s[cur_q ^ 1], 1)] = j;

@@ -2,6 +2,7 @@
 // scalar stage, build, blocked left-looking Cholesky (DMMA update / potrf / trsm per block column), solve.
 #include <cstdlib>
 #include "bb_stb_large.cuh"
+#include "bb_stb_wide.cuh"
 
 namespace bb {
 
@@ -16,6 +17,8 @@ void stb_large_prepare(int P) {
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_trsm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_update2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stbl_update2_smem()));
+  BB_CUDA_CHECK(cudaFuncSetAttribute(wide_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));   // N <= P there
+  if ((size_t)P * sizeof(double) > 48 * 1024) BB_CUDA_CHECK(cudaFuncSetAttribute(wide_draw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((size_t)P * sizeof(double))));
 }
 
 // block column kb > 0 brought up to date by the 64 x 64 kernel.  BB_STBL_TILE128=1: the row tiles below the diagonal tile in
@@ -48,6 +51,22 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
     if (do_alpha) { stbl_alpha_kernel<<<(nch + 7) / 8, 256, 0, st>>>(L); ++n; }
     return n;
   }
+  if (L.wide) {
+    // the same draw through the N x N system (bb_stb_wide.cuh): u and the right-hand side, M = X D^-1 X' + I on the tensor
+    // cores, its blocked Cholesky with the kernels below (dimension N), both substitutions and beta = sig (u + D^-1 X'w)
+    const int N = L.m.N, nbn = (N + SL_NB - 1) / SL_NB, ntile = nbn * (nbn + 1) / 2;
+    wide_draw_kernel<<<nch, 256, (size_t)P * sizeof(double), st>>>(L); ++n;
+    wide_gram_kernel<<<dim3(ntile, nch), 256, 0, st>>>(L); ++n;
+    for (int kb = 0; kb < nbn; ++kb) {
+      if (kb > 0) n += launch_update(L.A, N, kb, nbn, nch, st);
+      stbl_potrf_kernel<<<nch, SL_T, (size_t)2 * SL_NB * (SL_NB + 1) * sizeof(double), st>>>(L.A, L.W, N, kb, L.status); ++n;
+      const int rem = nbn - kb - 1;
+      if (rem > 0) { stbl_trsm_kernel<<<dim3(rem, nch), 256, smem_sy, st>>>(L.A, L.W, N, kb); ++n; }
+    }
+    wide_solve_kernel<<<nch, SV_T, ((size_t)N + SL_NB * (SL_NB + 1) + 16 * SL_NB) * sizeof(double), st>>>(L); ++n;
+    if (do_alpha) { stbl_alpha_kernel<<<(nch + 7) / 8, 256, 0, st>>>(L); ++n; }
+    return n;
+  }
   stbl_build_kernel<<<dim3(64, nch), 256, 0, st>>>(L); ++n;
   for (int kb = 0; kb < nblk; ++kb) {   // left-looking: bring block column kb up to date, factor its diagonal block, solve its panel
     if (kb > 0) n += launch_update(L.A, P, kb, nblk, nch, st);
@@ -58,6 +77,11 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
   stbl_solve_kernel<<<nch, SV_T, smem_sv, st>>>(L); ++n;
   if (do_alpha) { stbl_alpha_kernel<<<(nch + 7) / 8, 256, 0, st>>>(L); ++n; }
   return n;
+}
+
+int stb_large_advance(long long* ctl, int stored, cudaStream_t st) {
+  stbl_advance_kernel<<<1, 1, 0, st>>>(ctl, stored);
+  return 1;
 }
 
 // Cholesky of ONE P x P matrix with the same kernels (a batch of one chain): on return the lower triangle of A

@@ -88,6 +88,11 @@ __global__ void __launch_bounds__(256) stbl_quad_kernel(const StbLargeLaunch L, 
   }
 }
 
+// iteration index / sink slot of this launch (see StbLargeLaunch::ctl)
+__device__ __forceinline__ uint32_t stbl_iter(const StbLargeLaunch& L) { return L.iter + (L.ctl ? (uint32_t)L.ctl[0] : 0u); }
+__device__ __forceinline__ long long stbl_slot(const StbLargeLaunch& L) { return L.slot < 0 ? -1 : L.slot + (L.ctl ? L.ctl[1] : 0); }
+__global__ void stbl_advance_kernel(long long* ctl, int stored) { ctl[0] += 1; ctl[1] += stored; }
+
 // ---- tau, sig2, lambda: one CTA per chain -------------------------------------------------
 __global__ void __launch_bounds__(SL_T) stbl_scalar_kernel(const StbLargeLaunch L) {
   extern __shared__ double smem[];
@@ -99,7 +104,7 @@ __global__ void __launch_bounds__(SL_T) stbl_scalar_kernel(const StbLargeLaunch 
   int* qn_s = q_s + 2 * P;
   uint32_t* kk_s = reinterpret_cast<uint32_t*>(qn_s + 2);
   const int ch = blockIdx.x; if (ch >= L.nchains) return;
-  const uint32_t gch = L.chain0 + (uint32_t)ch, t = L.iter;
+  const uint32_t gch = L.chain0 + (uint32_t)ch, t = stbl_iter(L);
   const double alpha = L.h.true_alpha > 0 ? L.h.true_alpha : L.alpha[ch];   // unknown alpha: chain state (stbl_alpha_kernel moves it)
   const bool know_tau = L.h.true_tau > 0, know_sig2 = L.h.true_sig2 > 0;
   const bool do_tau = ((L.stages & 1) || L.pre) && !know_tau, do_sig2 = (L.stages & 2) && !know_sig2 && !L.pre;
@@ -428,33 +433,21 @@ __global__ void __launch_bounds__(256, 2) stbl_update2_kernel(double* Aall, int 
     }
 }
 
-// ---- beta = L^-T (L^-1 Xy + sig eps): one CTA per chain, blocked substitution ----
-constexpr int SV_T = 1024;   // threads of the solve kernel: one CTA streams a chain's 16 MB factor twice, it needs the loads in flight
-__global__ void __launch_bounds__(SV_T) stbl_solve_kernel(const StbLargeLaunch L) {
-  extern __shared__ double smem[];
-  const int P = L.m.P, tid = threadIdx.x, ch = blockIdx.x;
-  if (ch >= L.nchains) return;
-  double* x = smem;                 // [P]
-  double* D = x + P;                // [64][65] inverse W = L_kk^-1 of the current diagonal block (from stbl_potrf_kernel)
-  double* ps = D + SL_NB * (SL_NB + 1);   // [16][64] partial sums of the 64 x 64 matrix-vector products
-  const double* A = L.A + (size_t)ch * P * P;
-  const int nblk = (P + SL_NB - 1) / SL_NB;
-  const double* Wg = L.W + (size_t)ch * nblk * SL_NB * SL_NB;
-  const uint32_t gch = L.chain0 + (uint32_t)ch;
-  const int lane = tid & 31, warp = tid >> 5;
+// ---- the two blocked substitutions with a factor left by stbl_potrf / stbl_trsm (lower triangle of A, leading dimension P;
+//      Wg = inverses of its diagonal blocks): x <- L^-1 x and x <- L^-T x, x in shared memory, one CTA of SV_T threads ----
+constexpr int SV_T = 1024;   // threads of the solve kernels: one CTA streams a chain's factor twice, it needs the loads in flight
+__device__ __forceinline__ void stbl_stage_w(const double* Wg, int kb, double* D, int tid) {
+  const double* W = Wg + (size_t)kb * SL_NB * SL_NB;
+  for (int e = tid; e < SL_NB * SL_NB; e += SV_T) D[(e & (SL_NB - 1)) * (SL_NB + 1) + (e >> 6)] = W[e];   // W[e] = W(e % 64, e / 64)
+}
+// The diagonal blocks are applied as products with their inverses (rows / columns beyond the matrix are zero in W): a 64-term
+// dot product per unknown, all unknowns of the block at once, instead of 64 dependent substitution steps with a division each.
+__device__ __forceinline__ void stbl_forward(const double* __restrict__ A, const double* __restrict__ Wg, int P, double* x, double* D, double* ps, int tid) {
   const int vr = tid & (SL_NB - 1), vp = tid >> 6;     // matrix-vector product: index vr, 16 parts of 4 terms (SV_T = 1024)
-  const double sig = sqrt(L.sig2[ch]);
-  for (int j = tid; j < P; j += SV_T) x[j] = __ldg(L.m.Xy + j);
-  // The diagonal blocks are applied as products with their inverses (rows / columns beyond the matrix are zero in W): a 64-term
-  // dot product per unknown, all unknowns of the block at once, instead of 64 dependent substitution steps with a division each.
-  auto stage_w = [&](int kb) {
-    const double* W = Wg + (size_t)kb * SL_NB * SL_NB;
-    for (int e = tid; e < SL_NB * SL_NB; e += SV_T) D[(e & (SL_NB - 1)) * (SL_NB + 1) + (e >> 6)] = W[e];   // W[e] = W(e % 64, e / 64)
-  };
   // forward: L w = Xy, column-oriented
   for (int k0 = 0; k0 < P; k0 += SL_NB) {
     const int nb = min(SL_NB, P - k0);
-    stage_w(k0 / SL_NB);
+    stbl_stage_w(Wg, k0 / SL_NB, D, tid);
     __syncthreads();
     {   // w_blk = W x_blk
       double s = 0.0;
@@ -478,13 +471,15 @@ __global__ void __launch_bounds__(SV_T) stbl_solve_kernel(const StbLargeLaunch L
     }
     __syncthreads();
   }
-  for (int j = tid; j < P; j += SV_T) { Stream s(L.key, gch, L.iter, ST_BETA_STB, (uint32_t)j); x[j] = fma(sig, s.norm(0), x[j]); }
-  __syncthreads();
+}
+__device__ __forceinline__ void stbl_backward(const double* __restrict__ A, const double* __restrict__ Wg, int P, double* x, double* D, double* ps, int tid) {
+  const int vr = tid & (SL_NB - 1), vp = tid >> 6, lane = tid & 31, warp = tid >> 5;
+  const int nblk = (P + SL_NB - 1) / SL_NB;
   // backward: L' b = x over the stored lower triangle: column k of L is contiguous, one warp per column, lanes along r
   double* pk = ps + 15 * SL_NB;     // [64] column sums (the last part of ps is free until the product below)
   for (int kbk = nblk - 1; kbk >= 0; --kbk) {
     const int k0 = kbk * SL_NB, nb = min(SL_NB, P - k0);
-    stage_w(kbk);
+    stbl_stage_w(Wg, kbk, D, tid);
     for (int kk = warp; kk < nb; kk += SV_T / 32) {
       const double* col = A + (size_t)(k0 + kk) * P;
       double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
@@ -516,17 +511,38 @@ __global__ void __launch_bounds__(SV_T) stbl_solve_kernel(const StbLargeLaunch L
     }
     __syncthreads();
   }
+}
+
+// ---- beta = L^-T (L^-1 Xy + sig eps): one CTA per chain, blocked substitution ----
+__global__ void __launch_bounds__(SV_T) stbl_solve_kernel(const StbLargeLaunch L) {
+  extern __shared__ double smem[];
+  const int P = L.m.P, tid = threadIdx.x, ch = blockIdx.x;
+  if (ch >= L.nchains) return;
+  double* x = smem;                 // [P]
+  double* D = x + P;                // [64][65] inverse W = L_kk^-1 of the current diagonal block (from stbl_potrf_kernel)
+  double* ps = D + SL_NB * (SL_NB + 1);   // [16][64] partial sums of the 64 x 64 matrix-vector products
+  const double* A = L.A + (size_t)ch * P * P;
+  const int nblk = (P + SL_NB - 1) / SL_NB;
+  const double* Wg = L.W + (size_t)ch * nblk * SL_NB * SL_NB;
+  const uint32_t gch = L.chain0 + (uint32_t)ch, it_ = stbl_iter(L);
+  const double sig = sqrt(L.sig2[ch]);
+  for (int j = tid; j < P; j += SV_T) x[j] = __ldg(L.m.Xy + j);
+  stbl_forward(A, Wg, P, x, D, ps, tid);          // w = L^-1 Xy (the reference's first trsm, BridgeRegression.cpp:564)
+  for (int j = tid; j < P; j += SV_T) { Stream s(L.key, gch, it_, ST_BETA_STB, (uint32_t)j); x[j] = fma(sig, s.norm(0), x[j]); }
+  __syncthreads();
+  stbl_backward(A, Wg, P, x, D, ps, tid);         // beta = L^-T (w + sig eps)  (:565, :570-574)
   double* beta = L.beta + (size_t)ch * P;
+  const long long slot = stbl_slot(L);
   for (int j = tid; j < P; j += SV_T) {
     beta[j] = x[j];
-    if (L.slot >= 0) {
-      const size_t o = ((size_t)ch * L.sink.chain_stride + L.slot) * P + j;
+    if (slot >= 0) {
+      const size_t o = ((size_t)ch * L.sink.chain_stride + slot) * P + j;
       if (L.sink.beta) L.sink.beta[o] = x[j];
       if (L.sink.lambda) L.sink.lambda[o] = L.lambda[(size_t)ch * P + j];
     }
   }
-  if (tid == 0 && L.slot >= 0) {
-    const size_t o = (size_t)ch * L.sink.chain_stride + L.slot;
+  if (tid == 0 && slot >= 0) {
+    const size_t o = (size_t)ch * L.sink.chain_stride + slot;
     if (L.sink.sig2) L.sink.sig2[o] = L.sig2[ch];
     if (L.sink.tau) L.sink.tau[o] = L.tau[ch];
     if (L.sink.alpha) L.sink.alpha[o] = L.alpha[ch];
@@ -540,7 +556,7 @@ __global__ void __launch_bounds__(256) stbl_alpha_kernel(const StbLargeLaunch L)
   if (ch >= L.nchains) return;
   const double* beta = L.beta + (size_t)ch * P;
   const double tau = L.h.true_tau > 0 ? L.h.true_tau : L.tau[ch];
-  Stream sa(L.key, L.chain0 + (uint32_t)ch, L.iter, ST_ALPHA, 0);
+  Stream sa(L.key, L.chain0 + (uint32_t)ch, stbl_iter(L), ST_ALPHA, 0);
   const AlphaProposal pr = alpha_propose(sa, L.alpha[ch]);
   double sn = 0.0, so = 0.0;
   for (int j = lane; j < P; j += 32) alpha_terms(beta[j], tau, pr, sn, so);
@@ -548,7 +564,8 @@ __global__ void __launch_bounds__(256) stbl_alpha_kernel(const StbLargeLaunch L)
   if (lane == 0) {
     const double a = alpha_decide(sa, pr, sn, so, P, L.h.alpha_a, L.h.alpha_b);
     L.alpha[ch] = a;
-    if (L.slot >= 0 && L.sink.alpha) L.sink.alpha[(size_t)ch * L.sink.chain_stride + L.slot] = a;
+    const long long slot = stbl_slot(L);
+    if (slot >= 0 && L.sink.alpha) L.sink.alpha[(size_t)ch * L.sink.chain_stride + slot] = a;
   }
 }
 

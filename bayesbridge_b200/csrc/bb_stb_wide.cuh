@@ -1,0 +1,161 @@
+// bb_stb_wide.cuh -- the Gaussian draw of the stable sampler for WIDE designs (P > N), opt-in.
+//
+// The reference draws  beta | lambda, sig2, tau ~ N(VInv^-1 X'y, sig2 VInv^-1),  VInv = X'X + D,  D = diag(lambda sig2/tau^2),
+// through a P x P Cholesky (/root/reference/Code/C/BridgeRegression.cpp:552-575): P^3/3 flops per chain and iteration, which
+// the authors themselves flag for P > N (Code/R/Benchmark.R:734-742).  The same law through an N x N system
+// (Bhattacharya, Chakraborty & Mallick 2016, Biometrika 103(4)): with theta = beta / sig,
+//     u ~ N(0, D^-1),  delta ~ N(0, I_N),  v = X u + delta,
+//     M = X D^-1 X' + I_N,   w = M^-1 (y / sig - v),   theta = u + D^-1 X' w
+// has theta ~ N(VInv^-1 X'y / sig, VInv^-1).  Cost N^2 P (the product, on the FP64 tensor cores) + N^3/3 instead of P^3/3:
+// config c4 (N = 500, P = 2000) 5.4e8 against 2.7e9 flops, and a 2 MB instead of a 32 MB workspace per chain.
+// Not the reference's arithmetic: the draws differ from sample_beta_stable's for the same normals (the LAW is the same), so
+// the path is opt-in (bb_chains_option(BB_OPT_WIDE_GAUSSIAN)) and is checked distributionally and against a host
+// restatement of these formulas (tests/test_gpu_wide.py), never draw for draw against the reference.
+//
+// Normals: item j < P of stage ST_BETA_STB is the one behind u_j, item P + n the one behind delta_n.
+#pragma once
+#include "bb_stb_large.cuh"
+
+namespace bb {
+
+constexpr int GR_T = 64;    // tile edge of the product kernel (the tiling of gram_kernel, bb_pre.cuh)
+constexpr int GR_K = 32;    // k chunk
+constexpr int GR_LD = 36;   // smem leading dimension (doubles)
+
+// ---- u = D^-1/2 eps, r = y / sig - X u - delta : one CTA per chain ----
+__global__ void __launch_bounds__(256) wide_draw_kernel(const StbLargeLaunch L) {
+  extern __shared__ double smem[];          // [P] u
+  const int P = L.m.P, N = L.m.N, tid = threadIdx.x, ch = blockIdx.x;
+  if (ch >= L.nchains) return;
+  const uint32_t gch = L.chain0 + (uint32_t)ch, it_ = stbl_iter(L);
+  const double sig2 = L.sig2[ch], tau = L.tau[ch];
+  const double f = tau * tau / sig2;        // D_j^-1 = f / lambda_j
+  const double isig = 1.0 / sqrt(sig2);
+  const double* lam = L.lambda + (size_t)ch * P;
+  double* U = L.U + (size_t)ch * P;
+  for (int j = tid; j < P; j += 256) {
+    Stream s(L.key, gch, it_, ST_BETA_STB, (uint32_t)j);
+    const double u = s.norm(0) * sqrt(f / lam[j]);
+    smem[j] = u; U[j] = u;
+  }
+  __syncthreads();
+  double* R = L.R + (size_t)ch * N;
+  for (int n = tid; n < N; n += 256) {      // rows of X are contiguous along n: coalesced
+    const double* x = L.m.X + n;
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    int k = 0;
+    for (; k + 3 < P; k += 4) {
+      s0 = fma(__ldg(x + (size_t)k * N), smem[k], s0); s1 = fma(__ldg(x + (size_t)(k + 1) * N), smem[k + 1], s1);
+      s2 = fma(__ldg(x + (size_t)(k + 2) * N), smem[k + 2], s2); s3 = fma(__ldg(x + (size_t)(k + 3) * N), smem[k + 3], s3);
+    }
+    for (; k < P; ++k) s0 = fma(__ldg(x + (size_t)k * N), smem[k], s0);
+    Stream s(L.key, gch, it_, ST_BETA_STB, (uint32_t)(P + n));
+    R[n] = __ldg(L.m.y + n) * isig - ((s0 + s1) + (s2 + s3)) - s.norm(0);
+  }
+}
+
+// ---- M_c = X D_c^-1 X' + I  (N x N, lower 64 x 64 tiles, diagonal tiles in full) on the FP64 tensor cores ----
+// CTA = one tile (bi >= bj) of one chain, 8 warps; warp w owns rows 8w..8w+7 of the tile and all 8 n-tiles (the mapping of
+// gram_kernel, bb_pre.cuh).  The contraction runs over the P columns of X: a chunk of 32 columns of the 64 rows of both
+// operands is staged in shared memory, the left one scaled by D^-1.
+__global__ void __launch_bounds__(256) wide_gram_kernel(const StbLargeLaunch L) {
+  __shared__ double As[GR_T * GR_LD];
+  __shared__ double Bs[GR_T * GR_LD];
+  __shared__ double dv[GR_K];
+  const int P = L.m.P, N = L.m.N, ch = blockIdx.y;
+  int tIdx = blockIdx.x, bi = 0;
+  while ((bi + 1) * (bi + 2) / 2 <= tIdx) ++bi;
+  const int bj = tIdx - bi * (bi + 1) / 2;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const double f = L.tau[ch] * L.tau[ch] / L.sig2[ch];
+  const double* lam = L.lambda + (size_t)ch * P;
+  const double* X = L.m.X;
+  double acc[8][2];
+#pragma unroll
+  for (int t = 0; t < 8; ++t) { acc[t][0] = 0.0; acc[t][1] = 0.0; }
+  for (int k0 = 0; k0 < P; k0 += GR_K) {
+    if (tid < GR_K) dv[tid] = (k0 + tid < P) ? f / lam[k0 + tid] : 0.0;
+    __syncthreads();
+    for (int e = tid; e < GR_T * GR_K; e += 256) {       // lanes run along the rows: X is column-major
+      const int r = e & (GR_T - 1), kk = e >> 6;
+      const int k = k0 + kk, ra = bi * GR_T + r, rb = bj * GR_T + r;
+      double va = 0.0, vb = 0.0;
+      if (k < P) {
+        if (ra < N) va = X[(size_t)k * N + ra] * dv[kk];
+        if (rb < N) vb = X[(size_t)k * N + rb];
+      }
+      As[r * GR_LD + kk] = va;
+      Bs[r * GR_LD + kk] = vb;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < GR_K; kk += 4) {
+      const double a = As[(warp * 8 + (lane >> 2)) * GR_LD + kk + (lane & 3)];
+#pragma unroll
+      for (int t = 0; t < 8; ++t) {
+        const double b = Bs[(t * 8 + (lane >> 2)) * GR_LD + kk + (lane & 3)];
+        dmma_m8n8k4(acc[t][0], acc[t][1], a, b);
+      }
+    }
+    __syncthreads();
+  }
+  // C fragment: row = lane/4, cols = 2*(lane%4) + {0,1};  M is stored column-major with leading dimension N
+  double* M = L.A + (size_t)ch * N * N;
+#pragma unroll
+  for (int t = 0; t < 8; ++t) {
+    const int r = bi * GR_T + warp * 8 + (lane >> 2);
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const int c = bj * GR_T + t * 8 + 2 * (lane & 3) + q;
+      if (r < N && c < N) M[r + (size_t)c * N] = acc[t][q] + (r == c ? 1.0 : 0.0);
+    }
+  }
+}
+
+// ---- w = M^-1 r (both substitutions with the factor of M), beta = sig (u + D^-1 X' w) : one CTA per chain ----
+__global__ void __launch_bounds__(SV_T) wide_solve_kernel(const StbLargeLaunch L) {
+  extern __shared__ double smem[];
+  const int P = L.m.P, N = L.m.N, tid = threadIdx.x, ch = blockIdx.x;
+  if (ch >= L.nchains) return;
+  double* x = smem;                        // [N]
+  double* D = x + N;                       // [64][65]
+  double* ps = D + SL_NB * (SL_NB + 1);    // [16][64]
+  const double* A = L.A + (size_t)ch * N * N;
+  const int nblk = (N + SL_NB - 1) / SL_NB;
+  const double* Wg = L.W + (size_t)ch * nblk * SL_NB * SL_NB;
+  const int lane = tid & 31, warp = tid >> 5;
+  const double* R = L.R + (size_t)ch * N;
+  for (int n = tid; n < N; n += SV_T) x[n] = R[n];
+  stbl_forward(A, Wg, N, x, D, ps, tid);
+  stbl_backward(A, Wg, N, x, D, ps, tid);
+  __syncthreads();
+  const double sig2 = L.sig2[ch], tau = L.tau[ch];
+  const double f = tau * tau / sig2, sig = sqrt(sig2);
+  const double* lam = L.lambda + (size_t)ch * P;
+  const double* U = L.U + (size_t)ch * P;
+  double* beta = L.beta + (size_t)ch * P;
+  const long long slot = stbl_slot(L);
+  for (int k = warp; k < P; k += SV_T / 32) {        // (X' w)_k: column k of X is contiguous, lanes along the rows
+    const double* col = L.m.X + (size_t)k * N;
+    double s = 0.0;
+    for (int n = lane; n < N; n += 32) s = fma(__ldg(col + n), x[n], s);
+    s = warp_sum(s);
+    if (lane == 0) {
+      const double b = sig * fma(f / lam[k], s, U[k]);
+      beta[k] = b;
+      if (slot >= 0) {
+        const size_t o = ((size_t)ch * L.sink.chain_stride + slot) * P + k;
+        if (L.sink.beta) L.sink.beta[o] = b;
+        if (L.sink.lambda) L.sink.lambda[o] = lam[k];
+      }
+    }
+  }
+  if (tid == 0 && slot >= 0) {
+    const size_t o = (size_t)ch * L.sink.chain_stride + slot;
+    if (L.sink.sig2) L.sink.sig2[o] = L.sig2[ch];
+    if (L.sink.tau) L.sink.tau[o] = L.tau[ch];
+    if (L.sink.alpha) L.sink.alpha[o] = L.alpha[ch];
+  }
+}
+
+}  // namespace bb

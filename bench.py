@@ -51,6 +51,8 @@ WORKLOADS = {
                chains=512, iters=100, scaling="weak"),
     "c4": dict(desc="bridge.reg.stb n=500 p=2000 alpha=0.25 (p>n), 1024 chains in total split over the GPUs", data="c4",
                method="stable", chains_total=1024, iters=2, scaling="strong", burn=6),
+    "c4w": dict(desc="c4 with the opt-in N x N Gaussian draw (same law, not the reference's arithmetic; SURVEY row f4), 1024 chains in total",
+                data="c4", method="stable", chains_total=1024, iters=4, scaling="strong", burn=8, wide=True),
     "c5": dict(desc="bridge.reg.tri n=100000 p=256, row-sharded Gram + all-reduce, 256 chains/GPU", data="c5", method="triangle",
                chains=256, iters=100, scaling="weak", sharded=True),
     "c5s": dict(desc="bridge.reg.stb n=100000 p=256, row-sharded Gram + all-reduce, 256 chains/GPU", data="c5", method="stable",
@@ -296,8 +298,9 @@ def kernel_name(method, P):
     return "stb_small_kernel" if P <= 128 else "stbl_update_kernel (+ potrf / trsm / solve / scalar)"
 
 
-def roofline_of(name, method, P, nch, ips, steps, T_local, peaks):
-    flops_step = flops_per_chain_iter(method, P) * nch * ips
+def roofline_of(name, method, P, nch, ips, steps, T_local, peaks, N=None):
+    per_chain = flops_per_chain_iter(method, P) if N is None else (float(N) * N * P + N ** 3 / 3.0 + 4.0 * N * P + 2.0 * N * N)
+    flops_step = per_chain * nch * ips
     achieved = flops_step * steps / T_local / 1e12
     traffic, ncu_info = None, None
     tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
@@ -306,7 +309,7 @@ def roofline_of(name, method, P, nch, ips, steps, T_local, peaks):
         traffic = (ncu_info or {}).get("bytes_per_launch")
     hbm, hbm_src = measured_hbm()
     out = {"kernel": kernel_name(method, P), "achieved": achieved, "unit": "TFLOP/s", "traffic": traffic,
-           "algorithmic_flops_per_chain_iter": flops_per_chain_iter(method, P),
+           "algorithmic_flops_per_chain_iter": per_chain,
            "hbm_store_GBs": 8.0 * P * nch * ips * steps / T_local / 1e9, "hbm_peak_GBs": hbm, "hbm_peak_source": hbm_src, "ncu": ncu_info}
     if method == "triangle":
         out.update(bound="fp64-vector", peak=peaks["dfma_tflops"], frac=achieved / peaks["dfma_tflops"],
@@ -326,11 +329,13 @@ def roofline_of(name, method, P, nch, ips, steps, T_local, peaks):
 
 
 def measure_sweep(torch, bb, bdist, L, dev, name, method, alpha, model, P, nch, chain0, ips, steps, warmup, burn, peaks,
-                  want_ess=True, sample_clocks=False, world=1):
+                  want_ess=True, sample_clocks=False, world=1, wide=False):
     """device-timed sweep of `nch` chains of this rank: W warm-up + K timed steps of `ips` iterations, L2 flushed between steps."""
     from bayesbridge_b200._lib import ST_ALL
     hyp = bb.make_hyper(alpha=alpha)
     chains = model.chains(method, nch, seed=20121027, chain0=chain0)
+    if wide:
+        chains.wide_gaussian()
     chains.reserve(steps * ips, ("beta",))
     chains.run(hyp, burn, 0, ST_ALL, pre_tau=1)        # burn-in, untimed: the timed iterations run in the stationary regime
     it0 = burn
@@ -359,7 +364,7 @@ def measure_sweep(torch, bb, bdist, L, dev, name, method, alpha, model, P, nch, 
     res = {"value": chains_total * P * ips * steps / T, "unit": UNIT, "ms_per_step": 1e3 * T / steps, "chains_total": chains_total,
            "chains_this_rank": nch, "iters_per_step": ips, "burn_in_untimed": burn, "gpu_launches": int(launches),
            "chain_status_nonzero": int((chains.get()["status"] != 0).sum()),
-           "roofline": roofline_of(name, method, P, nch, ips, steps, T_local, peaks)}
+           "roofline": roofline_of(name, method, P, nch, ips, steps, T_local, peaks, N=model.N if wide else None)}
     if clk:
         res["clocks"] = clk
     if want_ess:
@@ -406,7 +411,7 @@ def e2e_capi(torch, bb, L, dev, method, Xp, yp, N, P, alpha, nch, chain0, ips, s
                                   "posterior_mean_beta0": float(beta[:, 1:, 0].mean()), "comm_ms": 0.0}
 
 
-def e2e_dist(torch, bb, bdist, dev, method, host_pack, N, P, alpha, nch, chain0, ips, steps, sharded, rank):
+def e2e_dist(torch, bb, bdist, dev, method, host_pack, N, P, alpha, nch, chain0, ips, steps, sharded, rank, wide=False):
     """The same call at N > 1 through bayesbridge_b200.dist: host -> device on the source rank(s), ONE collective, then
     constructor + sweep + download on every rank.  host_pack: pinned packed [X | y] (rank 0) or this rank's row shard."""
     from bayesbridge_b200._lib import ST_ALL
@@ -428,6 +433,8 @@ def e2e_dist(torch, bb, bdist, dev, method, host_pack, N, P, alpha, nch, chain0,
             model = bdist.replicated_model(host_pack, None, N, P, dev.index, timing=tm)
             h2d = 8 * host_pack.numel() if rank == 0 else 0
         ch = model.chains(method, nch, seed=20121027 + s, chain0=chain0)
+        if wide:
+            ch.wide_gaussian()
         ch.reserve(nsamp, ("beta", "sig2", "tau"))
         nburn = 0 if method == "triangle" else 1      # run_driver's schedule at burn = 0 (BridgeWrapper.cpp:142-145, 262-266)
         ch.run(hyp, nburn, 0, ST_ALL, pre_tau=1)
@@ -476,7 +483,7 @@ def run_workload(ctx, name, alpha=None, model=None, steps=None, warmup=None, mai
     precompute_s = time.perf_counter() - t0
     burn = args.burn if (main and args.burn is not None) else wl.get("burn", max(ips, 50 if P >= 1000 else 200))
     res = measure_sweep(torch, bb, bdist, L, dev, name, method, alpha, model, P, nch, chain0, ips, steps, warmup, burn, peaks,
-                        want_ess=args.ess, sample_clocks=main, world=world)
+                        want_ess=args.ess, sample_clocks=main, world=world, wide=bool(wl.get("wide")))
     res["scaling"] = wl["scaling"]
     res["config"] = dict(cfg, chains_per_gpu=nch if "chains_total" not in wl else None, chains_total=res["chains_total"],
                          iters_per_step=ips, multi_gpu=("row-sharded Gram + all-reduce" if sharded else
@@ -487,6 +494,7 @@ def run_workload(ctx, name, alpha=None, model=None, steps=None, warmup=None, mai
 
     # ---- end to end with host buffers ----
     e2e_steps = max(1, min(steps, args.e2e_steps))
+    L.bb_set_wide_gaussian(1 if wl.get("wide") else 0)
     if world == 1:
         Xp = torch.from_numpy(np.asfortranarray(X).ravel(order="F").copy()).pin_memory()
         yp = torch.from_numpy(np.ascontiguousarray(y).copy()).pin_memory()
@@ -497,7 +505,8 @@ def run_workload(ctx, name, alpha=None, model=None, steps=None, warmup=None, mai
             pack = torch.from_numpy(np.concatenate([np.asfortranarray(X[lo:hi]).ravel(order="F"), y[lo:hi]])).pin_memory()
         else:
             pack = torch.from_numpy(np.concatenate([np.asfortranarray(X).ravel(order="F"), y])).pin_memory() if rank == 0 else None
-        T_e, info = e2e_dist(torch, bb, bdist, dev, method, pack, N, P, alpha, nch, chain0, ips, e2e_steps, sharded, rank)
+        T_e, info = e2e_dist(torch, bb, bdist, dev, method, pack, N, P, alpha, nch, chain0, ips, e2e_steps, sharded, rank, wide=bool(wl.get("wide")))
+    L.bb_set_wide_gaussian(0)
     T_e = bdist.max_over_ranks(T_e, dev)
     info["comm_ms"] = bdist.max_over_ranks(info["comm_ms"], dev)
     res["e2e"] = dict(value=res["chains_total"] * P * ips * e2e_steps / T_e, unit=UNIT, steps=e2e_steps, **info)
@@ -577,7 +586,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--sub", default=None, help="comma list of the other configurations carried under `workloads` "
-                                                "(default: c1,c2,c4,c5 when --workload is the default, none otherwise)")
+                                                "(default: c1,c2,c4,c4w,c5 when --workload is the default, none otherwise)")
     ap.add_argument("--no-sub", action="store_true")
     ap.add_argument("--sub-steps", type=int, default=3)
     ap.add_argument("--chains", type=int, default=0, help="chains per GPU of the headline workload (default: the workload's)")
@@ -591,7 +600,7 @@ def main():
     ap.add_argument("--no-ess", dest="ess", action="store_false")
     args = ap.parse_args()
     if args.sub is None:
-        args.sub = "c1,c2,c4,c5" if ("--workload" not in " ".join(sys.argv)) else ""
+        args.sub = "c1,c2,c4,c4w,c5" if ("--workload" not in " ".join(sys.argv)) else ""
     if args.no_sub:
         args.sub = ""
     if args.impl == "reference":

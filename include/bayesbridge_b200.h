@@ -181,6 +181,17 @@ int bb_chains_get(const bb_chains *c, double *beta, double *u, double *aux, doub
  * values are copied to `get` (may be NULL).  Chains start at 0.5 (BridgeWrapper.cpp:125,246,363,474); the
  * state only moves when alpha is unknown (true_alpha <= 0, BridgeWrapper.cpp:109,152,185). */
 int bb_chains_alpha(bb_chains *c, const double *set, double *get);
+/* Options of a set of chains.  BB_OPT_WIDE_GAUSSIAN (stable sampler, ortho = 0, P > 128, rows of X on the device): draw
+ * beta | lambda, sig2, tau through the N x N system  M = X D^-1 X' + I  (Bhattacharya, Chakraborty & Mallick 2016) instead of
+ * the P x P Cholesky of X'X + D (Code/C/BridgeRegression.cpp:552-575) -- the P > N remedy the reference's authors point at
+ * (Code/R/Benchmark.R:734-742).  Same LAW, different arithmetic: for the same Philox stream the draws
+ * differ from the reference's, so it is off by default and the per-draw parity tests do not apply to it.  N^2 P + N^3/3 flops
+ * and N^2 doubles of workspace per chain instead of P^3/3 and P^2.  Returns non-zero (bb_last_error) when it does not apply. */
+enum { BB_OPT_WIDE_GAUSSIAN = 1 };
+int bb_chains_option(bb_chains *c, int option, int value);
+/* Default for the drivers (bridge_reg_stable, bb_bridge_batched*): 1 = opt their chains into BB_OPT_WIDE_GAUSSIAN wherever it
+ * applies (stable sampler, ortho = 0, P > 128, N <= P).  0 (the default) keeps the reference's P x P arithmetic. */
+void bb_set_wide_gaussian(int on);
 /* reserve a device buffer for `nslots` stored iterations per chain of the outputs in out_mask */
 int bb_chains_reserve(bb_chains *c, long long nslots, int out_mask);
 /* Advance every chain by niter iterations; iteration index of the first = iter0 (RNG counter).

@@ -425,3 +425,11 @@ def flat_at(seed, chain, it, stage, item, a, b):
     L.bbo_flat_at.restype = C.c_double
     L.bbo_flat_at.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32] + [C.c_double] * 2
     return L.bbo_flat_at(seed, chain, it, stage, item, a, b)
+
+
+def norm_at(seed, chain, it, stage, item):
+    """the standard normal of Philox block 0 at (chain, iteration, stage, item): what Stream::norm(0) returns on the device"""
+    L = Port().L
+    L.bbo_norm_at.restype = C.c_double
+    L.bbo_norm_at.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
+    return L.bbo_norm_at(seed, chain, it, stage, item)

@@ -48,6 +48,7 @@ enum {
 };
 
 #define BBO_K_CAP (1u << 24) /* trial cap: k must stay below 2^24 */
+#define BBO_RET_CAP (1u << 18) /* trial cap of the tilted-stable double rejection (same as the device's RET_CAP) */
 #define BBO_RTG_CAP (1u << 16) /* trial cap of the right-truncated gamma's naive rejection */
 
 typedef struct {

@@ -391,7 +391,7 @@ double bbo_retstable_LD(double h, double alpha, double V0, bbo_rng *r) {
       if (U >= 0 && U <= M_PI && gamma < 1) d += xi;
       rho *= d;
       Z = W * rho;
-      if (r->k >= BBO_K_CAP - 8) return NAN;
+      if (r->k >= BBO_RET_CAP - 8) return NAN;
     } while (!(U < M_PI && Z <= 1.));
     double a = pow(A_(U, alpha), 1. / (1. - alpha));
     double m = pow(b / a, alpha) * lambda_alpha;
@@ -637,6 +637,10 @@ double bbo_tnorm_at(uint64_t seed, uint32_t chain, uint32_t iter, uint32_t stage
                     double left, double right, double mu, double sd) {
   bbo_rng r; bbo_rng_key(&r, seed, chain); bbo_rng_at(&r, iter, stage, item);
   return bbo_tnorm(&r, left, right, mu, sd);
+}
+double bbo_norm_at(uint64_t seed, uint32_t chain, uint32_t iter, uint32_t stage, uint32_t item) {
+  bbo_rng r; bbo_rng_key(&r, seed, chain); bbo_rng_at(&r, iter, stage, item);
+  return bbo_norm(&r);
 }
 double bbo_flat_at(uint64_t seed, uint32_t chain, uint32_t iter, uint32_t stage, uint32_t item, double a, double b) {
   bbo_rng r; bbo_rng_key(&r, seed, chain); bbo_rng_at(&r, iter, stage, item);
