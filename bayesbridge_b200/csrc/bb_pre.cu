@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <cstdint>
 #include <cstring>
 #include <vector>
 #include <mutex>
@@ -31,7 +32,17 @@ int gram_device(const double* X, const double* y, int N, int P, double* G, cudaS
   nsplit = (N + rows - 1) / rows;
   if (nsplit < 1) nsplit = 1;
   double* part = dalloc<double>((size_t)nsplit * ntile * GR_T * GR_T);
-  gram_kernel<<<dim3(ntile, 1, nsplit), 256, 0, st>>>(X, y, N, P, rows, part);
+  // TMA-staged operands whenever the bulk copies' alignment rules hold (N even, 16-byte aligned bases); BB_GRAM_LDG=1 forces
+  // the LDG -> STS kernel (same arithmetic, same summation order: the two kernels produce identical bits)
+  static const bool force_ldg = std::getenv("BB_GRAM_LDG") != nullptr;
+  const bool tma_ok = !force_ldg && (N % 2 == 0) && ((uintptr_t)X % 16 == 0) && ((uintptr_t)y % 16 == 0);
+  if (tma_ok) {
+    static bool attr_set = false;
+    if (!attr_set) { BB_CUDA_CHECK(cudaFuncSetAttribute(gram_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gram_tma_smem())); attr_set = true; }
+    gram_tma_kernel<<<dim3(ntile, 1, nsplit), 288, gram_tma_smem(), st>>>(X, y, N, P, rows, part);
+  } else {
+    gram_kernel<<<dim3(ntile, 1, nsplit), 256, 0, st>>>(X, y, N, P, rows, part);
+  }
   check_launch();
   gram_reduce_kernel<<<296, 256, 0, st>>>(part, P, nsplit, G);
   check_launch();

@@ -75,6 +75,130 @@ __global__ void __launch_bounds__(256) gram_kernel(const double* __restrict__ X,
   }
 }
 
+// The same tile product with TMA-staged operands (north_star item 1).  A ninth warp is the producer: per 32-row chunk every
+// one of its lanes issues the bulk copies (cp.async.bulk, 256 bytes = 32 rows of one column) of the columns it owns into a
+// ring of GT_S stages, all signalling one mbarrier per stage (complete_tx); the eight consumer warps wait for the stage, run the
+// 64 DMMAs of the chunk straight from shared memory (rows padded to GR_LD doubles: the bulk copies place each column at its
+// padded offset, so the fragment loads stay conflict-free without a swizzle) and hand the stage back through a second
+// mbarrier.  The copy of chunk i + GT_S - 1 is in flight while chunk i is multiplied; the LDG -> STS staging and its two
+// CTA-wide barriers per chunk are gone.  A diagonal tile (bi == bj) loads its operand once.
+// Needs N even and 16-byte aligned X, y (a bulk copy moves multiples of 16 bytes from 16-byte aligned addresses); the host
+// falls back to gram_kernel otherwise.  The rows of a split that do not fill a chunk are added by the consumers with plain loads.
+constexpr int GT_S = 3;                                  // ring depth
+constexpr int GT_STAGE = 2 * GR_T * GR_LD;               // doubles per stage: A block then B block
+__host__ __device__ inline size_t gram_tma_smem() { return (size_t)GT_S * GT_STAGE * sizeof(double) + 2 * GT_S * sizeof(uint64_t); }
+
+__global__ void __launch_bounds__(288) gram_tma_kernel(const double* __restrict__ X, const double* __restrict__ y,
+                                                       int N, int P, int rows_per_split, double* __restrict__ part) {
+  extern __shared__ __align__(16) unsigned char gt_raw[];
+  double* ring = reinterpret_cast<double*>(gt_raw);
+  uint64_t* full = reinterpret_cast<uint64_t*>(ring + (size_t)GT_S * GT_STAGE);
+  uint64_t* empty = full + GT_S;
+  const int PA = P + 1;
+  const int nt = (PA + GR_T - 1) / GR_T;
+  int tIdx = blockIdx.x, bi = 0;
+  while ((bi + 1) * (bi + 2) / 2 <= tIdx) ++bi;
+  const int bj = tIdx - bi * (bi + 1) / 2;
+  const bool diag = bi == bj;
+  const int k_begin = blockIdx.z * rows_per_split;
+  const int k_end = min(N, k_begin + rows_per_split);
+  const int nfull = (k_end - k_begin) / GR_K;            // chunks staged by TMA
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  // columns beyond the augmented matrix are never copied: their rows of every stage stay zero
+  for (int e = tid; e < GT_S * GT_STAGE; e += 288) ring[e] = 0.0;
+  if (tid == 0) {
+    for (int s = 0; s < GT_S; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 8); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the zero fill (generic proxy) before the bulk copies (async proxy)
+  double acc[8][2];
+#pragma unroll
+  for (int t = 0; t < 8; ++t) { acc[t][0] = 0.0; acc[t][1] = 0.0; }
+
+  if (warp == 8) {
+    // ---------------- producer ----------------
+    int ncols = 0;                                       // valid columns of both operands -> bytes per stage
+    for (int c = 0; c < GR_T; ++c) { if (bi * GR_T + c < PA) ++ncols; if (!diag && bj * GR_T + c < PA) ++ncols; }
+    const uint32_t bytes = (uint32_t)ncols * GR_K * sizeof(double);
+    for (int i = 0; i < nfull; ++i) {
+      const int s = i % GT_S;
+      if (i >= GT_S) mbar_wait(&empty[s], ((i / GT_S) - 1) & 1);
+      if (lane == 0) mbar_arrive_expect_tx(&full[s], bytes);
+      __syncwarp();
+      const int k = k_begin + i * GR_K;
+      double* stage = ring + (size_t)s * GT_STAGE;
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const int c = lane + 32 * q;
+        const int ca = bi * GR_T + c, cb = bj * GR_T + c;
+        if (ca < PA) tma_load_1d(stage + c * GR_LD, (ca < P ? X + (size_t)ca * N : y) + k, GR_K * sizeof(double), &full[s]);
+        if (!diag && cb < PA) tma_load_1d(stage + GR_T * GR_LD + c * GR_LD, (cb < P ? X + (size_t)cb * N : y) + k, GR_K * sizeof(double), &full[s]);
+      }
+    }
+  } else {
+    // ---------------- consumers ----------------
+    for (int i = 0; i < nfull; ++i) {
+      const int s = i % GT_S;
+      mbar_wait(&full[s], (i / GT_S) & 1);
+      const double* As = ring + (size_t)s * GT_STAGE;
+      const double* Bs = diag ? As : As + GR_T * GR_LD;
+#pragma unroll
+      for (int kk = 0; kk < GR_K; kk += 4) {
+        const double a = As[(warp * 8 + (lane >> 2)) * GR_LD + kk + (lane & 3)];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+          const double b = Bs[(t * 8 + (lane >> 2)) * GR_LD + kk + (lane & 3)];
+          dmma_m8n8k4(acc[t][0], acc[t][1], a, b);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[s]);
+    }
+  }
+  // ---------------- rows that do not fill a chunk (last split only): plain loads into stage 0 ----------------
+  const int k_tail = k_begin + nfull * GR_K;
+  if (k_tail < k_end) {
+    __syncthreads();                                     // every consumer is through with the ring
+    double* As = ring;
+    double* Bs = ring + GR_T * GR_LD;
+    if (tid < 256)
+      for (int e = tid; e < GR_T * GR_K; e += 256) {
+        const int col = e / GR_K, kk = e - col * GR_K;
+        const int k = k_tail + kk;
+        const int ca = bi * GR_T + col, cb = bj * GR_T + col;
+        double va = 0.0, vb = 0.0;
+        if (k < k_end) {
+          if (ca < P) va = X[(size_t)ca * N + k]; else if (ca == P) va = y[k];
+          if (cb < P) vb = X[(size_t)cb * N + k]; else if (cb == P) vb = y[k];
+        }
+        As[col * GR_LD + kk] = va;
+        Bs[col * GR_LD + kk] = vb;
+      }
+    __syncthreads();
+    if (warp < 8) {
+#pragma unroll
+      for (int kk = 0; kk < GR_K; kk += 4) {
+        const double a = As[(warp * 8 + (lane >> 2)) * GR_LD + kk + (lane & 3)];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+          const double b = Bs[(t * 8 + (lane >> 2)) * GR_LD + kk + (lane & 3)];
+          dmma_m8n8k4(acc[t][0], acc[t][1], a, b);
+        }
+      }
+    }
+  }
+  if (warp < 8) {
+    double* out = part + ((size_t)blockIdx.z * (nt * (nt + 1) / 2) + tIdx) * (GR_T * GR_T);
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+      const int r = warp * 8 + (lane >> 2), c = t * 8 + 2 * (lane & 3);
+      out[r * GR_T + c] = acc[t][0];
+      out[r * GR_T + c + 1] = acc[t][1];
+    }
+  }
+}
+
 // G (PA x PA, column-major, symmetric) = sum over splits of the partial tiles
 __global__ void gram_reduce_kernel(const double* __restrict__ part, int P, int nsplit, double* __restrict__ G) {
   const int PA = P + 1;
