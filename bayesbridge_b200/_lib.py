@@ -27,7 +27,7 @@ EXPORTS = [
     "bb_last_error", "bb_device_count", "bb_model_create", "bb_model_create_factors", "bb_gram", "bb_gram_noalloc",
     "bb_model_create_gram", "bb_model_resid_partial", "bb_model_set_r0", "bb_model_free", "bb_model_clone", "bb_model_status", "bb_model_get",
     "bb_model_precompute_ms", "bb_chains_create", "bb_chains_free", "bb_chains_set", "bb_chains_get", "bb_chains_alpha",
-    "bb_chains_option", "bb_set_wide_gaussian", "bb_chains_reserve", "bb_chains_run", "bb_chains_store_state", "bb_chains_fetch", "bb_chains_summary", "bb_launch_count", "bb_measure_fp64_fma",
+    "bb_chains_option", "bb_set_wide_gaussian", "bb_chains_reserve", "bb_chains_run", "bb_chains_store_state", "bb_chains_fetch", "bb_chains_summary", "bb_chains_summary_begin", "bb_chains_summary_add", "bb_chains_summary_end", "bb_launch_count", "bb_measure_fp64_fma",
     "bb_bridge_batched", "bb_bridge_batched_multi", "bb_bridge_batched_summary",
     "rtexpon_rate_left", "rtexpon_rate_both", "rtexpon_rate", "rtnorm_left", "rtnorm_both", "rtnorm", "rrtgamma_rate", "retstable_LD",
 ]
@@ -93,6 +93,9 @@ def load():
     L.bb_chains_store_state.argtypes = [vp, C.c_longlong]
     L.bb_chains_fetch.argtypes = [vp, C.c_int, C.c_longlong, C.c_longlong, vp]
     L.bb_chains_summary.argtypes = [vp, C.c_int, C.c_longlong, C.c_longlong, C.c_double, vp, vp]
+    L.bb_chains_summary_begin.argtypes = [vp, C.c_int]
+    L.bb_chains_summary_add.argtypes = [vp, C.c_longlong, C.c_longlong]
+    L.bb_chains_summary_end.argtypes = [vp, C.c_double, vp, vp]
     L.bb_measure_fp64_fma.argtypes = [C.c_int, dp]
     L.bb_bridge_batched.argtypes = [C.c_int, C.c_int, dp, dp, C.c_int, C.c_int, C.POINTER(Hyper), C.c_int, C.c_ulonglong,
                                     C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int] + [dp] * 7 + [up, dp]

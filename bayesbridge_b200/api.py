@@ -328,6 +328,25 @@ class Chains:
             out["chains"] = pc
         return out
 
+    def running_begin(self, name="beta"):
+        """RUNNING sum.stat (bb_chains_summary_begin / add / end): fold chunks of stored draws into per-series accumulators,
+        reuse the draw buffer, read the table at the end -- no limit on the run length."""
+        self._ck(self.L.bb_chains_summary_begin(self.h, _OUT[name]))
+
+    def running_add(self, slot0, nslots):
+        self._ck(self.L.bb_chains_summary_add(self.h, slot0, nslots))
+
+    def running_end(self, runtime=None, per_chain=False):
+        pooled = np.zeros((7, self.P))
+        pc = np.zeros((self.nchains, 5, self.P)) if per_chain else None
+        self._ck(self.L.bb_chains_summary_end(self.h, float(runtime or 0.0), pc.ctypes.data if per_chain else None, pooled.ctypes.data))
+        out = dict(zip(("mean", "sd", "ESS", "ESS.sec", "t", "Q.1", "Q.9"), pooled))
+        if runtime is None:
+            del out["ESS.sec"]
+        if per_chain:
+            out["chains"] = pc
+        return out
+
     # ---- the conditionals of class BridgeRegression, one launch each over all chains ----
     def sample_tau_marg(self, hyper, it):  # BridgeRegression.cpp:453-465
         return self.run(hyper, 1, it, ST_TAU)

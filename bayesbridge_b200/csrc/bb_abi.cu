@@ -257,6 +257,8 @@ struct bb_chains {
   double *sig2 = nullptr, *tau = nullptr, *alpha = nullptr;
   uint32_t* status = nullptr;
   double *A = nullptr, *W = nullptr, *Q = nullptr;   // large-P stable workspace: factors, inverse diagonal blocks, partial sums of d'X'Xd
+  // running sum.stat (bb_running.cu): accumulators of one vector output, n draws per chain folded so far
+  double *rs_state = nullptr, *rs_range = nullptr; unsigned int* rs_hist = nullptr; long long rs_n = 0; int rs_which = 0;
   int wide = 0;                                      // BB_OPT_WIDE_GAUSSIAN: the Gaussian draw through the N x N system (bb_stb_wide.cuh)
   double *U = nullptr, *R = nullptr;                 // its workspace: u [nchains][P], right-hand side [nchains][N]
   // draw buffer
@@ -275,7 +277,7 @@ struct bb_chains {
   void free_draws() { dfree(o_beta); dfree(o_u); dfree(o_omega); dfree(o_shape); dfree(o_lambda); dfree(o_sig2); dfree(o_tau); dfree(o_alpha); nslots = 0; out_mask = 0; }
   ~bb_chains() {
     cudaSetDevice(device);
-    dfree(beta); dfree(u); dfree(aux); dfree(shape); dfree(z); dfree(sig2); dfree(tau); dfree(alpha); dfree(status); dfree(A); dfree(W); dfree(Q); dfree(U); dfree(R);
+    dfree(beta); dfree(u); dfree(aux); dfree(shape); dfree(z); dfree(sig2); dfree(tau); dfree(alpha); dfree(status); dfree(A); dfree(W); dfree(Q); dfree(U); dfree(R); dfree(rs_state); dfree(rs_range); dfree(rs_hist);
     free_draws();
     for (int i = 0; i < 4; ++i) if (gx[i]) cudaGraphExecDestroy(gx[i]);
     dfree(ctl);
@@ -858,6 +860,66 @@ int bb_chains_summary(const bb_chains* c, int which, long long slot0, long long 
   });
 }
 
+namespace {
+const double* vector_output(const bb_chains* c, int which) {
+  switch (which) {
+    case BB_OUT_BETA: return c->o_beta;
+    case BB_OUT_U: return c->o_u;
+    case BB_OUT_OMEGA: return c->o_omega;
+    case BB_OUT_SHAPE: return c->o_shape;
+    case BB_OUT_LAMBDA: return c->o_lambda;
+    default: return nullptr;
+  }
+}
+}  // namespace
+
+int bb_chains_summary_begin(bb_chains* c, int which) {
+  return guarded([&] {
+    BB_CUDA_CHECK(cudaSetDevice(c->m->device));
+    if (which != BB_OUT_BETA && which != BB_OUT_U && which != BB_OUT_OMEGA && which != BB_OUT_SHAPE && which != BB_OUT_LAMBDA)
+      throw std::string("bb_chains_summary_begin: not a vector output");
+    const int P = c->m->P;
+    if (!c->rs_state) {
+      c->rs_state = dalloc<double>(bb::running_state_doubles(c->nchains, P));
+      c->rs_range = dalloc<double>((size_t)2 * P);
+      c->rs_hist = dalloc<unsigned int>(bb::running_hist_words(P));
+    }
+    c->rs_n = 0; c->rs_which = which;
+  });
+}
+
+int bb_chains_summary_add(bb_chains* c, long long slot0, long long nslots) {
+  return guarded([&] {
+    BB_CUDA_CHECK(cudaSetDevice(c->m->device));
+    if (!c->rs_state || !c->rs_which) throw std::string("bb_chains_summary_add: call bb_chains_summary_begin first");
+    const double* src = vector_output(c, c->rs_which);
+    if (!src) throw std::string("bb_chains_summary_add: that output is not reserved");
+    if (slot0 < 0 || nslots < 1 || slot0 + nslots > c->nslots) throw std::string("bb_chains_summary_add: slot range out of bounds");
+    if (c->rs_n == 0 && nslots < 2) throw std::string("bb_chains_summary_add: the first chunk needs at least 2 slots (it fixes the range of the quantile sketch)");
+    long long done = 0;
+    while (done < nslots) {                     // at most 4096 slots per launch (shared memory of the fold kernel)
+      const int m = (int)std::min(4096LL, nslots - done);
+      launched(bb::running_add_device(src, c->m->P, c->nslots, slot0 + done, m, c->nchains, c->rs_n, c->rs_state, c->rs_range, c->rs_hist, c->stream));
+      c->rs_n += m; done += m;
+    }
+    BB_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+  });
+}
+
+int bb_chains_summary_end(bb_chains* c, double runtime_sec, double* per_chain, double* pooled) {
+  return guarded([&] {
+    BB_CUDA_CHECK(cudaSetDevice(c->m->device));
+    if (!c->rs_state || c->rs_n < 2) throw std::string("bb_chains_summary_end: fewer than 2 draws per chain were added");
+    const size_t P = c->m->P, n1 = (size_t)c->nchains * 5 * P, n2 = 7 * P;
+    DBuf<double> d_pc(n1);
+    DBuf<double> d_po(n2);
+    launched(bb::running_end_device(c->rs_state, c->rs_range, c->rs_hist, (int)P, c->nchains, c->rs_n, runtime_sec, d_pc, d_po, c->stream));
+    if (per_chain) BB_CUDA_CHECK(cudaMemcpyAsync(per_chain, d_pc, n1 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (pooled) BB_CUDA_CHECK(cudaMemcpyAsync(pooled, d_po, n2 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    BB_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+  });
+}
+
 int bb_chains_fetch(const bb_chains* c, int which, long long slot0, long long nslots, double* out) {
   return guarded([&] {
     BB_CUDA_CHECK(cudaSetDevice(c->m->device));
@@ -949,7 +1011,11 @@ double run_driver_on_model(const bb_model* m, int method, int ortho, const bb_hy
   int mask = 0;
   for (const Out& o : outs) if (o.host) mask |= o.which;
   if (mask == 0 || out.sum_pooled || out.sum_chain) mask |= BB_OUT_BETA;
-  if (bb_chains_reserve(g.c, nsamp, mask)) throw std::string(g_err);
+  // Summary mode keeps RUNNING summaries (bb_running.cu): the draw buffer holds one chunk (at most 1024 slots) that is folded
+  // into the accumulators and reused, so the run length is not bounded by device memory or by a slot limit.
+  const bool running = out.sum_pooled || out.sum_chain;
+  const long long cap = running ? std::min<long long>(nsamp, 1024) : nsamp;
+  if (bb_chains_reserve(g.c, cap, mask)) throw std::string(g_err);
   for (Out& o : outs) {
     switch (o.host ? o.which : 0) {
       case BB_OUT_BETA: o.dev = g.c->o_beta; break;
@@ -967,12 +1033,13 @@ double run_driver_on_model(const bb_model* m, int method, int ortho, const bb_hy
   // the layout of the draw buffer, [chain][sample][w], so a slot range is one strided (2-D) copy per output.
   struct CopyStream { cudaStream_t s = nullptr; ~CopyStream() { if (s) cudaStreamDestroy(s); } } cps;
   BB_CUDA_CHECK(cudaStreamCreateWithFlags(&cps.s, cudaStreamNonBlocking));
-  auto download = [&](long long s0, long long ns) {
+  auto download = [&](long long s0, long long ns, long long d0 = -1) {   // host slots [s0, s0 + ns) <- device slots [d0, d0 + ns) (d0 < 0: the same)
+    if (d0 < 0) d0 = s0;
     for (const Out& o : outs) {
       if (!o.dev || ns <= 0) continue;
-      const size_t pitch = (size_t)nsamp * o.w * sizeof(double), off = (size_t)s0 * o.w;
-      BB_CUDA_CHECK(cudaMemcpy2DAsync(o.host + off, pitch, o.dev + off, pitch, (size_t)ns * o.w * sizeof(double), (size_t)nchains,
-                                      cudaMemcpyDeviceToHost, cps.s));
+      const size_t hpitch = (size_t)nsamp * o.w * sizeof(double), dpitch = (size_t)cap * o.w * sizeof(double);
+      BB_CUDA_CHECK(cudaMemcpy2DAsync(o.host + (size_t)s0 * o.w, hpitch, o.dev + (size_t)d0 * o.w, dpitch, (size_t)ns * o.w * sizeof(double),
+                                      (size_t)nchains, cudaMemcpyDeviceToHost, cps.s));
     }
   };
   auto interrupted = [&]() { return poll && g_interrupt && g_interrupt() != 0; };
@@ -1018,13 +1085,22 @@ double run_driver_on_model(const bb_model* m, int method, int ortho, const bb_hy
   // (BridgeWrapper.cpp:294; its burn-in :272 and the other three drivers pass (alpha_a, alpha_b)): kept as written
   bb_hyper hs = *h;
   if (method != BB_TRI && !ortho) hs.alpha_a = hs.alpha_b;
+  if (running && bb_chains_summary_begin(g.c, BB_OUT_BETA)) throw std::string(g_err);
+  long long dev_base = 1;                         // running mode: the chunk starts behind sample 0 the first time, at slot 0 afterwards
+  if (running && total == 0 && bb_chains_summary_add(g.c, 0, 1)) throw std::string(g_err);
   while (done < total) {
-    const long long n = std::min(chunk, total - done);
+    long long n = std::min(chunk, total - done);
+    if (running) n = std::min(n, (cap - dev_base) * thin);
     auto ts = std::chrono::steady_clock::now();
-    chains_run(g.c, &hs, (unsigned)(nburn + done), (int)n, BB_ST_ALL, 0, 0, thin, 1 + done / thin, nullptr);
+    chains_run(g.c, &hs, (unsigned)(nburn + done), (int)n, BB_ST_ALL, 0, 0, thin, running ? dev_base : 1 + done / thin, nullptr);
     done += n;
     const long long have = 1 + done / thin;
-    download(copied, have - copied); copied = have;
+    if (running) {
+      const long long cnt = have - copied;        // device slots [0, cnt) = host samples [copied, have)
+      if (bb_chains_summary_add(g.c, 0, cnt)) throw std::string(g_err);
+      download(copied, cnt, 0); copied = have; dev_base = 0;
+      BB_CUDA_CHECK(cudaStreamSynchronize(cps.s));   // the next chunk overwrites these slots
+    } else { download(copied, have - copied); copied = have; }
     if (interrupted()) {
       BB_CUDA_CHECK(cudaStreamSynchronize(cps.s));
       throw std::string("interrupted by the caller's hook (bb_set_interrupt) after ") + std::to_string(have) + " of " + std::to_string(nsamp) + " samples";
@@ -1034,12 +1110,12 @@ double run_driver_on_model(const bb_model* m, int method, int ortho, const bb_hy
       if (sec > 0) chunk = std::max(16LL, std::min(8192LL, (long long)((chunk / thin) * 0.2 / sec))) * thin;
     }
   }
-  download(copied, nsamp - copied);
+  if (!running) download(copied, nsamp - copied);
   BB_CUDA_CHECK(cudaStreamSynchronize(cps.s));    // the clock stops when the last draws are in host memory
   const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   lap("sampling loop + download");
   // summary mode: sum.stat of beta over the nsamp stored samples, on the device (the draws need not leave the GPU)
-  if ((out.sum_pooled || out.sum_chain) && bb_chains_summary(g.c, BB_OUT_BETA, 0, nsamp, secs, out.sum_chain, out.sum_pooled)) throw std::string(g_err);
+  if (running && bb_chains_summary_end(g.c, secs, out.sum_chain, out.sum_pooled)) throw std::string(g_err);
   if (out.status && bb_chains_get(g.c, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, out.status)) throw std::string(g_err);
   if (g_verbose && poll) std::printf("Sampling complete: %g sec. for %i iterations.\n", secs, nsamp);
   return secs;

@@ -98,6 +98,14 @@ int chol_lower_device(double* A, int P, double* Winv, uint32_t* status, cudaStre
 int summary_device(const double* draws, int P, long long chain_stride, long long slot0, int n, int nchains, double runtime_sec,
                    double* per_chain_dev, double* pooled_dev, cudaStream_t st);
 
+// ---- running sum.stat (bb_running.cu): chunks of stored draws folded into per-series accumulators ----
+size_t running_state_doubles(int nchains, int P);
+size_t running_hist_words(int P);
+int running_add_device(const double* draws, int P, long long chain_stride, long long slot0, int m, int nchains, long long n_before,
+                       double* state, double* range, unsigned int* hist, cudaStream_t st);
+int running_end_device(const double* state, const double* range, const unsigned int* hist, int P, int nchains, long long n,
+                       double runtime_sec, double* per_chain_dev, double* pooled_dev, cudaStream_t st);
+
 // ---- one-time precompute (bb_pre.cu) ----
 int gram_device(const double* X, const double* y, int N, int P, double* G, cudaStream_t st);   // G = [X y]'[X y]
 int gram_device_noalloc(const double* X, const double* y, int N, int P, double* G, cudaStream_t st);   // same, partial tiles in a static __device__ array

@@ -139,6 +139,10 @@ __global__ void summary_pool_kernel(const double* __restrict__ per_chain, int P,
   }
 }
 
+void summary_pool_launch(const double* per_chain, int P, int nchains, long long n, double runtime_sec, double* pooled, cudaStream_t st) {
+  summary_pool_kernel<<<(P + 3) / 4, 128, 0, st>>>(per_chain, P, nchains, (int)n, runtime_sec, pooled);
+}
+
 // order-preserving map double -> uint64
 __device__ __forceinline__ unsigned long long dkey(double x) {
   const unsigned long long b = (unsigned long long)__double_as_longlong(x);

@@ -212,6 +212,16 @@ int bb_chains_fetch(const bb_chains *c, int which, long long slot0, long long ns
  *   when runtime_sec <= 0), t = mean / sd, quantiles are R's type 7 over the pooled draws. */
 int bb_chains_summary(const bb_chains *c, int which, long long slot0, long long nslots, double runtime_sec,
                       double *per_chain, double *pooled);
+/* RUNNING sum.stat: the same table from a run of ANY length with a draw buffer of one chunk (SURVEY section 7.1 K_out).  begin
+ * resets the accumulators of one vector output; add folds the stored slots [slot0, slot0 + nslots) of every chain into them, in
+ * order (the caller then reuses the slots); end writes the table.  Kept per (chain, coefficient): the raw lagged products up to
+ * lag 48, the first and last 48 values and the sum -- mean, sd and the autocovariances ar.yw needs are recovered exactly, so
+ * ESS is coda's definition with the lag window floor(10 log10 n) capped at 48.  Quantiles come from a mergeable sketch (2048
+ * bins over +-10 sd of the first chunk per coefficient, shared by all chains; resolution 0.01 sd): pooled Q.1 / Q.9 only,
+ * per_chain's two quantile rows are NaN.  The first add needs >= 2 slots.  bb_bridge_batched_summary runs on this. */
+int bb_chains_summary_begin(bb_chains *c, int which);
+int bb_chains_summary_add(bb_chains *c, long long slot0, long long nslots);
+int bb_chains_summary_end(bb_chains *c, double runtime_sec, double *per_chain, double *pooled);
 /* number of kernels launched by this library in this process so far */
 long long bb_launch_count(void);
 /* Measurement aid, no counterpart in the reference: measured peak of the FP64 vector pipe (DFMA) of `device` in
@@ -249,7 +259,8 @@ int bb_bridge_batched_multi(int method, int ortho,
 /* The same run in SUMMARY mode: the draws of beta stay in HBM and sum.stat is taken on the
  * device.  pooled: [7][P] (mean, sd, ESS, ESS.sec, t, Q.1, Q.9 over all chains, ESS.sec = ESS / runtime of the
  * post-burn-in loop); per_chain: [nchains][5][P] (mean, sd, ESS, Q.1, Q.9); either may be NULL (not both).
- * sig2 / tau: [nchains][nsamp] or NULL.  2 <= nsamp <= 16384. */
+ * sig2 / tau: [nchains][nsamp] or NULL.  nsamp >= 2, no upper limit: the summaries are running ones (bb_chains_summary_begin /
+ * add / end) over a draw buffer of at most 1024 slots; per_chain's quantile rows are NaN (see there). */
 int bb_bridge_batched_summary(int method, int ortho,
                               const double *X, const double *y, int N, int P, const bb_hyper *h,
                               int nchains, unsigned long long seed, unsigned int chain0,

@@ -96,3 +96,46 @@ def test_port_vector_entry_points_agree_with_the_bulk_draws():
     assert np.array_equal(O.draw_vec("rtnorm", [1.0 * one, inf, 0.0 * one, 2.0 * one], seed=11), O.draw_many(4, n, (1.0, 0.0, 2.0), seed=11))
     assert np.array_equal(O.draw_vec("rtnorm", [-inf, -1.0 * one, 0.0 * one, 2.0 * one], seed=11), -O.draw_many(4, n, (1.0, -0.0, 2.0), seed=11))
     assert np.array_equal(O.draw_vec("rtexpon_rate", [0.3 * one, inf, 2.0 * one], seed=11), O.draw_many(5, n, (0.3, 2.0), seed=11))
+
+
+def test_ess_ar_against_an_independent_statement_of_ar_yw():
+    """ess.py (and with it the device summaries, which are checked against it) pinned by an independent statement of what
+    coda::effectiveSize computes: R's ar.yw solves the Yule-Walker equations of every order p <= floor(10 log10 n) on the
+    mean-centred sample autocovariances (divisor n), takes the order with the smallest AIC = n log v_p + 2 p, rescales the
+    innovation variance by n / (n - (p + 1)), and ESS = n var / S(0) with S(0) = v / (1 - sum phi)^2.  Here every order is
+    solved DIRECTLY (dense Toeplitz system, numpy) instead of by the Levinson-Durbin recursion ess.py uses; the two must agree
+    to rounding on every series, and on a long AR(p) both must recover the known coefficients."""
+    from bayesbridge_b200 import ess
+
+    def direct(x):
+        x = np.asarray(x, float); n = x.size
+        xc = x - x.mean()
+        K = min(n - 1, int(np.floor(10 * np.log10(n))))
+        g = np.array([xc[: n - k] @ xc[k:] / n for k in range(K + 1)])
+        best = (n * np.log(g[0]), 0, np.zeros(0), g[0])
+        for p in range(1, K + 1):
+            R = np.array([[g[abs(i - j)] for j in range(p)] for i in range(p)])
+            phi = np.linalg.solve(R, g[1:p + 1])
+            v = g[0] - phi @ g[1:p + 1]
+            if v <= 0:
+                break
+            aic = n * np.log(v) + 2 * p
+            if aic < best[0]:
+                best = (aic, p, phi, v)
+        _, p, phi, v = best
+        v *= n / (n - (p + 1))
+        return n * x.var(ddof=1) * (1 - phi.sum()) ** 2 / v, p, phi
+
+    r = np.random.default_rng(11)
+    for phis, n in (([0.6], 3000), ([0.5, -0.3], 5000), ([0.2, 0.1, 0.4], 20000), ([], 1000)):
+        x = np.zeros(n + 200)
+        e = r.standard_normal(n + 200)
+        for t in range(len(x)):
+            x[t] = e[t] + sum(ph * x[t - 1 - j] for j, ph in enumerate(phis) if t - 1 - j >= 0)
+        x = x[200:]
+        want, p, phi = direct(x)
+        np.testing.assert_allclose(ess.ess_ar(x), want, rtol=1e-9)
+        if n >= 20000:                       # long series: the fitted model is the generating one
+            assert p == len(phis)
+            np.testing.assert_allclose(phi, phis, atol=0.03)
+            np.testing.assert_allclose(want, n * (1 - sum(phis)) ** 2 * x.var(ddof=1) / 1.0, rtol=0.05)   # S(0) = sigma_e^2 / (1 - sum phi)^2
