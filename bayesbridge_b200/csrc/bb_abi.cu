@@ -446,7 +446,10 @@ void chains_run(bb_chains* c, const bb_hyper* hh, unsigned iter0, int niter, int
     // captured once -- and again whenever a frozen parameter (hyper-parameters, stages, store or not) changes -- then
     // replayed niter times: one cudaGraphLaunch per sub-batch and iteration instead of ~50 launches, which at P = 256 took
     // longer to issue from the host than to run.  thin > 1 (stores on some iterations only) and short runs launch directly.
-    static const bool graph_off = std::getenv("BB_STBL_NOGRAPH") != nullptr;
+    // MEASURED (B200, round 2): no gain -- c5s 124.6 M draws/s replayed against 125.1 M launched directly, c4 identical; at two
+    // processes per box the replay was 15 % SLOWER.  The iteration is bound by the chain of ~50 dependent small kernels on the
+    // GPU, not by issuing them.  The replay therefore stays opt-in (BB_STBL_GRAPH=1) for callers whose host thread is the bottleneck.
+    static const bool graph_off = std::getenv("BB_STBL_GRAPH") == nullptr;
     const bool storing = c->nslots > 0 && thin == 1;
     const bool use_graph = !graph_off && niter >= 4 && (thin == 1 || thin == 0 || c->nslots == 0);
     int it_first = -pre_tau;
