@@ -250,6 +250,9 @@ __device__ unsigned long long bb_phase_cyc[16];   // development: [0..7] stb64 p
 // coordinate values (shared or global), lam_out: where 2*draw goes (shared or global).
 // q_s: [2][qld] ints, qn_s: [2] ints (both zero on entry and on exit), kk_s: [P] block positions.
 // rc_s: optional [P] cache of the per-item constants (nullptr: recompute every pass).
+#ifdef BB_LAMBDA_STATS
+__device__ unsigned long long bb_lambda_stats[8];
+#endif
 template <int NT>
 __device__ inline void lambda_stage_cta(const int tid, int P, const double* beta, double* lam_out, double tau, double alpha_half,
                                         const RngKey key, uint32_t gch, uint32_t t, RetConst* rc_s,
@@ -309,6 +312,9 @@ __device__ inline void lambda_stage_cta(const int tid, int P, const double* beta
       BB_LAM_MARK(0);
       // walk the sequential path through the G evaluated offsets (uniform trip count: shuffles)
       int pos = 0, res = -1;
+#ifdef BB_LAMBDA_STATS
+      int st_in = 0, st_out = 0;
+#endif
       for (int lvl = 0; lvl < nlvl; ++lvl) {
         const int idx = lut_slot[pos < 63 ? pos : 63];
         const bool covered = idx < G;
@@ -316,9 +322,24 @@ __device__ inline void lambda_stage_cta(const int tid, int P, const double* beta
         if (res == -1) {
           if (!covered) res = -2;
           else if (c == 2) res = idx;
-          else pos += (c == 0) ? 3 : 5;
+          else {
+            pos += (c == 0) ? 3 : 5;
+#ifdef BB_LAMBDA_STATS
+            if (c == 0) ++st_in; else ++st_out;
+#endif
+          }
         }
       }
+#ifdef BB_LAMBDA_STATS
+      // development counters (trials per draw of the tilted-stable stage): rounds of the SEQUENTIAL sampler's
+      // path rejected at the inner / outer trial, accepted draws, rounds evaluated by the lanes (speculation included), passes
+      if (valid) atomicAdd(&bb_lambda_stats[3], 1ull);
+      if (valid && sub == 0) {
+        atomicAdd(&bb_lambda_stats[0], (unsigned long long)st_in); atomicAdd(&bb_lambda_stats[1], (unsigned long long)st_out);
+        if (res >= 0) atomicAdd(&bb_lambda_stats[2], 1ull);
+      }
+      if (tid == 0 && base == 0) atomicAdd(&bb_lambda_stats[4], 1ull);
+#endif
       BB_LAM_MARK(1);
       const double val = __shfl_sync(0xffffffffu, out, res >= 0 ? res : 0, G);
       if (valid && sub == 0) {

@@ -25,6 +25,19 @@ void launch64(const StbLaunch& L, cudaStream_t st) {
   BB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   kern<<<(L.nchains + NCH - 1) / NCH, S64_T * NCH, smem, st>>>(L);
   check_launch();
+#ifdef BB_LAMBDA_STATS
+  if (L.niter >= 8) {
+    BB_CUDA_CHECK(cudaStreamSynchronize(st));
+    unsigned long long q[8];
+    static unsigned long long qp[8] = {0};
+    BB_CUDA_CHECK(cudaMemcpyFromSymbol(q, bb_lambda_stats, sizeof(q)));
+    const double in = (double)(q[0] - qp[0]), out = (double)(q[1] - qp[1]), acc = (double)(q[2] - qp[2]), ev = (double)(q[3] - qp[3]), ps = (double)(q[4] - qp[4]);
+    std::printf("  [lambda stats] draws %.0f: sequential rounds per draw %.3f (inner rejections %.3f, outer rejections %.3f, + the accepted one); "
+                "rounds evaluated per draw (speculation included) %.3f; passes per chain-iteration %.2f\n",
+                acc, (in + out + acc) / acc, in / acc, out / acc, ev / acc, ps / ((double)L.nchains / NCH * L.niter));
+    for (int k = 0; k < 8; ++k) qp[k] = q[k];
+  }
+#endif
 #ifdef BB_PHASES
   BB_CUDA_CHECK(cudaStreamSynchronize(st));
   unsigned long long h[16];

@@ -203,3 +203,25 @@ def test_constructor_falls_back_for_ill_conditioned_and_rank_deficient_tall_desi
         assert rel_err(V @ np.diag(f["d"] ** 2) @ V.T, X.T @ X) < 1e-11
         if sv.min() == 0.0:   # singular: the least-squares start is 0 (BridgeRegression.cpp:79-91)
             assert not f["bhat"].any()
+
+
+def test_large_p_graph_replay_reproduces_direct_launches():
+    """BB_STBL_GRAPH=1 (one iteration of the large-P stable path captured as a CUDA graph and replayed, iteration index and sink
+    slot read from device memory) must give the draws of the plain launches bit for bit.  The switch is read once per process,
+    so each arm runs in its own interpreter."""
+    import subprocess
+    import sys
+    code = ("import sys, hashlib; sys.path[:0]=['.','tests']; import numpy as np; import bayesbridge_b200 as bb; from helpers import small_problem;"
+            "X, y, _ = small_problem(300, 150, seed=8);"
+            "o = bb.bridge_batched(y, X, 40, method='stable', nchains=20, seed=3, burn=25, want=('beta','sig2','tau'), alpha=0.5);"
+            "assert not o['status'].any();"
+            "print(hashlib.sha256(o['beta'].tobytes() + o['sig2'].tobytes() + o['tau'].tobytes()).hexdigest())")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for env_extra in ({}, {"BB_STBL_GRAPH": "1"}):
+        env = dict(os.environ, **env_extra)
+        env.pop("BB_STBL_GRAPH", None) if not env_extra else None
+        r = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append(r.stdout.strip().splitlines()[-1])
+    assert outs[0] == outs[1]
