@@ -56,7 +56,7 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
     // cores, its blocked Cholesky with the kernels below (dimension N), both substitutions and beta = sig (u + D^-1 X'w)
     const int N = L.m.N, nbn = (N + SL_NB - 1) / SL_NB, ntile = nbn * (nbn + 1) / 2;
     wide_draw_kernel<<<nch, 256, (size_t)P * sizeof(double), st>>>(L); ++n;
-    wide_gram_kernel<<<dim3(ntile, nch), 256, 0, st>>>(L); ++n;
+    wide_gram_kernel<<<dim3(ntile, nch), WG_T, 0, st>>>(L); ++n;
     for (int kb = 0; kb < nbn; ++kb) {
       if (kb > 0) n += launch_update(L.A, N, kb, nbn, nch, st);
       stbl_potrf_kernel<<<nch, SL_T, (size_t)2 * SL_NB * (SL_NB + 1) * sizeof(double), st>>>(L.A, L.W, N, kb, L.status); ++n;

@@ -55,10 +55,13 @@ __global__ void __launch_bounds__(256) wide_draw_kernel(const StbLargeLaunch L) 
 }
 
 // ---- M_c = X D_c^-1 X' + I  (N x N, lower 64 x 64 tiles, diagonal tiles in full) on the FP64 tensor cores ----
-// CTA = one tile (bi >= bj) of one chain, 8 warps; warp w owns rows 8w..8w+7 of the tile and all 8 n-tiles (the mapping of
-// gram_kernel, bb_pre.cuh).  The contraction runs over the P columns of X: a chunk of 32 columns of the 64 rows of both
-// operands is staged in shared memory, the left one scaled by D^-1.
-__global__ void __launch_bounds__(256) wide_gram_kernel(const StbLargeLaunch L) {
+// CTA = one tile (bi >= bj) of one chain, FOUR warps; warp w owns rows 16w..16w+15 of the tile (two A fragments) and all 8
+// n-tiles, so that one B fragment load feeds two DMMAs: 10 shared-memory loads per 16 DMMAs instead of 9 per 8 (the 8-warp
+// mapping of gram_kernel ran the shared-memory LSU at 54 % with the DMMA pipe at 50 %, profiles/r2_c4w_wide_gram.md).
+// The contraction runs over the P columns of X: a chunk of 32 columns of the 64 rows of both operands is staged in shared
+// memory, the left one scaled by D^-1.
+constexpr int WG_T = 128;
+__global__ void __launch_bounds__(WG_T) wide_gram_kernel(const StbLargeLaunch L) {
   __shared__ double As[GR_T * GR_LD];
   __shared__ double Bs[GR_T * GR_LD];
   __shared__ double dv[GR_K];
@@ -70,13 +73,15 @@ __global__ void __launch_bounds__(256) wide_gram_kernel(const StbLargeLaunch L) 
   const double f = L.tau[ch] * L.tau[ch] / L.sig2[ch];
   const double* lam = L.lambda + (size_t)ch * P;
   const double* X = L.m.X;
-  double acc[8][2];
+  double acc[2][8][2];
 #pragma unroll
-  for (int t = 0; t < 8; ++t) { acc[t][0] = 0.0; acc[t][1] = 0.0; }
+  for (int h = 0; h < 2; ++h)
+#pragma unroll
+    for (int t = 0; t < 8; ++t) { acc[h][t][0] = 0.0; acc[h][t][1] = 0.0; }
   for (int k0 = 0; k0 < P; k0 += GR_K) {
     if (tid < GR_K) dv[tid] = (k0 + tid < P) ? f / lam[k0 + tid] : 0.0;
     __syncthreads();
-    for (int e = tid; e < GR_T * GR_K; e += 256) {       // lanes run along the rows: X is column-major
+    for (int e = tid; e < GR_T * GR_K; e += WG_T) {      // lanes run along the rows: X is column-major
       const int r = e & (GR_T - 1), kk = e >> 6;
       const int k = k0 + kk, ra = bi * GR_T + r, rb = bj * GR_T + r;
       double va = 0.0, vb = 0.0;
@@ -90,11 +95,13 @@ __global__ void __launch_bounds__(256) wide_gram_kernel(const StbLargeLaunch L) 
     __syncthreads();
 #pragma unroll
     for (int kk = 0; kk < GR_K; kk += 4) {
-      const double a = As[(warp * 8 + (lane >> 2)) * GR_LD + kk + (lane & 3)];
+      const double a0 = As[(warp * 16 + (lane >> 2)) * GR_LD + kk + (lane & 3)];
+      const double a1 = As[(warp * 16 + 8 + (lane >> 2)) * GR_LD + kk + (lane & 3)];
 #pragma unroll
       for (int t = 0; t < 8; ++t) {
         const double b = Bs[(t * 8 + (lane >> 2)) * GR_LD + kk + (lane & 3)];
-        dmma_m8n8k4(acc[t][0], acc[t][1], a, b);
+        dmma_m8n8k4(acc[0][t][0], acc[0][t][1], a0, b);
+        dmma_m8n8k4(acc[1][t][0], acc[1][t][1], a1, b);
       }
     }
     __syncthreads();
@@ -102,14 +109,16 @@ __global__ void __launch_bounds__(256) wide_gram_kernel(const StbLargeLaunch L) 
   // C fragment: row = lane/4, cols = 2*(lane%4) + {0,1};  M is stored column-major with leading dimension N
   double* M = L.A + (size_t)ch * N * N;
 #pragma unroll
-  for (int t = 0; t < 8; ++t) {
-    const int r = bi * GR_T + warp * 8 + (lane >> 2);
+  for (int h = 0; h < 2; ++h)
 #pragma unroll
-    for (int q = 0; q < 2; ++q) {
-      const int c = bj * GR_T + t * 8 + 2 * (lane & 3) + q;
-      if (r < N && c < N) M[r + (size_t)c * N] = acc[t][q] + (r == c ? 1.0 : 0.0);
+    for (int t = 0; t < 8; ++t) {
+      const int r = bi * GR_T + warp * 16 + 8 * h + (lane >> 2);
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const int c = bj * GR_T + t * 8 + 2 * (lane & 3) + q;
+        if (r < N && c < N) M[r + (size_t)c * N] = acc[h][t][q] + (r == c ? 1.0 : 0.0);
+      }
     }
-  }
 }
 
 // ---- w = M^-1 r (both substitutions with the factor of M), beta = sig (u + D^-1 X' w) : one CTA per chain ----

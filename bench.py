@@ -318,6 +318,11 @@ def roofline_of(name, method, P, nch, ips, steps, T_local, peaks, N=None):
                    note="6 P^2 FP64 operations per chain-iteration as evaluated (SURVEY's as-written count is 10 P^2: frac_survey_10P2); "
                         "latency-bound: P sequential coordinate steps per iteration, see profiles/ for fp64-pipe utilisation and stalls")
     elif P <= 128:
+        ls = (ncu_info or {}).get("lambda_stage")
+        if ls:   # trials/s and mean trials per draw of the tilted-stable stage (counters of a dev build, profiles/)
+            draws_per_s = P * nch * ips * steps / T_local
+            out["lambda_stage"] = dict(ls, sequential_rounds_per_s=ls["sequential_rounds_per_draw"] * draws_per_s,
+                                       rounds_evaluated_per_s=ls["rounds_evaluated_per_draw"] * draws_per_s)
         out.update(bound="fp64-latency", peak=peaks["dgemm_tflops"], frac=achieved / peaks["dgemm_tflops"],
                    peak_source="cuBLAS DGEMM 8192^3 measured in this run",
                    note="P^3/3 + 5 P^2 flops are tiny at this P; the iteration is dependent FP64 chains (half of it the tilted-stable "
