@@ -14,6 +14,7 @@ void stb_large_prepare(int P) {
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_potrf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pf));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_scalar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sc));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));
+
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_trsm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_update2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stbl_update2_smem()));

@@ -436,18 +436,24 @@ __global__ void __launch_bounds__(256, 2) stbl_update2_kernel(double* Aall, int 
 // ---- the two blocked substitutions with a factor left by stbl_potrf / stbl_trsm (lower triangle of A, leading dimension P;
 //      Wg = inverses of its diagonal blocks): x <- L^-1 x and x <- L^-T x, x in shared memory, one CTA of SV_T threads ----
 constexpr int SV_T = 1024;   // threads of the solve kernels: one CTA streams a chain's factor twice, it needs the loads in flight
-__device__ __forceinline__ void stbl_stage_w(const double* Wg, int kb, double* D, int tid) {
+// (x, D, ps are OFFSETS into the dynamic shared memory: handed over as generic pointers the compiler loses the address space
+//  and every access becomes a generic load -- the solve kernel ran 2x slower, 51 -> 111 us at P = 256)
+__device__ __forceinline__ void stbl_stage_w(const double* Wg, int kb, int D_off, int tid) {
+  extern __shared__ double smem[];
+  double* D = smem + D_off;
   const double* W = Wg + (size_t)kb * SL_NB * SL_NB;
   for (int e = tid; e < SL_NB * SL_NB; e += SV_T) D[(e & (SL_NB - 1)) * (SL_NB + 1) + (e >> 6)] = W[e];   // W[e] = W(e % 64, e / 64)
 }
 // The diagonal blocks are applied as products with their inverses (rows / columns beyond the matrix are zero in W): a 64-term
 // dot product per unknown, all unknowns of the block at once, instead of 64 dependent substitution steps with a division each.
-__device__ __forceinline__ void stbl_forward(const double* __restrict__ A, const double* __restrict__ Wg, int P, double* x, double* D, double* ps, int tid) {
+__device__ __forceinline__ void stbl_forward(const double* A, const double* Wg, int P, int x_off, int D_off, int ps_off, int tid) {
+  extern __shared__ double smem[];
+  double* x = smem + x_off; double* D = smem + D_off; double* ps = smem + ps_off;
   const int vr = tid & (SL_NB - 1), vp = tid >> 6;     // matrix-vector product: index vr, 16 parts of 4 terms (SV_T = 1024)
   // forward: L w = Xy, column-oriented
   for (int k0 = 0; k0 < P; k0 += SL_NB) {
     const int nb = min(SL_NB, P - k0);
-    stbl_stage_w(Wg, k0 / SL_NB, D, tid);
+    stbl_stage_w(Wg, k0 / SL_NB, D_off, tid);
     __syncthreads();
     {   // w_blk = W x_blk
       double s = 0.0;
@@ -472,14 +478,16 @@ __device__ __forceinline__ void stbl_forward(const double* __restrict__ A, const
     __syncthreads();
   }
 }
-__device__ __forceinline__ void stbl_backward(const double* __restrict__ A, const double* __restrict__ Wg, int P, double* x, double* D, double* ps, int tid) {
+__device__ __forceinline__ void stbl_backward(const double* A, const double* Wg, int P, int x_off, int D_off, int ps_off, int tid) {
+  extern __shared__ double smem[];
+  double* x = smem + x_off; double* D = smem + D_off; double* ps = smem + ps_off;
   const int vr = tid & (SL_NB - 1), vp = tid >> 6, lane = tid & 31, warp = tid >> 5;
   const int nblk = (P + SL_NB - 1) / SL_NB;
   // backward: L' b = x over the stored lower triangle: column k of L is contiguous, one warp per column, lanes along r
   double* pk = ps + 15 * SL_NB;     // [64] column sums (the last part of ps is free until the product below)
   for (int kbk = nblk - 1; kbk >= 0; --kbk) {
     const int k0 = kbk * SL_NB, nb = min(SL_NB, P - k0);
-    stbl_stage_w(Wg, kbk, D, tid);
+    stbl_stage_w(Wg, kbk, D_off, tid);
     for (int kk = warp; kk < nb; kk += SV_T / 32) {
       const double* col = A + (size_t)(k0 + kk) * P;
       double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
@@ -518,19 +526,19 @@ __global__ void __launch_bounds__(SV_T) stbl_solve_kernel(const StbLargeLaunch L
   extern __shared__ double smem[];
   const int P = L.m.P, tid = threadIdx.x, ch = blockIdx.x;
   if (ch >= L.nchains) return;
-  double* x = smem;                 // [P]
-  double* D = x + P;                // [64][65] inverse W = L_kk^-1 of the current diagonal block (from stbl_potrf_kernel)
-  double* ps = D + SL_NB * (SL_NB + 1);   // [16][64] partial sums of the 64 x 64 matrix-vector products
+  double* x = smem;                 // [P]; then D [64][65]: inverse W = L_kk^-1 of the current diagonal block (from stbl_potrf_kernel),
+                                    // then ps [16][64]: partial sums of the 64 x 64 matrix-vector products (see stbl_forward)
   const double* A = L.A + (size_t)ch * P * P;
   const int nblk = (P + SL_NB - 1) / SL_NB;
   const double* Wg = L.W + (size_t)ch * nblk * SL_NB * SL_NB;
   const uint32_t gch = L.chain0 + (uint32_t)ch, it_ = stbl_iter(L);
   const double sig = sqrt(L.sig2[ch]);
   for (int j = tid; j < P; j += SV_T) x[j] = __ldg(L.m.Xy + j);
-  stbl_forward(A, Wg, P, x, D, ps, tid);          // w = L^-1 Xy (the reference's first trsm, BridgeRegression.cpp:564)
+  const int D_off = P, ps_off = P + SL_NB * (SL_NB + 1);
+  stbl_forward(A, Wg, P, 0, D_off, ps_off, tid);  // w = L^-1 Xy (the reference's first trsm, BridgeRegression.cpp:564)
   for (int j = tid; j < P; j += SV_T) { Stream s(L.key, gch, it_, ST_BETA_STB, (uint32_t)j); x[j] = fma(sig, s.norm(0), x[j]); }
   __syncthreads();
-  stbl_backward(A, Wg, P, x, D, ps, tid);         // beta = L^-T (w + sig eps)  (:565, :570-574)
+  stbl_backward(A, Wg, P, 0, D_off, ps_off, tid); // beta = L^-T (w + sig eps)  (:565, :570-574)
   double* beta = L.beta + (size_t)ch * P;
   const long long slot = stbl_slot(L);
   for (int j = tid; j < P; j += SV_T) {

@@ -126,17 +126,15 @@ __global__ void __launch_bounds__(SV_T) wide_solve_kernel(const StbLargeLaunch L
   extern __shared__ double smem[];
   const int P = L.m.P, N = L.m.N, tid = threadIdx.x, ch = blockIdx.x;
   if (ch >= L.nchains) return;
-  double* x = smem;                        // [N]
-  double* D = x + N;                       // [64][65]
-  double* ps = D + SL_NB * (SL_NB + 1);    // [16][64]
+  double* x = smem;                        // [N], then D [64][65] and ps [16][64] of the substitutions
   const double* A = L.A + (size_t)ch * N * N;
   const int nblk = (N + SL_NB - 1) / SL_NB;
   const double* Wg = L.W + (size_t)ch * nblk * SL_NB * SL_NB;
   const int lane = tid & 31, warp = tid >> 5;
   const double* R = L.R + (size_t)ch * N;
   for (int n = tid; n < N; n += SV_T) x[n] = R[n];
-  stbl_forward(A, Wg, N, x, D, ps, tid);
-  stbl_backward(A, Wg, N, x, D, ps, tid);
+  stbl_forward(A, Wg, N, 0, N, N + SL_NB * (SL_NB + 1), tid);
+  stbl_backward(A, Wg, N, 0, N, N + SL_NB * (SL_NB + 1), tid);
   __syncthreads();
   const double sig2 = L.sig2[ch], tau = L.tau[ch];
   const double f = tau * tau / sig2, sig = sqrt(sig2);
