@@ -483,28 +483,61 @@ __global__ void __maxnreg__(tri_maxnreg(32 * W * NGMAX)) tri_sweep_kernel(const 
           double znew;
           if (di > 1e-16) {   // BridgeRegression.cpp:268-273
             const double a = (lm - mean) * isd, b = (rm - mean) * isd;
-            const TnPlan p = tn_setup_fast(a, b);
-            BB_TRI_MARK(10);
             double x = 0.0;
             bool fin = false;
-            if (p.mode == 5) { status |= ST_NAN; x = a + b; fin = true; }
-            else if (p.mode == 4) { if (a > b) status |= ST_EMPTY_INTERVAL; x = a; fin = true; }
             uint32_t base = 0;
-            while (true) {
-              double xt = 0.0;
-              const bool acc_ = !fin && tn_eval_log(p, td, xt);
-              const uint32_t all = __ballot_sync(0xffffffffu, acc_ || fin);   // a finished slice reports all its lanes
+            // Fast path, branch-free: the plans with a UNIFORM proposal -- mode 3 (interval in a tail and narrow: 91 % of the steps
+            // at c3) and mode 1 (interval around 0 and narrower than sqrt(2 pi): 9 %) -- classified and evaluated without a branch,
+            // so that the two chains of a group never diverge over the plan (tn_setup_fast is five dependent compare-and-branch
+            // steps, taken by the two slices of the warp one after the other when they disagree).  Same decisions, same
+            // arithmetic and same trial order as tn_setup_fast + tn_eval_log; anything else falls through to them.
+            const bool neg = b < 0.0;
+            const bool tail = (a > 0.0) || neg;
+            const double qa = neg ? -b : a, qb = neg ? -a : b;       // working orientation (tn_setup_fast: p.a, p.b)
+            const double qw = qb - qa;
+            const bool m3 = tail && (qw * (qa + 1.0) < 1.0);
+            const bool m1 = !tail && !(qw >= SQRT_2PI);
+            const bool quick = (a < b) && (m1 || m3);
+            bool general = true;
+            if (__all_sync(0xffffffffu, quick)) {
+              const double xt = qa + (qb - qa) * td.ua;
+              const double c0 = m3 ? qa * qa : 0.0;
+              const bool acc_ = td.lub <= 0.5 * (c0 - xt * xt);
+              const uint32_t all = __ballot_sync(0xffffffffu, acc_);
               const uint32_t mine = all & slmask;
               const int src = mine ? (__ffs(mine) - 1) : lane;
               const double xs = __shfl_sync(0xffffffffu, xt, src);
-              if (!fin && mine) { x = p.sgn * xs; fin = true; }
-              bool done = true;                                               // every slice has an accepting (or finished) lane
+              if (mine) { x = (neg ? -1.0 : 1.0) * xs; fin = true; }
+              bool done = true;
 #pragma unroll
               for (int c = 0; c < C; ++c) done = done && ((all >> (c * SL)) & ((SL == 32) ? 0xffffffffu : ((1u << SL) - 1u))) != 0u;
-              if (done) break;
-              base += SL;
-              if (base >= K_CAP - 32) { if (!fin) { status |= ST_TRIAL_CAP; x = nan(""); fin = true; } break; }
-              if (!fin) { double ua, ub; s.block(base + (uint32_t)sl, ua, ub); td.set(ua, ub); }
+              general = !done;
+              if (general) {                                         // a slice without an accepting trial among its SL lanes: next block
+                base = SL;
+                if (!fin) { double ua, ub; s.block(base + (uint32_t)sl, ua, ub); td.set(ua, ub); }
+              }
+            }
+            BB_TRI_MARK(10);
+            if (general) {
+              const TnPlan p = tn_setup_fast(a, b);
+              if (p.mode == 5) { status |= ST_NAN; x = a + b; fin = true; }
+              else if (p.mode == 4) { if (a > b) status |= ST_EMPTY_INTERVAL; x = a; fin = true; }
+              while (true) {
+                double xt = 0.0;
+                const bool acc_ = !fin && tn_eval_log(p, td, xt);
+                const uint32_t all = __ballot_sync(0xffffffffu, acc_ || fin);   // a finished slice reports all its lanes
+                const uint32_t mine = all & slmask;
+                const int src = mine ? (__ffs(mine) - 1) : lane;
+                const double xs = __shfl_sync(0xffffffffu, xt, src);
+                if (!fin && mine) { x = p.sgn * xs; fin = true; }
+                bool done = true;                                               // every slice has an accepting (or finished) lane
+#pragma unroll
+                for (int c = 0; c < C; ++c) done = done && ((all >> (c * SL)) & ((SL == 32) ? 0xffffffffu : ((1u << SL) - 1u))) != 0u;
+                if (done) break;
+                base += SL;
+                if (base >= K_CAP - 32) { if (!fin) { status |= ST_TRIAL_CAP; x = nan(""); fin = true; } break; }
+                if (!fin) { double ua, ub; s.block(base + (uint32_t)sl, ua, ub); td.set(ua, ub); }
+              }
             }
             BB_TRI_MARK(11);
             znew = mean + sd * x;
