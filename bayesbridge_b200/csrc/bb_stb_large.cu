@@ -10,7 +10,7 @@ void stb_large_prepare(int P) {
   const size_t smem_sc = ((size_t)P + 26) * sizeof(double) + ((size_t)3 * P + 2) * sizeof(int);
   const size_t smem_sv = ((size_t)P + SL_NB * (SL_NB + 1) + 16 * SL_NB) * sizeof(double);
   const size_t smem_sy = (size_t)2 * SL_NB * SL_LD * sizeof(double);
-  const size_t smem_pf = (size_t)2 * SL_NB * (SL_NB + 1) * sizeof(double);
+  const size_t smem_pf = stbl_potrf_smem();
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_potrf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pf));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_scalar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sc));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));
@@ -60,7 +60,7 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
     wide_gram_kernel<<<dim3(ntile, nch), WG_T, 0, st>>>(L); ++n;
     for (int kb = 0; kb < nbn; ++kb) {
       if (kb > 0) n += launch_update(L.A, N, kb, nbn, nch, st);
-      stbl_potrf_kernel<<<nch, SL_T, (size_t)2 * SL_NB * (SL_NB + 1) * sizeof(double), st>>>(L.A, L.W, N, kb, L.status); ++n;
+      stbl_potrf_kernel<<<nch, SL_T, stbl_potrf_smem(), st>>>(L.A, L.W, N, kb, L.status); ++n;
       const int rem = nbn - kb - 1;
       if (rem > 0) { stbl_trsm_kernel<<<dim3(rem, nch), 256, smem_sy, st>>>(L.A, L.W, N, kb); ++n; }
     }
@@ -71,11 +71,22 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
   stbl_build_kernel<<<dim3(64, nch), 256, 0, st>>>(L); ++n;
   for (int kb = 0; kb < nblk; ++kb) {   // left-looking: bring block column kb up to date, factor its diagonal block, solve its panel
     if (kb > 0) n += launch_update(L.A, P, kb, nblk, nch, st);
-    stbl_potrf_kernel<<<nch, SL_T, (size_t)2 * SL_NB * (SL_NB + 1) * sizeof(double), st>>>(L.A, L.W, P, kb, L.status); ++n;
+    stbl_potrf_kernel<<<nch, SL_T, stbl_potrf_smem(), st>>>(L.A, L.W, P, kb, L.status); ++n;
     const int rem = nblk - kb - 1;
     if (rem > 0) { stbl_trsm_kernel<<<dim3(rem, nch), 256, smem_sy, st>>>(L.A, L.W, P, kb); ++n; }
   }
   stbl_solve_kernel<<<nch, SV_T, smem_sv, st>>>(L); ++n;
+#ifdef BB_STBL_PHASES
+  {
+    static int calls = 0;
+    if (++calls == 40) {
+      cudaStreamSynchronize(st);
+      long long ph[2][8]; cudaMemcpyFromSymbol(ph, bb_stbl_ph, sizeof(ph));
+      fprintf(stderr, "[stbl phases] scalar: sums %lld  tau/sig2 %lld  lambda %lld | solve: forward %lld  normals %lld  backward %lld\n",
+              ph[0][1] - ph[0][0], ph[0][2] - ph[0][1], ph[0][3] - ph[0][2], ph[1][1] - ph[1][0], ph[1][2] - ph[1][1], ph[1][3] - ph[1][2]);
+    }
+  }
+#endif
   if (do_alpha) { stbl_alpha_kernel<<<(nch + 7) / 8, 256, 0, st>>>(L); ++n; }
   return n;
 }
@@ -96,7 +107,7 @@ int chol_lower_device(double* A, int P, double* Winv, uint32_t* status, cudaStre
   int n = 0;
   for (int kb = 0; kb < nblk; ++kb) {
     if (kb > 0) n += launch_update(A, P, kb, nblk, 1, st);
-    stbl_potrf_kernel<<<1, SL_T, (size_t)2 * SL_NB * (SL_NB + 1) * sizeof(double), st>>>(A, Winv, P, kb, status); ++n;
+    stbl_potrf_kernel<<<1, SL_T, stbl_potrf_smem(), st>>>(A, Winv, P, kb, status); ++n;
     const int rem = nblk - kb - 1;
     if (rem > 0) { stbl_trsm_kernel<<<dim3(rem, 1), 256, smem_sy, st>>>(A, Winv, P, kb); ++n; }
   }

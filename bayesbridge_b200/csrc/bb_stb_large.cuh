@@ -93,6 +93,15 @@ __device__ __forceinline__ uint32_t stbl_iter(const StbLargeLaunch& L) { return 
 __device__ __forceinline__ long long stbl_slot(const StbLargeLaunch& L) { return L.slot < 0 ? -1 : L.slot + (L.ctl ? L.ctl[1] : 0); }
 __global__ void stbl_advance_kernel(long long* ctl, int stored) { ctl[0] += 1; ctl[1] += stored; }
 
+// Phase clocks of the one-CTA-per-chain kernels (development, -DBB_STBL_PHASES): CTA 0, thread 0 stores clock64 at the marks;
+// launch_stb_large_iter prints the differences of one launch.
+#ifdef BB_STBL_PHASES
+__device__ long long bb_stbl_ph[2][8];
+#define STBL_MARK(k, i) do { __syncthreads(); if (threadIdx.x == 0 && blockIdx.x == 0) bb_stbl_ph[k][i] = clock64(); } while (0)
+#else
+#define STBL_MARK(k, i) do { } while (0)
+#endif
+
 // ---- tau, sig2, lambda: one CTA per chain -------------------------------------------------
 __global__ void __launch_bounds__(SL_T) stbl_scalar_kernel(const StbLargeLaunch L) {
   extern __shared__ double smem[];
@@ -104,6 +113,7 @@ __global__ void __launch_bounds__(SL_T) stbl_scalar_kernel(const StbLargeLaunch 
   int* qn_s = q_s + 2 * P;
   uint32_t* kk_s = reinterpret_cast<uint32_t*>(qn_s + 2);
   const int ch = blockIdx.x; if (ch >= L.nchains) return;
+  STBL_MARK(0, 0);
   const uint32_t gch = L.chain0 + (uint32_t)ch, t = stbl_iter(L);
   const double alpha = L.h.true_alpha > 0 ? L.h.true_alpha : L.alpha[ch];   // unknown alpha: chain state (stbl_alpha_kernel moves it)
   const bool know_tau = L.h.true_tau > 0, know_sig2 = L.h.true_sig2 > 0;
@@ -133,6 +143,7 @@ __global__ void __launch_bounds__(SL_T) stbl_scalar_kernel(const StbLargeLaunch 
   pt = warp_sum(pt); pq = warp_sum(pq); pg = warp_sum(pg);
   if (lane == 0) { red[warp] = pt; red[8 + warp] = pq; red[16 + warp] = pg; }
   __syncthreads();
+  STBL_MARK(0, 1);
   if (warp == 0 && do_tau) {
     double st = lane < 8 ? red[lane] : 0.0; st = warp_sum(st);
     Stream s(L.key, gch, t, L.pre ? ST_TAU_INIT : ST_TAU, 0);
@@ -148,10 +159,12 @@ __global__ void __launch_bounds__(SL_T) stbl_scalar_kernel(const StbLargeLaunch 
     if (lane == 0) sc[1] = (L.h.sig2_scale + 0.5 * rss) / g;
   }
   __syncthreads();
+  STBL_MARK(0, 2);
   const double tau = sc[0];
   if (tid == 0) { L.tau[ch] = sc[0]; L.sig2[ch] = sc[1]; L.alpha[ch] = alpha; }
   double* lam = L.lambda + (size_t)ch * P;
   if (do_lambda) lambda_stage_cta<SL_T>(tid, P, beta, lam, tau, 0.5 * alpha, L.key, gch, t, nullptr, q_s, P, qn_s, kk_s, status);
+  STBL_MARK(0, 3);
   status = __reduce_or_sync(0xffffffffu, status);
   if (lane == 0 && status) atomicOr(L.status + ch, status);
 }
@@ -169,116 +182,187 @@ __global__ void stbl_build_kernel(const StbLargeLaunch L) {
   }
 }
 
-// ---- Cholesky of the diagonal block kb (<= 64 x 64) in shared memory, and the inverse of its factor ----
+// ---- Cholesky of the diagonal block kb (<= 64 x 64) and the inverse of its factor, on the FP64 tensor cores ----
+// History of this kernel (us per launch of 64 chains, P = 256): scaled columns, three barriers and a libm rsqrt per column 87;
+// unscaled columns through shared memory 50; the block in registers (thread = row x column class), one barrier per column 52
+// -- every one of its 16 conditional updates per column had become a divergent branch around a dependent LDS + DFMA, 1700
+// cycles per column (scripts/mb/mb_potrf.cu); the same with unconditional loads and selects 41; this form, blocked by 8 x 8
+// tiles like stb64_kernel (bb_stb64.cuh): see DESIGN.md 4.3.
+constexpr int SP_LD = 68;    // row stride of the 64 x 64 arrays (4 mod 16: the DMMA fragment loads are conflict-free)
+constexpr int SP_PB = 12;    // row stride of a published 8 x 8 tile / inverse diagonal block
+inline size_t stbl_potrf_smem() { return (size_t)2 * SL_NB * SP_LD * sizeof(double); }
+
+// Factor and inverse factor of one 8 x 8 diagonal tile, in registers, every lane redundantly (static indices, no shuffles on
+// the dependent chain).  Columns stay UNSCALED during the elimination (multiplier = a(r,k) / a(k,k) through a reciprocal, 56
+// cycles, instead of an rsqrt, 95, on the chain of the 8 pivots); the rsqrt of the pivots are taken off the chain.
+// a(r,c), c <= r: on return the factor L (lower, scaled).  W = L^-1 (lower) -> Wout[8][SP_PB]: lane c < 8 computes column c
+// (W(c,c) = 1/L(c,c), W(r,c) = -1/L(r,r) sum_{m=c}^{r-1} L(r,m) W(m,c); entries above the diagonal are zero), the sums of all
+// rows advanced as soon as W(m,c) is known: a chain of 7 x (FMA + multiply).
+__device__ __forceinline__ bool chol8_factor_inverse(double (&a)[8][8], double* __restrict__ Wout, int lane) {
+  double rs[8];
+  bool bad = false;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const double piv = a[k][k];
+    bad = bad || !(piv > 0.0);
+    const double rc = x_rcp(piv);
+    rs[k] = x_rsqrt(piv);
+#pragma unroll
+    for (int r = k + 1; r < 8; ++r) {
+      const double lip = a[r][k] * rc;
+#pragma unroll
+      for (int c = k + 1; c <= r; ++c) a[r][c] = fma(-lip, a[c][k], a[r][c]);
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < 8; ++r)
+#pragma unroll
+    for (int c = 0; c <= r; ++c) a[r][c] *= rs[c];
+  double w[8], sum[8];
+#pragma unroll
+  for (int r = 0; r < 8; ++r) sum[r] = 0.0;
+#pragma unroll
+  for (int m = 0; m < 8; ++m) {
+    w[m] = m == lane ? rs[m] : (m > lane ? -rs[m] * sum[m] : 0.0);
+#pragma unroll
+    for (int r = m + 1; r < 8; ++r) sum[r] = fma(a[r][m], w[m], sum[r]);
+  }
+  if (lane < 8) {
+#pragma unroll
+    for (int r = 0; r < 8; ++r) Wout[r * SP_PB + lane] = w[r];
+  }
+  return bad;
+}
+
+#ifdef BB_POTRF_PHASES
+__device__ long long bb_potrf_ph[8];
+#define POTRF_MARK(i) do { __syncthreads(); if (threadIdx.x == 0 && blockIdx.x == 0) bb_potrf_ph[i] = clock64(); } while (0)
+#else
+#define POTRF_MARK(i) do { } while (0)
+#endif
+// The 36 lower 8 x 8 tiles of the block live in registers as DMMA accumulator fragments: tile n = i (i + 1) / 2 + j belongs to
+// warp n & 7, slot n >> 3.  Block column s: publish the tiles (i,s) -> warp 0 factors the diagonal tile and inverts its factor
+// -> panel L(i,s) = T(i,s) W_s' by DMMA -> trailing T(i,j) -= L(i,s) L(j,s)' by DMMA: three barriers per block column.
+// Rows / columns beyond the matrix are padded with the identity.
 __global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, double* Wall, int P, int kb, uint32_t* status) {
   extern __shared__ double smem[];
-  typedef double Row[SL_NB + 1];
-  Row* S = reinterpret_cast<Row*>(smem);                              // [64][65] the block / its factor
-  Row* Wm = reinterpret_cast<Row*>(smem + SL_NB * (SL_NB + 1));       // [64][65] inverse factor
-  const int ch = blockIdx.x, tid = threadIdx.x;
+  double* S = smem;                        // [64][SP_LD] row-major: the factor L
+  double* Wt = smem + SL_NB * SP_LD;       // [64][SP_LD] first the staged block (column-major), then W' : Wt[c][r] = W(r,c), W = L^-1
+  __shared__ double pb_s[SL_NB * SP_PB];   // the published block column: rows 0..63, 8 columns
+  __shared__ double wi_s[8 * 8 * SP_PB];   // the inverses of the 8 diagonal tiles of the factor
+  __shared__ double tt_s[8][8 * SP_PB];    // per warp: an 8 x 8 tile, transposed (the inverse stage)
+  const int ch = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   double* A = Aall + (size_t)ch * P * P;
   const int k0 = kb * SL_NB, nb = min(SL_NB, P - k0);
-  for (int e = tid; e < nb * nb; e += SL_T) { const int r = e % nb, c = e / nb; S[r][c] = A[(k0 + r) + (size_t)(k0 + c) * P]; }
+  POTRF_MARK(0);
+  const int fr = lane >> 2, fc = 2 * (lane & 3);      // accumulator fragment: row fr, columns fc, fc + 1
+  const int ar = lane >> 2, ak = lane & 3;            // A / B fragment: row ar, k = ak
+  double c0[5], c1[5];
+  int ti[5], tj[5];
+#pragma unroll
+  for (int sl = 0; sl < 5; ++sl) {                    // straight from global memory: 8 consecutive rows (64 B) per column and tile
+    const int n = sl * 8 + warp;
+    int i = 0;
+    while ((i + 1) * (i + 2) / 2 <= n) ++i;
+    ti[sl] = i; tj[sl] = n - i * (i + 1) / 2;
+    if (n >= 36) { ti[sl] = 0; tj[sl] = -1; }          // no tile
+    const int row = 8 * ti[sl] + fr, col = 8 * max(tj[sl], 0) + fc;
+    c0[sl] = (row < nb && col < nb) ? A[(k0 + row) + (size_t)(k0 + col) * P] : (row == col ? 1.0 : 0.0);
+    c1[sl] = (row < nb && col + 1 < nb) ? A[(k0 + row) + (size_t)(k0 + col + 1) * P] : (row == col + 1 ? 1.0 : 0.0);
+  }
+  POTRF_MARK(1);
+  bool bad = false;
+  for (int s = 0; s < 8; ++s) {
+    // (1) publish the tiles of block column s
+#pragma unroll
+    for (int sl = 0; sl < 5; ++sl)
+      if (tj[sl] == s) *reinterpret_cast<double2*>(pb_s + (ti[sl] * 8 + fr) * SP_PB + fc) = make_double2(c0[sl], c1[sl]);
+    __syncthreads();
+    // (2) diagonal tile: factor (written to S) and inverse factor
+    double a[8][8];
+    if (warp == 0) {
+#pragma unroll
+      for (int r = 0; r < 8; ++r)
+#pragma unroll
+        for (int c = 0; c <= r; ++c) a[r][c] = pb_s[(s * 8 + r) * SP_PB + c];
+      bad = chol8_factor_inverse(a, wi_s + s * 8 * SP_PB, lane) || bad;
+    }
+    __syncthreads();
+    if (warp == 0) {            // warp 0 owns no panel tile: it writes the factor of the diagonal tile meanwhile
+#pragma unroll
+      for (int r = 0; r < 8; ++r)
+#pragma unroll
+        for (int c = 0; c <= r; ++c) S[(8 * s + r) * SP_LD + 8 * s + c] = a[r][c];
+    }
+    // (3) panel: L(i,s) = T(i,s) W_s'  for i > s, tile i by warp i
+    if (warp > s) {
+      const int i = warp;
+      double d0 = 0.0, d1 = 0.0;
+#pragma unroll
+      for (int q = 0; q < 8; q += 4)
+        dmma_m8n8k4(d0, d1, pb_s[(i * 8 + ar) * SP_PB + q + ak], wi_s[(s * 8 + ar) * SP_PB + q + ak]);
+      *reinterpret_cast<double2*>(S + (8 * i + fr) * SP_LD + 8 * s + fc) = make_double2(d0, d1);
+    }
+    __syncthreads();
+    // (4) trailing update of my tiles (i,j), i >= j > s
+#pragma unroll
+    for (int sl = 0; sl < 5; ++sl)
+      if (tj[sl] > s) {
+#pragma unroll
+        for (int q = 0; q < 8; q += 4)
+          dmma_m8n8k4(c0[sl], c1[sl], -S[(8 * ti[sl] + ar) * SP_LD + 8 * s + q + ak], S[(8 * tj[sl] + ar) * SP_LD + 8 * s + q + ak]);
+      }
+  }
+  if (bad && lane == 0) atomicOr(status + ch, (uint32_t)ST_CHOL_FAIL);
+  POTRF_MARK(2);
+  for (int e = tid; e < SL_NB * SL_NB; e += SL_T) {
+    const int r = e & (SL_NB - 1), c = e >> 6;
+    if (r < nb && c <= r) A[(k0 + r) + (size_t)(k0 + c) * P] = S[r * SP_LD + c];
+    Wt[c * SP_LD + r] = 0.0;
+  }
+  POTRF_MARK(3);
   __syncthreads();
-  // Right-looking Cholesky with UNSCALED columns, ONE barrier per column and the matrix in REGISTERS: thread (row t, class h)
-  // owns S(t,j) for j = h, h + 4, ... (16 values, static indices: the 64 steps are unrolled).  Step k: the owners of column k
-  // publish it (64 values, double-buffered), barrier, every thread takes 1 / pivot and its multiplier from the published column
-  // and updates its own entries -- no read-modify-write through shared memory, no single thread computing the pivot for all.
-  // (History: a scaled form with a CTA-wide trailing update, three barriers and a libm rsqrt per column: 87 us per 64 x 64
-  // block; unscaled columns through shared memory, one barrier: 50 us, bound by dependent shared-memory round trips.)
-  // Rows / columns beyond the matrix are padded with the identity.
-  __shared__ double rs_s[SL_NB], colbuf[2][SL_NB];
+  // W = L^-1 (lower) by 8 x 8 tiles: the diagonal tiles are the inverses kept above; block row i = 1..7, tile (i,j) by warp j < i:
+  //   T(i,j) = sum_{k=j}^{i-1} L(i,k) W(k,j),   W(i,j) = -W(i,i) T(i,j)     (both on the tensor cores)
+  // -- depth 7 x (at most 14 dependent DMMAs) instead of the 64 dependent rows of a plain forward substitution.
+  // The panel solve below the block is a DMMA product with W' (stbl_trsm_kernel).
   {
-    const int t = tid & (SL_NB - 1), h = tid >> 6;
-    double rv[16];
+    const int j = warp;
 #pragma unroll
-    for (int v = 0; v < 16; ++v) {
-      const int j = h + 4 * v;
-      rv[v] = (t < nb && j < nb) ? S[t][j] : (t == j ? 1.0 : 0.0);
-    }
-    bool bad = false;
-#pragma unroll
-    for (int u = 0; u < 16; ++u) {
-#pragma unroll
-      for (int hh = 0; hh < 4; ++hh) {
-        const int k = 4 * u + hh;
-        if (h == hh) colbuf[k & 1][t] = rv[u];          // column k: S(t,k) L-unscaled, S(k,k) = pivot
-        __syncthreads();
-        const double piv = colbuf[k & 1][k];
-        if (t == k && h == hh) { rs_s[k] = piv > 0.0 ? x_rsqrt(piv) : rsqrt(piv); bad = bad || !(piv > 0.0); }
-        if (t > k) {
-          const double lip = colbuf[k & 1][t] * (piv > 0.0 ? x_rcp(piv) : 1.0 / piv);
-#pragma unroll
-          for (int v = u; v < 16; ++v) {
-            const int j = h + 4 * v;
-            if (j > k && j <= t) rv[v] = fma(-lip, colbuf[k & 1][j], rv[v]);
-          }
-        }
-      }
-    }
-    if (bad) atomicOr(status + ch, (uint32_t)ST_CHOL_FAIL);
-    __syncthreads();
-#pragma unroll
-    for (int v = 0; v < 16; ++v) {
-      const int j = h + 4 * v;
-      if (t < nb && j <= t) S[t][j] = rv[v] * rs_s[j];
-    }
-    __syncthreads();
-  }
-  for (int e = tid; e < nb * nb; e += SL_T) { const int r = e % nb, c = e / nb; if (r >= c) A[(k0 + r) + (size_t)(k0 + c) * P] = S[r][c]; }
-  // W = L^-1 (lower), by 8 x 8 blocks: the eight diagonal blocks are inverted independently (one thread per column, 1 / L(r,r) is
-  // the rs of the factorisation: no division), then block row i = 1..7:  T(i,j) = sum_{k=j}^{i-1} L(i,k) W(k,j)  for all j < i
-  // (one output element per thread), W(i,j) = -W(i,i) T(i,j).  Depth 8 x (a 56-term dot product + an 8-term one) instead of the
-  // 64 dependent rows of a plain forward substitution.  The panel solve below the block is a DMMA product with W' (stbl_trsm_kernel).
-  __shared__ double Tt[8][SL_NB];
-  __syncthreads();
-  for (int e = tid; e < SL_NB * SL_NB; e += SL_T) Wm[e / SL_NB][e % SL_NB] = 0.0;
-  __syncthreads();
-  if (tid < SL_NB) {
-    const int base = tid & ~7, c = tid & 7;
-    if (base + c < nb) {
-      double w[8];
-#pragma unroll
-      for (int r = 0; r < 8; ++r) {
-        w[r] = 0.0;
-        if (r == c) w[r] = rs_s[base + c];
-        else if (r > c && base + r < nb) {
-          double sum = 0.0;
-#pragma unroll
-          for (int m = 0; m < 8; ++m) if (m >= c && m < r) sum = fma(S[base + r][base + m], w[m], sum);
-          w[r] = -sum * rs_s[base + r];
-        }
-      }
-#pragma unroll
-      for (int r = 0; r < 8; ++r) if (r >= c && base + r < nb) Wm[base + r][base + c] = w[r];
+    for (int q = 0; q < 2; ++q) {    // diagonal tile j: Wt[8j + c][8j + r] = W_j(r,c)
+      const int e = lane + 32 * q, r = e & 7, c = e >> 3;
+      Wt[(8 * j + c) * SP_LD + 8 * j + r] = wi_s[(j * 8 + r) * SP_PB + c];
     }
   }
   __syncthreads();
-  for (int i = 1; 8 * i < nb; ++i) {
-    for (int e = tid; e < 64 * i; e += SL_T) {
-      const int r = e & 7, cc = e >> 3;              // row 8 i + r of L, column cc < 8 i of W
-      double sum = 0.0;
-      if (8 * i + r < nb) {
-        const double* lrow = &S[8 * i + r][0];
-#pragma unroll 4
-        for (int m = cc; m < 8 * i; ++m) sum = fma(lrow[m], Wm[m][cc], sum);   // W(m,cc) = 0 for m < cc
-      }
-      Tt[r][cc] = sum;
-    }
-    __syncthreads();
-    for (int e = tid; e < 64 * i; e += SL_T) {
-      const int r = e & 7, cc = e >> 3;
-      if (8 * i + r < nb) {
-        double sum = 0.0;
+  POTRF_MARK(4);
+  for (int i = 1; i < 8; ++i) {
+    const int j = warp;
+    if (j < i) {
+      double t0 = 0.0, t1 = 0.0;
+      for (int k = j; k < i; ++k) {
 #pragma unroll
-        for (int q = 0; q < 8; ++q) if (q <= r) sum = fma(Wm[8 * i + r][8 * i + q], Tt[q][cc], sum);
-        Wm[8 * i + r][cc] = -sum;
+        for (int q = 0; q < 8; q += 4)     // A = L(i,k)[ar][q + ak],  B(kk, n) = W(k,j)(kk, n) = Wt[8j + n][8k + kk]
+          dmma_m8n8k4(t0, t1, S[(8 * i + ar) * SP_LD + 8 * k + q + ak], Wt[(8 * j + ar) * SP_LD + 8 * k + q + ak]);
       }
+      double* tt = tt_s[warp];             // transposed: tt[n][kk] = T(kk, n)
+      tt[fc * SP_PB + fr] = t0; tt[(fc + 1) * SP_PB + fr] = t1;
+      __syncwarp();
+      double w0 = 0.0, w1 = 0.0;
+#pragma unroll
+      for (int q = 0; q < 8; q += 4)
+        dmma_m8n8k4(w0, w1, -wi_s[(i * 8 + ar) * SP_PB + q + ak], tt[ar * SP_PB + q + ak]);
+      Wt[(8 * j + fc) * SP_LD + 8 * i + fr] = w0; Wt[(8 * j + fc + 1) * SP_LD + 8 * i + fr] = w1;
     }
     __syncthreads();
   }
+  POTRF_MARK(5);
   double* W = Wall + ((size_t)ch * ((P + SL_NB - 1) / SL_NB) + kb) * SL_NB * SL_NB;   // kept per block column: the solve kernel uses them all
-  for (int e = tid; e < SL_NB * SL_NB; e += SL_T) { const int r = e % SL_NB, c = e / SL_NB; W[e] = Wm[r][c]; }
+  for (int e = tid; e < SL_NB * SL_NB; e += SL_T) {    // W[e] = W(e % 64, e / 64); rows / columns beyond the matrix are zero
+    const int r = e & (SL_NB - 1), c = e >> 6;
+    W[e] = (r < nb && c < nb) ? Wt[c * SP_LD + r] : 0.0;
+  }
+  POTRF_MARK(6);
 }
 
 // ---- panel: rows below the diagonal block,  L(i,kb) = C(i,kb) W_kb'  on the FP64 tensor cores ----
@@ -533,12 +617,16 @@ __global__ void __launch_bounds__(SV_T) stbl_solve_kernel(const StbLargeLaunch L
   const double* Wg = L.W + (size_t)ch * nblk * SL_NB * SL_NB;
   const uint32_t gch = L.chain0 + (uint32_t)ch, it_ = stbl_iter(L);
   const double sig = sqrt(L.sig2[ch]);
+  STBL_MARK(1, 0);
   for (int j = tid; j < P; j += SV_T) x[j] = __ldg(L.m.Xy + j);
   const int D_off = P, ps_off = P + SL_NB * (SL_NB + 1);
   stbl_forward(A, Wg, P, 0, D_off, ps_off, tid);  // w = L^-1 Xy (the reference's first trsm, BridgeRegression.cpp:564)
+  STBL_MARK(1, 1);
   for (int j = tid; j < P; j += SV_T) { Stream s(L.key, gch, it_, ST_BETA_STB, (uint32_t)j); x[j] = fma(sig, s.norm(0), x[j]); }
   __syncthreads();
+  STBL_MARK(1, 2);
   stbl_backward(A, Wg, P, 0, D_off, ps_off, tid); // beta = L^-T (w + sig eps)  (:565, :570-574)
+  STBL_MARK(1, 3);
   double* beta = L.beta + (size_t)ch * P;
   const long long slot = stbl_slot(L);
   for (int j = tid; j < P; j += SV_T) {
