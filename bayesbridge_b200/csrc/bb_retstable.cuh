@@ -256,7 +256,9 @@ __device__ unsigned long long bb_lambda_stats[8];
 template <int NT>
 __device__ inline void lambda_stage_cta(const int tid, int P, const double* beta, double* lam_out, double tau, double alpha_half,
                                         const RngKey key, uint32_t gch, uint32_t t, RetConst* rc_s,
-                                        int* q_s, int qld, int* qn_s, uint32_t* kk_s, uint32_t& status) {
+                                        int* q_s, int qld, int* qn_s, uint32_t* kk_s, uint32_t& status, int j0 = 0) {
+  // j0: index of beta[0] / lam_out[0] among the chain's coefficients (a CTA may serve a slice of them): the Philox item of
+  // coefficient j is j0 + j, so the draws do not depend on how the coefficients are split over CTAs
   // `tid` = index of the thread among the NT threads that serve THIS chain (a CTA may hold several chains,
   // each with its own queues; the barriers are CTA-wide and the loop runs until every chain is done)
   int cur_q = 0, n_act = P;
@@ -306,7 +308,7 @@ __device__ inline void lambda_stage_cta(const int tid, int P, const double* beta
           rc.init(b * b / (tau * tau), A);   // h = beta_j^2 / tau^2 (BridgeRegression.cpp:509)
           if (rc_s && sub == 0) rc_s[j] = rc;
         }
-        Stream s(key, gch, t, ST_LAMBDA, (uint32_t)j);
+        Stream s(key, gch, t, ST_LAMBDA, (uint32_t)(j0 + j));
         code = retstable_round_at(A, rc, s, k0 + (uint32_t)lut_reach[sub], out);
       }
       BB_LAM_MARK(0);

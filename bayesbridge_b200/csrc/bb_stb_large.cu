@@ -1,5 +1,6 @@
 // bb_stb_large.cu -- host side of the large-P stable sweep (bb_stb_large.cuh): one Gibbs iteration =
 // scalar stage, build, blocked left-looking Cholesky (DMMA update / potrf / trsm per block column), solve.
+#include <algorithm>
 #include <cstdlib>
 #include "bb_stb_large.cuh"
 #include "bb_stb_wide.cuh"
@@ -7,16 +8,18 @@
 namespace bb {
 
 void stb_large_prepare(int P) {
-  const size_t smem_sc = ((size_t)P + 26) * sizeof(double) + ((size_t)3 * P + 2) * sizeof(int);
-  const size_t smem_sv = ((size_t)P + SL_NB * (SL_NB + 1) + 16 * SL_NB) * sizeof(double);
+  const size_t smem_sc = stbl_scalar_smem(P);
+  const size_t smem_sv = stbl_solve_smem(P);
   const size_t smem_sy = (size_t)2 * SL_NB * SL_LD * sizeof(double);
   const size_t smem_pf = stbl_potrf_smem();
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_potrf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pf));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_scalar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sc));
+  BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_lambda_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(stbl_lambda_smem(P), stbl_lambda_smem(std::min(P, SC_RC_MAXP)))));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));
 
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_trsm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
+  BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_colblock_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_update2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stbl_update2_smem()));
   BB_CUDA_CHECK(cudaFuncSetAttribute(wide_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));   // N <= P there
   if ((size_t)P * sizeof(double) > 48 * 1024) BB_CUDA_CHECK(cudaFuncSetAttribute(wide_draw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((size_t)P * sizeof(double))));
@@ -35,10 +38,46 @@ static int launch_update(double* A, int P, int kb, int nblk, int nch, cudaStream
   return 2;
 }
 
+// Blocked Cholesky of nch P x P systems (lower triangle of A, leading dimension P; the inverses of the diagonal blocks of the
+// factor go to W), left-looking.  Up to SL_FUSED_MAXBLK block columns: one kernel per block column (panel solve of the previous
+// one + update) and one for its diagonal block; beyond: update / potrf / trsm kernels with the 128 x 64 update tiles.
+constexpr int SL_FUSED_MAXBLK = 8;
+static int launch_factor(double* A, double* W, int P, int nch, uint32_t* status, const StblSrc& X, cudaStream_t st) {
+  const size_t smem_sy = (size_t)2 * SL_NB * SL_LD * sizeof(double);
+  const int nblk = (P + SL_NB - 1) / SL_NB;
+  int n = 0;
+  if (nblk <= SL_FUSED_MAXBLK) {
+    for (int kb = 0; kb < nblk; ++kb) {
+      if (kb > 0) { stbl_colblock_kernel<<<dim3(nblk - kb, nch), 256, smem_sy, st>>>(A, W, P, kb, X); ++n; }
+      stbl_potrf_kernel<<<nch, SL_T, stbl_potrf_smem(), st>>>(A, W, P, kb, status, X, 1); ++n;
+    }
+    return n;
+  }
+  for (int kb = 0; kb < nblk; ++kb) {   // bring block column kb up to date, factor its diagonal block, solve its panel
+    if (kb > 0) n += launch_update(A, P, kb, nblk, nch, st);
+    stbl_potrf_kernel<<<nch, SL_T, stbl_potrf_smem(), st>>>(A, W, P, kb, status, StblSrc{}, 0); ++n;
+    const int rem = nblk - kb - 1;
+    if (rem > 0) { stbl_trsm_kernel<<<dim3(rem, nch), 256, smem_sy, st>>>(A, W, P, kb); ++n; }
+  }
+  return n;
+}
+
+// CTAs per chain of the lambda stage.  Splitting a chain shortens its passes but evaluates more speculative rounds; measured at c5s
+// (64 chains per launch, four launches in flight) 1 / 2 / 4 CTAs per chain = 157 / 154 / 148 M draws/s: the stage is bound by the
+// FP64 work, so a chain is split only when the chains alone would leave most SMs idle.  Slices of at least 64 coefficients.
+static int stbl_lambda_nsplit(int P, int nch) {
+  static int sms = 0;
+  if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); if (sms <= 0) sms = 148; }
+  static const int env = std::getenv("BB_STBL_LSPLIT") ? std::atoi(std::getenv("BB_STBL_LSPLIT")) : 0;
+  int ns = env > 0 ? env : sms / (4 * nch);
+  ns = std::min(ns, std::max(1, P / 64));
+  return std::max(1, std::min(ns, 64));
+}
+
 int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
   const int P = L.m.P, nch = L.nchains;
-  const size_t smem_sc = ((size_t)P + 26) * sizeof(double) + ((size_t)3 * P + 2) * sizeof(int);
-  const size_t smem_sv = ((size_t)P + SL_NB * (SL_NB + 1) + 16 * SL_NB) * sizeof(double);
+  const size_t smem_sc = stbl_scalar_smem(P);
+  const size_t smem_sv = stbl_solve_smem(P);
   const size_t smem_sy = (size_t)2 * SL_NB * SL_LD * sizeof(double);
   const int nblk = (P + SL_NB - 1) / SL_NB;
   int n = 0;
@@ -48,6 +87,10 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
     stbl_quad_kernel<<<dim3(nstrips, (nch + 31) / 32), 256, 0, st>>>(L, nstrips); ++n;
   }
   stbl_scalar_kernel<<<nch, SL_T, smem_sc, st>>>(L); ++n;
+  if ((L.stages & 32) && !L.pre) {
+    const int nsplit = stbl_lambda_nsplit(P, nch);
+    stbl_lambda_kernel<<<dim3(nsplit, nch), SL_T, stbl_lambda_smem(stbl_lambda_slice(P, nsplit)), st>>>(L, nsplit); ++n;
+  }
   if (L.pre || !beta_stage) {
     if (do_alpha) { stbl_alpha_kernel<<<(nch + 7) / 8, 256, 0, st>>>(L); ++n; }
     return n;
@@ -58,22 +101,17 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
     const int N = L.m.N, nbn = (N + SL_NB - 1) / SL_NB, ntile = nbn * (nbn + 1) / 2;
     wide_draw_kernel<<<nch, 256, (size_t)P * sizeof(double), st>>>(L); ++n;
     wide_gram_kernel<<<dim3(ntile, nch), WG_T, 0, st>>>(L); ++n;
-    for (int kb = 0; kb < nbn; ++kb) {
-      if (kb > 0) n += launch_update(L.A, N, kb, nbn, nch, st);
-      stbl_potrf_kernel<<<nch, SL_T, stbl_potrf_smem(), st>>>(L.A, L.W, N, kb, L.status); ++n;
-      const int rem = nbn - kb - 1;
-      if (rem > 0) { stbl_trsm_kernel<<<dim3(rem, nch), 256, smem_sy, st>>>(L.A, L.W, N, kb); ++n; }
-    }
-    wide_solve_kernel<<<nch, SV_T, ((size_t)N + SL_NB * (SL_NB + 1) + 16 * SL_NB) * sizeof(double), st>>>(L); ++n;
+    n += launch_factor(L.A, L.W, N, nch, L.status, StblSrc{}, st);
+    wide_solve_kernel<<<nch, SV_T, stbl_solve_smem(N), st>>>(L); ++n;
     if (do_alpha) { stbl_alpha_kernel<<<(nch + 7) / 8, 256, 0, st>>>(L); ++n; }
     return n;
   }
-  stbl_build_kernel<<<dim3(64, nch), 256, 0, st>>>(L); ++n;
-  for (int kb = 0; kb < nblk; ++kb) {   // left-looking: bring block column kb up to date, factor its diagonal block, solve its panel
-    if (kb > 0) n += launch_update(L.A, P, kb, nblk, nch, st);
-    stbl_potrf_kernel<<<nch, SL_T, stbl_potrf_smem(), st>>>(L.A, L.W, P, kb, L.status); ++n;
-    const int rem = nblk - kb - 1;
-    if (rem > 0) { stbl_trsm_kernel<<<dim3(rem, nch), 256, smem_sy, st>>>(L.A, L.W, P, kb); ++n; }
+  if (nblk <= SL_FUSED_MAXBLK) {        // no build pass: the kernels read X'X and add the diagonal themselves
+    StblSrc X; X.src = L.m.XX; X.stride = 0; X.lam = L.lambda; X.sig2 = L.sig2; X.tau = L.tau;
+    n += launch_factor(L.A, L.W, P, nch, L.status, X, st);
+  } else {
+    stbl_build_kernel<<<dim3(64, nch), 256, 0, st>>>(L); ++n;
+    n += launch_factor(L.A, L.W, P, nch, L.status, StblSrc{}, st);
   }
   stbl_solve_kernel<<<nch, SV_T, smem_sv, st>>>(L); ++n;
 #ifdef BB_STBL_PHASES
@@ -82,8 +120,19 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
     if (++calls == 40) {
       cudaStreamSynchronize(st);
       long long ph[2][8]; cudaMemcpyFromSymbol(ph, bb_stbl_ph, sizeof(ph));
-      fprintf(stderr, "[stbl phases] scalar: sums %lld  tau/sig2 %lld  lambda %lld | solve: forward %lld  normals %lld  backward %lld\n",
-              ph[0][1] - ph[0][0], ph[0][2] - ph[0][1], ph[0][3] - ph[0][2], ph[1][1] - ph[1][0], ph[1][2] - ph[1][1], ph[1][3] - ph[1][2]);
+      fprintf(stderr, "[stbl phases] scalar: sums %lld  tau/sig2 %lld | lambda %lld | solve: forward %lld  normals %lld  backward %lld\n",
+              ph[0][1] - ph[0][0], ph[0][2] - ph[0][1], ph[0][4] - ph[0][3], ph[1][1] - ph[1][0], ph[1][2] - ph[1][1], ph[1][3] - ph[1][2]);
+#ifdef BB_PHASES
+      unsigned long long hc[16]; cudaMemcpyFromSymbol(hc, bb_phase_cyc, sizeof(hc));
+      fprintf(stderr, "[stbl lambda stage, CTA 0 thread 0, per pass] passes %llu; setup+round %.0f walk %.0f queue+barriers %.0f loop head %.0f\n", hc[12],
+              (double)hc[8] / hc[12], (double)hc[9] / hc[12], (double)hc[10] / hc[12], (double)hc[11] / hc[12]);
+#endif
+#ifdef BB_LAMBDA_STATS
+      unsigned long long q[8]; cudaMemcpyFromSymbol(q, bb_lambda_stats, sizeof(q));
+      const double in = (double)q[0], out = (double)q[1], acc = (double)q[2], ev = (double)q[3], ps = (double)q[4];
+      fprintf(stderr, "[stbl lambda stats] draws %.0f: sequential rounds per draw %.3f (inner %.3f, outer %.3f); evaluated per draw %.3f; passes per chain-iteration %.2f\n",
+              acc, (in + out + acc) / acc, in / acc, out / acc, ev / acc, ps / (acc / P));
+#endif
     }
   }
 #endif
@@ -107,7 +156,7 @@ int chol_lower_device(double* A, int P, double* Winv, uint32_t* status, cudaStre
   int n = 0;
   for (int kb = 0; kb < nblk; ++kb) {
     if (kb > 0) n += launch_update(A, P, kb, nblk, 1, st);
-    stbl_potrf_kernel<<<1, SL_T, stbl_potrf_smem(), st>>>(A, Winv, P, kb, status); ++n;
+    stbl_potrf_kernel<<<1, SL_T, stbl_potrf_smem(), st>>>(A, Winv, P, kb, status, StblSrc{}, 0); ++n;
     const int rem = nblk - kb - 1;
     if (rem > 0) { stbl_trsm_kernel<<<dim3(rem, 1), 256, smem_sy, st>>>(A, Winv, P, kb); ++n; }
   }

@@ -102,36 +102,40 @@ __device__ long long bb_stbl_ph[2][8];
 #define STBL_MARK(k, i) do { } while (0)
 #endif
 
-// ---- tau, sig2, lambda: one CTA per chain -------------------------------------------------
+// ---- tau, sig2: one CTA per chain -------------------------------------------------
+inline size_t stbl_scalar_smem(int P) { return ((size_t)P + 26) * sizeof(double); }
 __global__ void __launch_bounds__(SL_T) stbl_scalar_kernel(const StbLargeLaunch L) {
   extern __shared__ double smem[];
   const int P = L.m.P, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   double* dl_s = smem;                       // [P] beta - bc
   double* red = dl_s + P;                    // [24]
   double* sc = red + 24;                     // tau, sig2
-  int* q_s = reinterpret_cast<int*>(sc + 2); // [2][P]
-  int* qn_s = q_s + 2 * P;
-  uint32_t* kk_s = reinterpret_cast<uint32_t*>(qn_s + 2);
   const int ch = blockIdx.x; if (ch >= L.nchains) return;
   STBL_MARK(0, 0);
   const uint32_t gch = L.chain0 + (uint32_t)ch, t = stbl_iter(L);
   const double alpha = L.h.true_alpha > 0 ? L.h.true_alpha : L.alpha[ch];   // unknown alpha: chain state (stbl_alpha_kernel moves it)
   const bool know_tau = L.h.true_tau > 0, know_sig2 = L.h.true_sig2 > 0;
   const bool do_tau = ((L.stages & 1) || L.pre) && !know_tau, do_sig2 = (L.stages & 2) && !know_sig2 && !L.pre;
-  const bool do_lambda = (L.stages & 32) && !L.pre;
   uint32_t status = 0;
   const double* beta = L.beta + (size_t)ch * P;
   for (int j = tid; j < P; j += SL_T) dl_s[j] = beta[j] - __ldg(L.m.bc + j);
-  if (tid == 0) { sc[0] = know_tau ? L.h.true_tau : L.tau[ch]; sc[1] = know_sig2 ? L.h.true_sig2 : L.sig2[ch]; qn_s[0] = 0; qn_s[1] = 0; }
+  if (tid == 0) { sc[0] = know_tau ? L.h.true_tau : L.tau[ch]; sc[1] = know_sig2 ? L.h.true_sig2 : L.sig2[ch]; }
   __syncthreads();
   double pt = 0.0, pq = 0.0, pg = 0.0;
   for (int k = tid; k < P; k += SL_T) {
     pt += exp(alpha * log(fabs(beta[k])));
     if (do_sig2) {
-      if (L.Q == nullptr) {
-        double s = 0.0;   // (X'X delta)_k
-        for (int j = 0; j < P; ++j) s = fma(__ldg(L.m.XX + k + (size_t)j * P), dl_s[j], s);
-        pq = fma(dl_s[k], s, pq);
+      if (L.Q == nullptr) {   // (X'X delta)_k: four partial sums, 16 loads in flight (one dependent chain of P L2 loads took 20 us at P = 256)
+        const double* xk = L.m.XX + k;
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+        int j = 0;
+#pragma unroll 4
+        for (; j + 3 < P; j += 4) {
+          s0 = fma(__ldg(xk + (size_t)j * P), dl_s[j], s0); s1 = fma(__ldg(xk + (size_t)(j + 1) * P), dl_s[j + 1], s1);
+          s2 = fma(__ldg(xk + (size_t)(j + 2) * P), dl_s[j + 2], s2); s3 = fma(__ldg(xk + (size_t)(j + 3) * P), dl_s[j + 3], s3);
+        }
+        for (; j < P; ++j) s0 = fma(__ldg(xk + (size_t)j * P), dl_s[j], s0);
+        pq = fma(dl_s[k], (s0 + s1) + (s2 + s3), pq);
       }
       pg = fma(dl_s[k], __ldg(L.m.gc + k), pg);
     }
@@ -160,11 +164,40 @@ __global__ void __launch_bounds__(SL_T) stbl_scalar_kernel(const StbLargeLaunch 
   }
   __syncthreads();
   STBL_MARK(0, 2);
-  const double tau = sc[0];
   if (tid == 0) { L.tau[ch] = sc[0]; L.sig2[ch] = sc[1]; L.alpha[ch] = alpha; }
-  double* lam = L.lambda + (size_t)ch * P;
-  if (do_lambda) lambda_stage_cta<SL_T>(tid, P, beta, lam, tau, 0.5 * alpha, L.key, gch, t, nullptr, q_s, P, qn_s, kk_s, status);
+  status = __reduce_or_sync(0xffffffffu, status);
+  if (lane == 0 && status) atomicOr(L.status + ch, status);
+}
+
+// ---- lambda (BridgeRegression.cpp:506-510): nsplit CTAs per chain, each a contiguous slice of the coefficients ----
+// One round of the tilted-stable sampler is ~1700 FP64 instructions per evaluation: 256 evaluations in flight keep the FP64 pipe
+// of one SM busy for ~8000 cycles (-DBB_STBL_PHASES -DBB_PHASES), and with one CTA per chain the nine passes of a P = 256 chain
+// took 62 of the 81 us of the scalar kernel while most SMs idled.  Split over CTAs the slices of a chain run on different SMs, and
+// with fewer coefficients per CTA the speculative look-ahead (lambda_stage_cta: G offsets of a coefficient's stream evaluated at
+// once) starts at the first pass.  The draws do not depend on the split (Philox item = coefficient index).
+// The per-coefficient constants (RetConst) are kept in shared memory over the passes when the slice has at most SC_RC_MAXP entries.
+constexpr int SC_RC_MAXP = 1024;
+inline size_t stbl_lambda_smem(int nmax) {
+  return (nmax <= SC_RC_MAXP ? (size_t)nmax * sizeof(RetConst) : 0) + ((size_t)3 * nmax + 2) * sizeof(int);
+}
+__host__ __device__ inline int stbl_lambda_slice(int P, int nsplit) { return (P + nsplit - 1) / nsplit; }   // the longest slice
+__global__ void __launch_bounds__(SL_T) stbl_lambda_kernel(const StbLargeLaunch L, int nsplit) {
+  extern __shared__ double smem[];
+  const int P = L.m.P, tid = threadIdx.x, lane = tid & 31, ch = blockIdx.y, sp = blockIdx.x;
+  const int j0 = (int)((long long)P * sp / nsplit), n = (int)((long long)P * (sp + 1) / nsplit) - j0;
+  const int nmax = stbl_lambda_slice(P, nsplit);
+  RetConst* rc_s = nmax <= SC_RC_MAXP ? reinterpret_cast<RetConst*>(smem) : nullptr;
+  int* q_s = reinterpret_cast<int*>(reinterpret_cast<char*>(smem) + (rc_s ? (size_t)nmax * sizeof(RetConst) : 0));   // [2][nmax]
+  int* qn_s = q_s + 2 * nmax;
+  uint32_t* kk_s = reinterpret_cast<uint32_t*>(qn_s + 2);
+  if (tid == 0) { qn_s[0] = 0; qn_s[1] = 0; }
+  __syncthreads();
   STBL_MARK(0, 3);
+  uint32_t status = 0;
+  const double tau = L.tau[ch], alpha = L.alpha[ch];      // as left by stbl_scalar_kernel (known values included)
+  lambda_stage_cta<SL_T>(tid, n, L.beta + (size_t)ch * P + j0, L.lambda + (size_t)ch * P + j0, tau, 0.5 * alpha, L.key,
+                         L.chain0 + (uint32_t)ch, stbl_iter(L), rc_s, q_s, nmax, qn_s, kk_s, status, j0);
+  STBL_MARK(0, 4);
   status = __reduce_or_sync(0xffffffffu, status);
   if (lane == 0 && status) atomicOr(L.status + ch, status);
 }
@@ -244,7 +277,16 @@ __device__ long long bb_potrf_ph[8];
 // warp n & 7, slot n >> 3.  Block column s: publish the tiles (i,s) -> warp 0 factors the diagonal tile and inverts its factor
 // -> panel L(i,s) = T(i,s) W_s' by DMMA -> trailing T(i,j) -= L(i,s) L(j,s)' by DMMA: three barriers per block column.
 // Rows / columns beyond the matrix are padded with the identity.
-__global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, double* Wall, int P, int kb, uint32_t* status) {
+// Where the not-yet-factored entries of the system come from.  src == nullptr: A itself (built beforehand; stbl_build_kernel,
+// wide_gram_kernel, chol_lower_device).  Otherwise the entries are read from src (X'X, the same for every chain: stride 0) with
+// lam[ch][r] sig2[ch] / tau[ch]^2 added on the diagonal, the first time a tile is touched -- no build pass over P x P per chain.
+struct StblSrc {
+  const double* src = nullptr; size_t stride = 0;
+  const double *lam = nullptr, *sig2 = nullptr, *tau = nullptr;
+};
+// fuse_panel: the kernel also solves the FIRST tile of the panel below its block, L(kb+1,kb) = C(kb+1,kb) W_kb' (the tile every
+// CTA of the next block column needs), see stbl_colblock_kernel.
+__global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, double* Wall, int P, int kb, uint32_t* status, const StblSrc X, int fuse_panel) {
   extern __shared__ double smem[];
   double* S = smem;                        // [64][SP_LD] row-major: the factor L
   double* Wt = smem + SL_NB * SP_LD;       // [64][SP_LD] first the staged block (column-major), then W' : Wt[c][r] = W(r,c), W = L^-1
@@ -254,6 +296,10 @@ __global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, double* 
   const int ch = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   double* A = Aall + (size_t)ch * P * P;
   const int k0 = kb * SL_NB, nb = min(SL_NB, P - k0);
+  const bool from_src = X.src != nullptr && kb == 0;  // (later diagonal blocks have been written to A by stbl_colblock_kernel)
+  const double* D0 = from_src ? X.src + (size_t)ch * X.stride : A;
+  const bool dadd = from_src && X.lam != nullptr;
+  const double fdiag = dadd ? X.sig2[ch] / (X.tau[ch] * X.tau[ch]) : 0.0;
   POTRF_MARK(0);
   const int fr = lane >> 2, fc = 2 * (lane & 3);      // accumulator fragment: row fr, columns fc, fc + 1
   const int ar = lane >> 2, ak = lane & 3;            // A / B fragment: row ar, k = ak
@@ -267,8 +313,12 @@ __global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, double* 
     ti[sl] = i; tj[sl] = n - i * (i + 1) / 2;
     if (n >= 36) { ti[sl] = 0; tj[sl] = -1; }          // no tile
     const int row = 8 * ti[sl] + fr, col = 8 * max(tj[sl], 0) + fc;
-    c0[sl] = (row < nb && col < nb) ? A[(k0 + row) + (size_t)(k0 + col) * P] : (row == col ? 1.0 : 0.0);
-    c1[sl] = (row < nb && col + 1 < nb) ? A[(k0 + row) + (size_t)(k0 + col + 1) * P] : (row == col + 1 ? 1.0 : 0.0);
+    c0[sl] = (row < nb && col < nb) ? D0[(k0 + row) + (size_t)(k0 + col) * P] : (row == col ? 1.0 : 0.0);
+    c1[sl] = (row < nb && col + 1 < nb) ? D0[(k0 + row) + (size_t)(k0 + col + 1) * P] : (row == col + 1 ? 1.0 : 0.0);
+    if (dadd && row < nb) {     // block column 0 straight from X'X: + lambda sig2 / tau^2 on the diagonal (BridgeRegression.cpp:554-556)
+      if (row == col) c0[sl] += X.lam[(size_t)ch * P + k0 + row] * fdiag;
+      if (row == col + 1) c1[sl] += X.lam[(size_t)ch * P + k0 + row] * fdiag;
+    }
   }
   POTRF_MARK(1);
   bool bad = false;
@@ -363,6 +413,32 @@ __global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, double* 
     W[e] = (r < nb && c < nb) ? Wt[c * SP_LD + r] : 0.0;
   }
   POTRF_MARK(6);
+  if (fuse_panel && k0 + SL_NB < P) {
+    // L(kb+1,kb) = C(kb+1,kb) W_kb'  (here nb = 64).  C staged k-major in S (the factor has been stored), warp w = rows 8w..8w+7.
+    const int i0 = k0 + SL_NB, nb2 = min(SL_NB, P - i0);
+    __syncthreads();
+    for (int e = tid; e < SL_NB * SL_NB; e += SL_T) {
+      const int r = e & (SL_NB - 1), k = e >> 6;
+      S[k * SP_LD + r] = r < nb2 ? D0[(i0 + r) + (size_t)(k0 + k) * P] : 0.0;
+    }
+    __syncthreads();
+    double acc[8][2];
+#pragma unroll
+    for (int t = 0; t < 8; ++t) { acc[t][0] = 0.0; acc[t][1] = 0.0; }
+#pragma unroll 4
+    for (int kk = 0; kk < SL_NB; kk += 4) {
+      const double a = S[(kk + ak) * SP_LD + 8 * warp + ar];
+#pragma unroll
+      for (int t = 0; t < 8; ++t) dmma_m8n8k4(acc[t][0], acc[t][1], a, Wt[(kk + ak) * SP_LD + 8 * t + ar]);   // B(k,n) = W(n,k)
+    }
+    if (8 * warp + fr < nb2) {
+#pragma unroll
+      for (int t = 0; t < 8; ++t) {
+        A[(i0 + 8 * warp + fr) + (size_t)(k0 + 8 * t + fc) * P] = acc[t][0];
+        A[(i0 + 8 * warp + fr) + (size_t)(k0 + 8 * t + fc + 1) * P] = acc[t][1];
+      }
+    }
+  }
 }
 
 // ---- panel: rows below the diagonal block,  L(i,kb) = C(i,kb) W_kb'  on the FP64 tensor cores ----
@@ -453,6 +529,115 @@ __global__ void __launch_bounds__(256, 2) stbl_update_kernel(double* Aall, int P
     }
 }
 
+// ---- block column jb >= 1 in ONE kernel (P <= 512): the panel solve of block column jb - 1 and the left-looking update ----
+//   CTA = row tile ti >= jb of one chain:
+//     ti > jb :  L(ti,jb-1) = C(ti,jb-1) W_{jb-1}'            (its own tile of the previous panel, written back as final)
+//     C(ti,jb) = S(ti,jb) - sum_{k<jb} L(ti,k) L(jb,k)'       (the last term with the tile just solved, from shared memory)
+//   L(jb,jb-1), which every CTA needs as the right-hand operand, was solved by stbl_potrf_kernel(jb-1, fuse_panel).
+// Against stbl_update_kernel + stbl_trsm_kernel (+ stbl_build_kernel): the same arithmetic, one launch per block column
+// instead of two, one pass less over the matrix -- at P = 256 the 64 x 64-tile kernels are bound by their latencies
+// (17 us for one to three tile products of 2 us), so the SM time goes with the number of CTA launches.
+__global__ void __launch_bounds__(256) stbl_colblock_kernel(double* Aall, const double* Wall, int P, int jb, const StblSrc X) {
+  extern __shared__ double smem[];
+  double* As = smem;
+  double* Bs = smem + SL_NB * SL_LD;
+  const int ch = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double* A = Aall + (size_t)ch * P * P;
+  const double* Sm = X.src ? X.src + (size_t)ch * X.stride : A;
+  const int ti = jb + blockIdx.x;
+  const int i0 = ti * SL_NB, j0 = jb * SL_NB, kc = jb - 1, c0 = kc * SL_NB;
+  double acc[2][4][2];
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int t = 0; t < 4; ++t) { acc[a][t][0] = 0.0; acc[a][t][1] = 0.0; }
+  const int r = tid & (SL_NB - 1), kq = tid >> 6;      // thread -> 16 elements of a 64 x 64 tile: row r, columns kq + 4 q
+  const bool ra = i0 + r < P, rb = j0 + r < P;
+  const int wr = (warp & 3) * 16 + (lane >> 2), wc = (warp >> 2) * 32 + 2 * (lane & 3);   // fragment: rows wr + 8 a, columns wc + 8 t + {0,1}
+  double pa[16], pb[16];
+  // my tile of the previous panel (unsolved) and W_{jb-1}' go first: the solve heads the chain
+  if (ti > jb) {
+    const double* Cs = (X.src && kc == 0) ? Sm : A;
+    const double* W = Wall + ((size_t)ch * ((P + SL_NB - 1) / SL_NB) + kc) * SL_NB * SL_NB;
+#pragma unroll
+    for (int q = 0; q < 16; ++q) {
+      pa[q] = ra ? Cs[(i0 + r) + (size_t)(c0 + kq + 4 * q) * P] : 0.0;
+      pb[q] = W[r + (kq + 4 * q) * SL_NB];             // B(k, c) = W(c, k)
+    }
+#pragma unroll
+    for (int q = 0; q < 16; ++q) { As[(kq + 4 * q) * SL_LD + r] = pa[q]; Bs[(kq + 4 * q) * SL_LD + r] = pb[q]; }
+    __syncthreads();
+  }
+  const double* pa_src = A + (i0 + r) + (size_t)kq * P;
+  const double* pb_src = A + (j0 + r) + (size_t)kq * P;
+  auto fetch = [&](int kb) {
+    const size_t off = (size_t)kb * SL_NB * P;
+#pragma unroll
+    for (int q = 0; q < 16; ++q) {
+      pa[q] = ra ? pa_src[off + (size_t)(4 * q) * P] : 0.0;
+      pb[q] = rb ? pb_src[off + (size_t)(4 * q) * P] : 0.0;
+    }
+  };
+  // block column kc = jb - 1 first: right-hand tile L(jb,kc) from memory, left-hand tile = the one solved here (ti > jb) or the same tile
+  fetch(kc);                                           // (for ti > jb only pb is used: in flight during the solve)
+  if (ti > jb) {
+    double dn[2][4][2];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int t = 0; t < 4; ++t) { dn[a][t][0] = 0.0; dn[a][t][1] = 0.0; }
+    tile_mma_16x32(As, Bs, dn, lane, warp);            // L(ti,kc) = C(ti,kc) W'
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const int rr = i0 + wr + 8 * a, c = c0 + wc + 8 * t;
+        if (rr < P) { A[rr + (size_t)c * P] = dn[a][t][0]; A[rr + (size_t)(c + 1) * P] = dn[a][t][1]; }
+      }
+    __syncthreads();
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        As[(wc + 8 * t) * SL_LD + wr + 8 * a] = dn[a][t][0]; As[(wc + 8 * t + 1) * SL_LD + wr + 8 * a] = dn[a][t][1];
+      }
+  } else {
+#pragma unroll
+    for (int q = 0; q < 16; ++q) As[(kq + 4 * q) * SL_LD + r] = pb[q];
+  }
+#pragma unroll
+  for (int q = 0; q < 16; ++q) Bs[(kq + 4 * q) * SL_LD + r] = pb[q];
+  __syncthreads();
+  if (kc > 0) fetch(0);
+  tile_mma_16x32(As, Bs, acc, lane, warp);
+  __syncthreads();
+  // the finished block columns k < jb - 1
+  for (int kb = 0; kb < kc; ++kb) {
+#pragma unroll
+    for (int q = 0; q < 16; ++q) { As[(kq + 4 * q) * SL_LD + r] = pa[q]; Bs[(kq + 4 * q) * SL_LD + r] = pb[q]; }
+    __syncthreads();
+    if (kb + 1 < kc) fetch(kb + 1);
+    tile_mma_16x32(As, Bs, acc, lane, warp);
+    __syncthreads();
+  }
+  const double fdiag = (X.lam && ti == jb) ? X.sig2[ch] / (X.tau[ch] * X.tau[ch]) : 0.0;
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const int rr = i0 + wr + 8 * a, c = j0 + wc + 8 * t;
+      if (rr < P) {
+#pragma unroll
+        for (int q = 0; q < 2; ++q)
+          if (c + q < P) {
+            double v = Sm[rr + (size_t)(c + q) * P];
+            if (X.lam && rr == c + q) v += X.lam[(size_t)ch * P + rr] * fdiag;
+            A[rr + (size_t)(c + q) * P] = v - acc[a][t][q];
+          }
+      }
+    }
+}
+
 // ---- the same update with a 128 x 64 CTA tile: every B fragment (the L(jb,k) panel, shared by all row tiles) feeds TWO
 // DMMAs, so the shared-memory loads per tensor instruction drop from 9/8 to 10/16 -- the 64 x 64 form is bound by them.
 // Warp w owns rows 16 w .. 16 w + 15 of the tile.  Launched for the row-tile PAIRS below the diagonal tile; the diagonal
@@ -522,22 +707,37 @@ __global__ void __launch_bounds__(256, 2) stbl_update2_kernel(double* Aall, int 
 constexpr int SV_T = 1024;   // threads of the solve kernels: one CTA streams a chain's factor twice, it needs the loads in flight
 // (x, D, ps are OFFSETS into the dynamic shared memory: handed over as generic pointers the compiler loses the address space
 //  and every access becomes a generic load -- the solve kernel ran 2x slower, 51 -> 111 us at P = 256)
-__device__ __forceinline__ void stbl_stage_w(const double* Wg, int kb, int D_off, int tid) {
+// W of the NEXT diagonal block travels through registers (4 values per thread): the loads are issued before the work on the
+// current block and stored to shared memory after it, so that their L2 latency is off the chain of dependent blocks.
+struct StblWRegs { double v[4]; };
+__device__ __forceinline__ void stbl_fetch_w(const double* Wg, int kb, int tid, StblWRegs& w) {
+  const double* W = Wg + (size_t)kb * SL_NB * SL_NB;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) w.v[q] = W[tid + q * SV_T];
+}
+__device__ __forceinline__ void stbl_store_w(int D_off, int tid, const StblWRegs& w) {
   extern __shared__ double smem[];
   double* D = smem + D_off;
-  const double* W = Wg + (size_t)kb * SL_NB * SL_NB;
-  for (int e = tid; e < SL_NB * SL_NB; e += SV_T) D[(e & (SL_NB - 1)) * (SL_NB + 1) + (e >> 6)] = W[e];   // W[e] = W(e % 64, e / 64)
+#pragma unroll
+  for (int q = 0; q < 4; ++q) { const int e = tid + q * SV_T; D[(e & (SL_NB - 1)) * (SL_NB + 1) + (e >> 6)] = w.v[q]; }   // W[e] = W(e % 64, e / 64)
 }
+constexpr int SV_SPLIT_MAXP = 4096;   // up to here the four partial sums of the rows below a block fit in shared memory
+inline size_t stbl_solve_smem(int P) { return ((size_t)P + SL_NB * (SL_NB + 1) + 16 * SL_NB + (P <= SV_SPLIT_MAXP ? 4 * (size_t)P : 0)) * sizeof(double); }
+// Shared-memory layout of the solves (doubles): x [P] | D [64][65] | ps [16][64] | part [4][P].
 // The diagonal blocks are applied as products with their inverses (rows / columns beyond the matrix are zero in W): a 64-term
 // dot product per unknown, all unknowns of the block at once, instead of 64 dependent substitution steps with a division each.
 __device__ __forceinline__ void stbl_forward(const double* A, const double* Wg, int P, int x_off, int D_off, int ps_off, int tid) {
   extern __shared__ double smem[];
-  double* x = smem + x_off; double* D = smem + D_off; double* ps = smem + ps_off;
+  double* x = smem + x_off; double* D = smem + D_off; double* ps = smem + ps_off; double* part = ps + 16 * SL_NB;
   const int vr = tid & (SL_NB - 1), vp = tid >> 6;     // matrix-vector product: index vr, 16 parts of 4 terms (SV_T = 1024)
+  const int rs = tid & 255, kp = tid >> 8;             // rows below the block: row slot rs, columns 16 kp .. 16 kp + 15
+  StblWRegs wn;
+  stbl_fetch_w(Wg, 0, tid, wn);
   // forward: L w = Xy, column-oriented
   for (int k0 = 0; k0 < P; k0 += SL_NB) {
     const int nb = min(SL_NB, P - k0);
-    stbl_stage_w(Wg, k0 / SL_NB, D_off, tid);
+    stbl_store_w(D_off, tid, wn);
+    if (k0 + SL_NB < P) stbl_fetch_w(Wg, k0 / SL_NB + 1, tid, wn);
     __syncthreads();
     {   // w_blk = W x_blk
       double s = 0.0;
@@ -553,12 +753,31 @@ __device__ __forceinline__ void stbl_forward(const double* A, const double* Wg, 
       x[k0 + tid] = s;
     }
     __syncthreads();
-    for (int r = k0 + nb + tid; r < P; r += SV_T) {   // rows below: coalesced along r
-      double s = x[r];
+    // rows below: x_r -= sum_k L(r,k) w_k, the 64 columns split over four thread groups (16 loads in flight per thread instead of
+    // a chain of 64: with 192 rows at P = 256 only 192 threads worked and the chain of L2 latencies was 5000 cycles per block)
+    if (P > SV_SPLIT_MAXP) {   // no room for the partial sums: one thread per row, the 64 columns in sequence
+      for (int r = k0 + nb + tid; r < P; r += SV_T) {
+        double s = x[r];
 #pragma unroll 8
-      for (int k = k0; k < k0 + nb; ++k) s = fma(-A[r + (size_t)k * P], x[k], s);
-      x[r] = s;
+        for (int k = k0; k < k0 + nb; ++k) s = fma(-A[r + (size_t)k * P], x[k], s);
+        x[r] = s;
+      }
+      __syncthreads();
+      continue;
     }
+    for (int r = k0 + nb + rs; r < P; r += 256) {
+      const double* ar = A + r + (size_t)(k0 + 16 * kp) * P;
+      double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+      for (int q = 0; q < 16; q += 2) {
+        const int c = 16 * kp + q;
+        const double a0 = c < nb ? ar[(size_t)q * P] : 0.0, a1 = c + 1 < nb ? ar[(size_t)(q + 1) * P] : 0.0;
+        s0 = fma(a0, x[k0 + min(c, nb - 1)], s0); s1 = fma(a1, x[k0 + min(c + 1, nb - 1)], s1);
+      }
+      part[kp * P + r] = s0 + s1;
+    }
+    __syncthreads();
+    for (int r = k0 + nb + tid; r < P; r += SV_T) x[r] -= (part[r] + part[P + r]) + (part[2 * P + r] + part[3 * P + r]);
     __syncthreads();
   }
 }
@@ -569,9 +788,12 @@ __device__ __forceinline__ void stbl_backward(const double* A, const double* Wg,
   const int nblk = (P + SL_NB - 1) / SL_NB;
   // backward: L' b = x over the stored lower triangle: column k of L is contiguous, one warp per column, lanes along r
   double* pk = ps + 15 * SL_NB;     // [64] column sums (the last part of ps is free until the product below)
+  StblWRegs wn;
+  stbl_fetch_w(Wg, nblk - 1, tid, wn);
   for (int kbk = nblk - 1; kbk >= 0; --kbk) {
     const int k0 = kbk * SL_NB, nb = min(SL_NB, P - k0);
-    stbl_stage_w(Wg, kbk, D_off, tid);
+    stbl_store_w(D_off, tid, wn);
+    if (kbk > 0) stbl_fetch_w(Wg, kbk - 1, tid, wn);
     for (int kk = warp; kk < nb; kk += SV_T / 32) {
       const double* col = A + (size_t)(k0 + kk) * P;
       double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;

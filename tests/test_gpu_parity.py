@@ -102,7 +102,8 @@ def test_tri_conditionals(port, N, P, alpha, nchains):
 
 
 @pytest.mark.parametrize("N,P,alpha,nchains", [(60, 8, 0.5, 5), (442, 64, 0.5, 4), (200, 50, 0.25, 3), (300, 100, 0.9, 2),
-                                               (400, 128, 0.5, 2), (300, 150, 0.5, 3), (120, 200, 0.25, 2)])
+                                               (400, 128, 0.5, 2), (300, 150, 0.5, 3), (120, 200, 0.25, 2),
+                                               (700, 321, 0.5, 2), (800, 512, 0.5, 2), (700, 530, 0.9, 2)])
 def test_stb_conditionals(port, N, P, alpha, nchains):
     import bayesbridge_b200 as bb
     from bayesbridge_b200._lib import ST_BETA, ST_LAMBDA, ST_SIG2, ST_TAU
