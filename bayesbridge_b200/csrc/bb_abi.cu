@@ -267,26 +267,26 @@ struct bb_chains {
   double *o_sig2 = nullptr, *o_tau = nullptr, *o_alpha = nullptr;
   // large-P stable path: one Gibbs iteration of a sub-batch (about 50 small launches at P = 256) captured once as a CUDA graph
   // and replayed; gkey = the frozen launch parameters the graph was captured with, ctl = [sub-batch][2] iteration / slot offsets
-  cudaGraphExec_t gx[4] = {nullptr, nullptr, nullptr, nullptr};
-  std::vector<char> gkey[4];
-  int glaunches[4] = {0, 0, 0, 0};
+  cudaGraphExec_t gx[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  std::vector<char> gkey[8];
+  int glaunches[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   long long* ctl = nullptr;
-  cudaStream_t stream = nullptr, stream2 = nullptr, xs[3] = {nullptr, nullptr, nullptr};   // xs: the other sub-batches of the large-P stable path
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr, ev_join = nullptr, xj[3] = {nullptr, nullptr, nullptr};
+  cudaStream_t stream = nullptr, stream2 = nullptr, xs[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // xs: the other sub-batches of the large-P stable path
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr, ev_join = nullptr, xj[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 
   void free_draws() { dfree(o_beta); dfree(o_u); dfree(o_omega); dfree(o_shape); dfree(o_lambda); dfree(o_sig2); dfree(o_tau); dfree(o_alpha); nslots = 0; out_mask = 0; }
   ~bb_chains() {
     cudaSetDevice(device);
     dfree(beta); dfree(u); dfree(aux); dfree(shape); dfree(z); dfree(sig2); dfree(tau); dfree(alpha); dfree(status); dfree(A); dfree(W); dfree(Q); dfree(U); dfree(R); dfree(rs_state); dfree(rs_range); dfree(rs_hist);
     free_draws();
-    for (int i = 0; i < 4; ++i) if (gx[i]) cudaGraphExecDestroy(gx[i]);
+    for (int i = 0; i < 8; ++i) if (gx[i]) cudaGraphExecDestroy(gx[i]);
     dfree(ctl);
     if (ev0) cudaEventDestroy(ev0);
     if (ev1) cudaEventDestroy(ev1);
     if (ev_fork) cudaEventDestroy(ev_fork);
     if (ev_join) cudaEventDestroy(ev_join);
     if (stream2) cudaStreamDestroy(stream2);
-    for (int i = 0; i < 3; ++i) { if (xj[i]) cudaEventDestroy(xj[i]); if (xs[i]) cudaStreamDestroy(xs[i]); }
+    for (int i = 0; i < 7; ++i) { if (xj[i]) cudaEventDestroy(xj[i]); if (xs[i]) cudaStreamDestroy(xs[i]); }
     if (stream) cudaStreamDestroy(stream);
   }
 };
@@ -411,14 +411,14 @@ void chains_run(bb_chains* c, const bb_hyper* hh, unsigned iter0, int niter, int
     // are independent chains, so they only meet again at the end of the call.  BB_STBL_SPLIT overrides the count (1..4).
     static const int split_env = std::getenv("BB_STBL_SPLIT") ? std::atoi(std::getenv("BB_STBL_SPLIT")) : 0;
     int nsub = c->nchains >= 64 ? 4 : (c->nchains >= 16 ? 2 : 1);   // measured: c4 (128 chains) 9.2 -> 9.4 M, c5s (256 chains) 68.6 -> 71.5 M draws/s from 2 to 4
-    if (split_env >= 1 && split_env <= 4) nsub = std::min(split_env, c->nchains);
+    if (split_env >= 1 && split_env <= 8) nsub = std::min(split_env, c->nchains);
     if (nsub > 1 && !c->ev_fork) BB_CUDA_CHECK(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     for (int i = 0; i + 1 < nsub; ++i)
       if (!c->xs[i]) {
         BB_CUDA_CHECK(cudaStreamCreateWithFlags(&c->xs[i], cudaStreamNonBlocking));
         BB_CUDA_CHECK(cudaEventCreateWithFlags(&c->xj[i], cudaEventDisableTiming));
       }
-    cudaStream_t sts[4] = {st, c->xs[0], c->xs[1], c->xs[2]};
+    cudaStream_t sts[8] = {st, c->xs[0], c->xs[1], c->xs[2], c->xs[3], c->xs[4], c->xs[5], c->xs[6]};
     if (nsub > 1) {
       BB_CUDA_CHECK(cudaEventRecord(c->ev_fork, st));
       for (int i = 1; i < nsub; ++i) BB_CUDA_CHECK(cudaStreamWaitEvent(sts[i], c->ev_fork, 0));
@@ -454,7 +454,7 @@ void chains_run(bb_chains* c, const bb_hyper* hh, unsigned iter0, int niter, int
     const bool use_graph = !graph_off && niter >= 4 && (thin == 1 || thin == 0 || c->nslots == 0);
     int it_first = -pre_tau;
     if (use_graph) {
-      if (!c->ctl) c->ctl = dalloc<long long>(8);
+      if (!c->ctl) c->ctl = dalloc<long long>(16);
       for (int it = it_first; it < 0; ++it) {          // the tau pre-draw: plain launches
         L.pre = true; L.iter = iter0; L.slot = -1;
         for (int h = 0; h < nsub; ++h) { bb::StbLargeLaunch H = sub(h); launched(bb::launch_stb_large_iter(H, (stages & BB_ST_BETA) != 0, sts[h])); }

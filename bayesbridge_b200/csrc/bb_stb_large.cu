@@ -15,13 +15,15 @@ void stb_large_prepare(int P) {
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_potrf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pf));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_scalar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sc));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_lambda_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(stbl_lambda_smem(P), stbl_lambda_smem(std::min(P, SC_RC_MAXP)))));
-  BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));
+  BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_solve_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));
+  BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_solve_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));
 
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_trsm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_colblock_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_update2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stbl_update2_smem()));
-  BB_CUDA_CHECK(cudaFuncSetAttribute(wide_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));   // N <= P there
+  BB_CUDA_CHECK(cudaFuncSetAttribute(wide_solve_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));
+  BB_CUDA_CHECK(cudaFuncSetAttribute(wide_solve_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));   // N <= P there
   if ((size_t)P * sizeof(double) > 48 * 1024) BB_CUDA_CHECK(cudaFuncSetAttribute(wide_draw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((size_t)P * sizeof(double))));
 }
 
@@ -39,9 +41,12 @@ static int launch_update(double* A, int P, int kb, int nblk, int nch, cudaStream
 }
 
 // Blocked Cholesky of nch P x P systems (lower triangle of A, leading dimension P; the inverses of the diagonal blocks of the
-// factor go to W), left-looking.  Up to SL_FUSED_MAXBLK block columns: one kernel per block column (panel solve of the previous
-// one + update) and one for its diagonal block; beyond: update / potrf / trsm kernels with the 128 x 64 update tiles.
-constexpr int SL_FUSED_MAXBLK = 8;
+// factor go to W), left-looking: one kernel per block column (panel solve of the previous one + update, stbl_colblock_kernel)
+// and one for its diagonal block.  Round 2: measured against the round-1 sequence (update / potrf / trsm kernels per block
+// column after a build pass) c5s 143 -> 177 M draws/s and c4 (P = 2000, 32 block columns) 12.1 -> 15.9 M = 60 % of the DGEMM
+// peak over the whole iteration.  The round-1 sequence stays reachable for comparison: BB_STBL_FUSED_MAXBLK=<n> uses it for
+// systems of more than n block columns (0: always).
+static const int SL_FUSED_MAXBLK = std::getenv("BB_STBL_FUSED_MAXBLK") ? std::atoi(std::getenv("BB_STBL_FUSED_MAXBLK")) : (1 << 20);
 static int launch_factor(double* A, double* W, int P, int nch, uint32_t* status, const StblSrc& X, cudaStream_t st) {
   const size_t smem_sy = (size_t)2 * SL_NB * SL_LD * sizeof(double);
   const int nblk = (P + SL_NB - 1) / SL_NB;
@@ -102,7 +107,9 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
     wide_draw_kernel<<<nch, 256, (size_t)P * sizeof(double), st>>>(L); ++n;
     wide_gram_kernel<<<dim3(ntile, nch), WG_T, 0, st>>>(L); ++n;
     n += launch_factor(L.A, L.W, N, nch, L.status, StblSrc{}, st);
-    wide_solve_kernel<<<nch, SV_T, stbl_solve_smem(N), st>>>(L); ++n;
+    if (N <= SV_SMALL_P) wide_solve_kernel<512><<<nch, 512, stbl_solve_smem(N), st>>>(L);
+    else wide_solve_kernel<1024><<<nch, 1024, stbl_solve_smem(N), st>>>(L);
+    ++n;
     if (do_alpha) { stbl_alpha_kernel<<<(nch + 7) / 8, 256, 0, st>>>(L); ++n; }
     return n;
   }
@@ -113,7 +120,9 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
     stbl_build_kernel<<<dim3(64, nch), 256, 0, st>>>(L); ++n;
     n += launch_factor(L.A, L.W, P, nch, L.status, StblSrc{}, st);
   }
-  stbl_solve_kernel<<<nch, SV_T, smem_sv, st>>>(L); ++n;
+  if (P <= SV_SMALL_P) stbl_solve_kernel<512><<<nch, 512, smem_sv, st>>>(L);
+  else stbl_solve_kernel<1024><<<nch, 1024, smem_sv, st>>>(L);
+  ++n;
 #ifdef BB_STBL_PHASES
   {
     static int calls = 0;
@@ -146,20 +155,12 @@ int stb_large_advance(long long* ctl, int stored, cudaStream_t st) {
 }
 
 // Cholesky of ONE P x P matrix with the same kernels (a batch of one chain): on return the lower triangle of A
-// holds L (A = L L'), the strict upper triangle still holds the input.  Winv: 64 x 64 scratch, status: one word,
+// holds L (A = L L'); the rest of A is scratch (the callers zero it).  status: one word,
 // ST_CHOL_FAIL is set when a pivot is not positive.  Used by the Cholesky-preconditioned SVD of the constructor.
 // Winv: ceil(P / 64) x 64 x 64 scratch (the inverses of all diagonal blocks of the factor are kept)
 int chol_lower_device(double* A, int P, double* Winv, uint32_t* status, cudaStream_t st) {
   stb_large_prepare(P);
-  const size_t smem_sy = (size_t)2 * SL_NB * SL_LD * sizeof(double);
-  const int nblk = (P + SL_NB - 1) / SL_NB;
-  int n = 0;
-  for (int kb = 0; kb < nblk; ++kb) {
-    if (kb > 0) n += launch_update(A, P, kb, nblk, 1, st);
-    stbl_potrf_kernel<<<1, SL_T, stbl_potrf_smem(), st>>>(A, Winv, P, kb, status, StblSrc{}, 0); ++n;
-    const int rem = nblk - kb - 1;
-    if (rem > 0) { stbl_trsm_kernel<<<dim3(rem, 1), 256, smem_sy, st>>>(A, Winv, P, kb); ++n; }
-  }
+  const int n = launch_factor(A, Winv, P, 1, status, StblSrc{}, st);
   BB_CUDA_CHECK(cudaGetLastError());
   return n;
 }

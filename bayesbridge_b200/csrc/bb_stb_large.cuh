@@ -268,7 +268,7 @@ __device__ __forceinline__ bool chol8_factor_inverse(double (&a)[8][8], double* 
 }
 
 #ifdef BB_POTRF_PHASES
-__device__ long long bb_potrf_ph[8];
+__device__ long long bb_potrf_ph[12];
 #define POTRF_MARK(i) do { __syncthreads(); if (threadIdx.x == 0 && blockIdx.x == 0) bb_potrf_ph[i] = clock64(); } while (0)
 #else
 #define POTRF_MARK(i) do { } while (0)
@@ -286,7 +286,10 @@ struct StblSrc {
 };
 // fuse_panel: the kernel also solves the FIRST tile of the panel below its block, L(kb+1,kb) = C(kb+1,kb) W_kb' (the tile every
 // CTA of the next block column needs), see stbl_colblock_kernel.
-__global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, double* Wall, int P, int kb, uint32_t* status, const StblSrc X, int fuse_panel) {
+#ifndef BB_POTRF_MINB
+#define BB_POTRF_MINB 1
+#endif
+__global__ void __launch_bounds__(SL_T, BB_POTRF_MINB) stbl_potrf_kernel(double* Aall, double* Wall, int P, int kb, uint32_t* status, const StblSrc X, int fuse_panel) {
   extern __shared__ double smem[];
   double* S = smem;                        // [64][SP_LD] row-major: the factor L
   double* Wt = smem + SL_NB * SP_LD;       // [64][SP_LD] first the staged block (column-major), then W' : Wt[c][r] = W(r,c), W = L^-1
@@ -364,6 +367,16 @@ __global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, double* 
       }
   }
   if (bad && lane == 0) atomicOr(status + ch, (uint32_t)ST_CHOL_FAIL);
+  // the tile of the fused panel solve is fetched now: its L2 latency (6000 cycles when loaded where it is used) hides behind
+  // the inverse stage.  Thread -> row r = tid & 63, columns (tid >> 6) + 4 q.
+  const bool do_panel = fuse_panel && k0 + SL_NB < P;
+  double pc[16];
+  if (do_panel) {
+    const int i0 = k0 + SL_NB, r = tid & (SL_NB - 1);
+    const bool rv = i0 + r < P;
+#pragma unroll
+    for (int q = 0; q < 16; ++q) pc[q] = rv ? D0[(i0 + r) + (size_t)(k0 + (tid >> 6) + 4 * q) * P] : 0.0;
+  }
   POTRF_MARK(2);
   for (int e = tid; e < SL_NB * SL_NB; e += SL_T) {
     const int r = e & (SL_NB - 1), c = e >> 6;
@@ -413,15 +426,14 @@ __global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, double* 
     W[e] = (r < nb && c < nb) ? Wt[c * SP_LD + r] : 0.0;
   }
   POTRF_MARK(6);
-  if (fuse_panel && k0 + SL_NB < P) {
+  if (do_panel) {
     // L(kb+1,kb) = C(kb+1,kb) W_kb'  (here nb = 64).  C staged k-major in S (the factor has been stored), warp w = rows 8w..8w+7.
     const int i0 = k0 + SL_NB, nb2 = min(SL_NB, P - i0);
     __syncthreads();
-    for (int e = tid; e < SL_NB * SL_NB; e += SL_T) {
-      const int r = e & (SL_NB - 1), k = e >> 6;
-      S[k * SP_LD + r] = r < nb2 ? D0[(i0 + r) + (size_t)(k0 + k) * P] : 0.0;
-    }
+#pragma unroll
+    for (int q = 0; q < 16; ++q) S[((tid >> 6) + 4 * q) * SP_LD + (tid & (SL_NB - 1))] = pc[q];
     __syncthreads();
+    POTRF_MARK(8);
     double acc[8][2];
 #pragma unroll
     for (int t = 0; t < 8; ++t) { acc[t][0] = 0.0; acc[t][1] = 0.0; }
@@ -431,6 +443,7 @@ __global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, double* 
 #pragma unroll
       for (int t = 0; t < 8; ++t) dmma_m8n8k4(acc[t][0], acc[t][1], a, Wt[(kk + ak) * SP_LD + 8 * t + ar]);   // B(k,n) = W(n,k)
     }
+    POTRF_MARK(9);
     if (8 * warp + fr < nb2) {
 #pragma unroll
       for (int t = 0; t < 8; ++t) {
@@ -439,6 +452,7 @@ __global__ void __launch_bounds__(SL_T) stbl_potrf_kernel(double* Aall, double* 
       }
     }
   }
+  POTRF_MARK(7);
 }
 
 // ---- panel: rows below the diagonal block,  L(i,kb) = C(i,kb) W_kb'  on the FP64 tensor cores ----
@@ -704,59 +718,67 @@ __global__ void __launch_bounds__(256, 2) stbl_update2_kernel(double* Aall, int 
 
 // ---- the two blocked substitutions with a factor left by stbl_potrf / stbl_trsm (lower triangle of A, leading dimension P;
 //      Wg = inverses of its diagonal blocks): x <- L^-1 x and x <- L^-T x, x in shared memory, one CTA of SV_T threads ----
-constexpr int SV_T = 1024;   // threads of the solve kernels: one CTA streams a chain's factor twice, it needs the loads in flight
+// Threads of the solve kernels (template parameter NT): 1024 -- one CTA streams a chain's factor twice, it needs the loads in
+// flight.  A 512-thread form (two CTAs per SM instead of a whole SM per chain) is kept behind BB_SV_SMALL_P (systems up to that
+// size use it) but is off: measured at c5s (P = 256) 181 M draws/s against 187 M with 1024 threads.
+#ifndef BB_SV_SMALL_P
+#define BB_SV_SMALL_P 0
+#endif
+constexpr int SV_SMALL_P = BB_SV_SMALL_P;
 // (x, D, ps are OFFSETS into the dynamic shared memory: handed over as generic pointers the compiler loses the address space
 //  and every access becomes a generic load -- the solve kernel ran 2x slower, 51 -> 111 us at P = 256)
 // W of the NEXT diagonal block travels through registers (4 values per thread): the loads are issued before the work on the
 // current block and stored to shared memory after it, so that their L2 latency is off the chain of dependent blocks.
-struct StblWRegs { double v[4]; };
-__device__ __forceinline__ void stbl_fetch_w(const double* Wg, int kb, int tid, StblWRegs& w) {
+struct StblWRegs { double v[8]; };
+template <int NT> __device__ __forceinline__ void stbl_fetch_w(const double* Wg, int kb, int tid, StblWRegs& w) {
   const double* W = Wg + (size_t)kb * SL_NB * SL_NB;
 #pragma unroll
-  for (int q = 0; q < 4; ++q) w.v[q] = W[tid + q * SV_T];
+  for (int q = 0; q < SL_NB * SL_NB / NT; ++q) w.v[q] = W[tid + q * NT];
 }
-__device__ __forceinline__ void stbl_store_w(int D_off, int tid, const StblWRegs& w) {
+template <int NT> __device__ __forceinline__ void stbl_store_w(int D_off, int tid, const StblWRegs& w) {
   extern __shared__ double smem[];
   double* D = smem + D_off;
 #pragma unroll
-  for (int q = 0; q < 4; ++q) { const int e = tid + q * SV_T; D[(e & (SL_NB - 1)) * (SL_NB + 1) + (e >> 6)] = w.v[q]; }   // W[e] = W(e % 64, e / 64)
+  for (int q = 0; q < SL_NB * SL_NB / NT; ++q) { const int e = tid + q * NT; D[(e & (SL_NB - 1)) * (SL_NB + 1) + (e >> 6)] = w.v[q]; }   // W[e] = W(e % 64, e / 64)
 }
 constexpr int SV_SPLIT_MAXP = 4096;   // up to here the four partial sums of the rows below a block fit in shared memory
 inline size_t stbl_solve_smem(int P) { return ((size_t)P + SL_NB * (SL_NB + 1) + 16 * SL_NB + (P <= SV_SPLIT_MAXP ? 4 * (size_t)P : 0)) * sizeof(double); }
 // Shared-memory layout of the solves (doubles): x [P] | D [64][65] | ps [16][64] | part [4][P].
 // The diagonal blocks are applied as products with their inverses (rows / columns beyond the matrix are zero in W): a 64-term
 // dot product per unknown, all unknowns of the block at once, instead of 64 dependent substitution steps with a division each.
-__device__ __forceinline__ void stbl_forward(const double* A, const double* Wg, int P, int x_off, int D_off, int ps_off, int tid) {
+template <int NT> __device__ __forceinline__ void stbl_forward(const double* A, const double* Wg, int P, int x_off, int D_off, int ps_off, int tid) {
   extern __shared__ double smem[];
   double* x = smem + x_off; double* D = smem + D_off; double* ps = smem + ps_off; double* part = ps + 16 * SL_NB;
-  const int vr = tid & (SL_NB - 1), vp = tid >> 6;     // matrix-vector product: index vr, 16 parts of 4 terms (SV_T = 1024)
-  const int rs = tid & 255, kp = tid >> 8;             // rows below the block: row slot rs, columns 16 kp .. 16 kp + 15
+  constexpr int PT = NT / SL_NB, TQ = SL_NB / PT;      // matrix-vector product: PT parts of TQ terms (16 x 4 at NT = 1024)
+  constexpr int KP = NT / 256, KQ = SL_NB / KP;        // rows below the block: KP column groups of KQ columns (4 x 16 at NT = 1024)
+  const int vr = tid & (SL_NB - 1), vp = tid >> 6;
+  const int rs = tid & 255, kp = tid >> 8;
   StblWRegs wn;
-  stbl_fetch_w(Wg, 0, tid, wn);
+  stbl_fetch_w<NT>(Wg, 0, tid, wn);
   // forward: L w = Xy, column-oriented
   for (int k0 = 0; k0 < P; k0 += SL_NB) {
     const int nb = min(SL_NB, P - k0);
-    stbl_store_w(D_off, tid, wn);
-    if (k0 + SL_NB < P) stbl_fetch_w(Wg, k0 / SL_NB + 1, tid, wn);
+    stbl_store_w<NT>(D_off, tid, wn);
+    if (k0 + SL_NB < P) stbl_fetch_w<NT>(Wg, k0 / SL_NB + 1, tid, wn);
     __syncthreads();
     {   // w_blk = W x_blk
       double s = 0.0;
 #pragma unroll
-      for (int q = 0; q < 4; ++q) { const int c = 4 * vp + q; if (c < nb) s = fma(D[vr * (SL_NB + 1) + c], x[k0 + c], s); }
+      for (int q = 0; q < TQ; ++q) { const int c = TQ * vp + q; if (c < nb) s = fma(D[vr * (SL_NB + 1) + c], x[k0 + c], s); }
       ps[vp * SL_NB + vr] = s;
     }
     __syncthreads();
     if (tid < nb) {
       double s = 0.0;
 #pragma unroll
-      for (int q = 0; q < 16; ++q) s += ps[q * SL_NB + tid];
+      for (int q = 0; q < PT; ++q) s += ps[q * SL_NB + tid];
       x[k0 + tid] = s;
     }
     __syncthreads();
     // rows below: x_r -= sum_k L(r,k) w_k, the 64 columns split over four thread groups (16 loads in flight per thread instead of
     // a chain of 64: with 192 rows at P = 256 only 192 threads worked and the chain of L2 latencies was 5000 cycles per block)
     if (P > SV_SPLIT_MAXP) {   // no room for the partial sums: one thread per row, the 64 columns in sequence
-      for (int r = k0 + nb + tid; r < P; r += SV_T) {
+      for (int r = k0 + nb + tid; r < P; r += NT) {
         double s = x[r];
 #pragma unroll 8
         for (int k = k0; k < k0 + nb; ++k) s = fma(-A[r + (size_t)k * P], x[k], s);
@@ -766,35 +788,41 @@ __device__ __forceinline__ void stbl_forward(const double* A, const double* Wg, 
       continue;
     }
     for (int r = k0 + nb + rs; r < P; r += 256) {
-      const double* ar = A + r + (size_t)(k0 + 16 * kp) * P;
+      const double* ar = A + r + (size_t)(k0 + KQ * kp) * P;
       double s0 = 0.0, s1 = 0.0;
 #pragma unroll
-      for (int q = 0; q < 16; q += 2) {
-        const int c = 16 * kp + q;
+      for (int q = 0; q < KQ; q += 2) {
+        const int c = KQ * kp + q;
         const double a0 = c < nb ? ar[(size_t)q * P] : 0.0, a1 = c + 1 < nb ? ar[(size_t)(q + 1) * P] : 0.0;
         s0 = fma(a0, x[k0 + min(c, nb - 1)], s0); s1 = fma(a1, x[k0 + min(c + 1, nb - 1)], s1);
       }
       part[kp * P + r] = s0 + s1;
     }
     __syncthreads();
-    for (int r = k0 + nb + tid; r < P; r += SV_T) x[r] -= (part[r] + part[P + r]) + (part[2 * P + r] + part[3 * P + r]);
+    for (int r = k0 + nb + tid; r < P; r += NT) {
+      double sum = part[r];
+#pragma unroll
+      for (int g = 1; g < KP; ++g) sum += part[g * P + r];
+      x[r] -= sum;
+    }
     __syncthreads();
   }
 }
-__device__ __forceinline__ void stbl_backward(const double* A, const double* Wg, int P, int x_off, int D_off, int ps_off, int tid) {
+template <int NT> __device__ __forceinline__ void stbl_backward(const double* A, const double* Wg, int P, int x_off, int D_off, int ps_off, int tid) {
   extern __shared__ double smem[];
   double* x = smem + x_off; double* D = smem + D_off; double* ps = smem + ps_off;
   const int vr = tid & (SL_NB - 1), vp = tid >> 6, lane = tid & 31, warp = tid >> 5;
   const int nblk = (P + SL_NB - 1) / SL_NB;
   // backward: L' b = x over the stored lower triangle: column k of L is contiguous, one warp per column, lanes along r
-  double* pk = ps + 15 * SL_NB;     // [64] column sums (the last part of ps is free until the product below)
+  constexpr int PT = NT / SL_NB, TQ = SL_NB / PT;
+  double* pk = ps + (PT - 1) * SL_NB;     // [64] column sums (the last part of ps is free until the product below)
   StblWRegs wn;
-  stbl_fetch_w(Wg, nblk - 1, tid, wn);
+  stbl_fetch_w<NT>(Wg, nblk - 1, tid, wn);
   for (int kbk = nblk - 1; kbk >= 0; --kbk) {
     const int k0 = kbk * SL_NB, nb = min(SL_NB, P - k0);
-    stbl_store_w(D_off, tid, wn);
-    if (kbk > 0) stbl_fetch_w(Wg, kbk - 1, tid, wn);
-    for (int kk = warp; kk < nb; kk += SV_T / 32) {
+    stbl_store_w<NT>(D_off, tid, wn);
+    if (kbk > 0) stbl_fetch_w<NT>(Wg, kbk - 1, tid, wn);
+    for (int kk = warp; kk < nb; kk += NT / 32) {
       const double* col = A + (size_t)(k0 + kk) * P;
       double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
       int r = k0 + nb + lane;
@@ -812,7 +840,7 @@ __device__ __forceinline__ void stbl_backward(const double* A, const double* Wg,
     {   // b_blk = W' x_blk
       double s = 0.0;
 #pragma unroll
-      for (int q = 0; q < 4; ++q) { const int r = 4 * vp + q; if (r < nb) s = fma(D[r * (SL_NB + 1) + vr], x[k0 + r], s); }
+      for (int q = 0; q < TQ; ++q) { const int r = TQ * vp + q; if (r < nb) s = fma(D[r * (SL_NB + 1) + vr], x[k0 + r], s); }
       __syncthreads();               // pk (inside ps) has been read by everyone
       ps[vp * SL_NB + vr] = s;
     }
@@ -820,7 +848,7 @@ __device__ __forceinline__ void stbl_backward(const double* A, const double* Wg,
     if (tid < nb) {
       double s = 0.0;
 #pragma unroll
-      for (int q = 0; q < 16; ++q) s += ps[q * SL_NB + tid];
+      for (int q = 0; q < PT; ++q) s += ps[q * SL_NB + tid];
       x[k0 + tid] = s;
     }
     __syncthreads();
@@ -828,7 +856,7 @@ __device__ __forceinline__ void stbl_backward(const double* A, const double* Wg,
 }
 
 // ---- beta = L^-T (L^-1 Xy + sig eps): one CTA per chain, blocked substitution ----
-__global__ void __launch_bounds__(SV_T) stbl_solve_kernel(const StbLargeLaunch L) {
+template <int NT> __global__ void __launch_bounds__(NT, 1024 / NT) stbl_solve_kernel(const StbLargeLaunch L) {
   extern __shared__ double smem[];
   const int P = L.m.P, tid = threadIdx.x, ch = blockIdx.x;
   if (ch >= L.nchains) return;
@@ -840,18 +868,18 @@ __global__ void __launch_bounds__(SV_T) stbl_solve_kernel(const StbLargeLaunch L
   const uint32_t gch = L.chain0 + (uint32_t)ch, it_ = stbl_iter(L);
   const double sig = sqrt(L.sig2[ch]);
   STBL_MARK(1, 0);
-  for (int j = tid; j < P; j += SV_T) x[j] = __ldg(L.m.Xy + j);
+  for (int j = tid; j < P; j += NT) x[j] = __ldg(L.m.Xy + j);
   const int D_off = P, ps_off = P + SL_NB * (SL_NB + 1);
-  stbl_forward(A, Wg, P, 0, D_off, ps_off, tid);  // w = L^-1 Xy (the reference's first trsm, BridgeRegression.cpp:564)
+  stbl_forward<NT>(A, Wg, P, 0, D_off, ps_off, tid);  // w = L^-1 Xy (the reference's first trsm, BridgeRegression.cpp:564)
   STBL_MARK(1, 1);
-  for (int j = tid; j < P; j += SV_T) { Stream s(L.key, gch, it_, ST_BETA_STB, (uint32_t)j); x[j] = fma(sig, s.norm(0), x[j]); }
+  for (int j = tid; j < P; j += NT) { Stream s(L.key, gch, it_, ST_BETA_STB, (uint32_t)j); x[j] = fma(sig, s.norm(0), x[j]); }
   __syncthreads();
   STBL_MARK(1, 2);
-  stbl_backward(A, Wg, P, 0, D_off, ps_off, tid); // beta = L^-T (w + sig eps)  (:565, :570-574)
+  stbl_backward<NT>(A, Wg, P, 0, D_off, ps_off, tid); // beta = L^-T (w + sig eps)  (:565, :570-574)
   STBL_MARK(1, 3);
   double* beta = L.beta + (size_t)ch * P;
   const long long slot = stbl_slot(L);
-  for (int j = tid; j < P; j += SV_T) {
+  for (int j = tid; j < P; j += NT) {
     beta[j] = x[j];
     if (slot >= 0) {
       const size_t o = ((size_t)ch * L.sink.chain_stride + slot) * P + j;

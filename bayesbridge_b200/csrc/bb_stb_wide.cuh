@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(WG_T) wide_gram_kernel(const StbLargeLaunch L)
 }
 
 // ---- w = M^-1 r (both substitutions with the factor of M), beta = sig (u + D^-1 X' w) : one CTA per chain ----
-__global__ void __launch_bounds__(SV_T) wide_solve_kernel(const StbLargeLaunch L) {
+template <int NT> __global__ void __launch_bounds__(NT, 1024 / NT) wide_solve_kernel(const StbLargeLaunch L) {
   extern __shared__ double smem[];
   const int P = L.m.P, N = L.m.N, tid = threadIdx.x, ch = blockIdx.x;
   if (ch >= L.nchains) return;
@@ -132,9 +132,9 @@ __global__ void __launch_bounds__(SV_T) wide_solve_kernel(const StbLargeLaunch L
   const double* Wg = L.W + (size_t)ch * nblk * SL_NB * SL_NB;
   const int lane = tid & 31, warp = tid >> 5;
   const double* R = L.R + (size_t)ch * N;
-  for (int n = tid; n < N; n += SV_T) x[n] = R[n];
-  stbl_forward(A, Wg, N, 0, N, N + SL_NB * (SL_NB + 1), tid);
-  stbl_backward(A, Wg, N, 0, N, N + SL_NB * (SL_NB + 1), tid);
+  for (int n = tid; n < N; n += NT) x[n] = R[n];
+  stbl_forward<NT>(A, Wg, N, 0, N, N + SL_NB * (SL_NB + 1), tid);
+  stbl_backward<NT>(A, Wg, N, 0, N, N + SL_NB * (SL_NB + 1), tid);
   __syncthreads();
   const double sig2 = L.sig2[ch], tau = L.tau[ch];
   const double f = tau * tau / sig2, sig = sqrt(sig2);
@@ -142,7 +142,7 @@ __global__ void __launch_bounds__(SV_T) wide_solve_kernel(const StbLargeLaunch L
   const double* U = L.U + (size_t)ch * P;
   double* beta = L.beta + (size_t)ch * P;
   const long long slot = stbl_slot(L);
-  for (int k = warp; k < P; k += SV_T / 32) {        // (X' w)_k: column k of X is contiguous, lanes along the rows
+  for (int k = warp; k < P; k += NT / 32) {        // (X' w)_k: column k of X is contiguous, lanes along the rows
     const double* col = L.m.X + (size_t)k * N;
     double s = 0.0;
     for (int n = lane; n < N; n += 32) s = fma(__ldg(col + n), x[n], s);

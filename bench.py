@@ -295,7 +295,7 @@ def kernel_name(method, P):
         return "tri_sweep_kernel"
     if P <= 64:
         return "stb64_kernel"
-    return "stb_small_kernel" if P <= 128 else "stbl_update_kernel (+ potrf / trsm / solve / scalar)"
+    return "stb_small_kernel" if P <= 128 else "stbl_colblock_kernel (+ potrf / solve / scalar / lambda)"
 
 
 def roofline_of(name, method, P, nch, ips, steps, T_local, peaks, N=None):

@@ -21,12 +21,12 @@ int main() {
   for (int rep = 0; rep < 5; ++rep) {
     cudaMemcpy(dA, dA0, A.size() * 8, cudaMemcpyDeviceToDevice);
     cudaEventRecord(e0);
-    stbl_potrf_kernel<<<nch, SL_T, sm>>>(dA, dW, P, 0, st);
+    stbl_potrf_kernel<<<nch, SL_T, sm>>>(dA, dW, P, 0, st, StblSrc{}, 1);
     cudaEventRecord(e1); cudaEventSynchronize(e1);
     float ms; cudaEventElapsedTime(&ms, e0, e1);
-    long long ph[8]; cudaMemcpyFromSymbol(ph, bb_potrf_ph, sizeof(ph));
-    printf("rep %d: %.1f us; cycles load %lld factor %lld scale %lld storeL %lld Wdiag %lld Wstages %lld storeW %lld  (%s)\n", rep, ms * 1e3,
-           ph[1] - ph[0], ph[2] - ph[1], 0LL, ph[3] - ph[2], ph[4] - ph[3], ph[5] - ph[4], ph[6] - ph[5], cudaGetErrorString(cudaGetLastError()));
+    long long ph[12]; cudaMemcpyFromSymbol(ph, bb_potrf_ph, sizeof(ph));
+    printf("rep %d: %.1f us; cycles load %lld factor %lld scale %lld storeL %lld Wdiag %lld Wstages %lld storeW %lld panel: stage %lld mma %lld store %lld  (%s)\n", rep, ms * 1e3,
+           ph[1] - ph[0], ph[2] - ph[1], 0LL, ph[3] - ph[2], ph[4] - ph[3], ph[5] - ph[4], ph[6] - ph[5], ph[8] - ph[6], ph[9] - ph[8], ph[7] - ph[9], cudaGetErrorString(cudaGetLastError()));
   }
   std::vector<double> L(64 * 64); uint32_t s0; cudaMemcpy(&s0, st, 4, cudaMemcpyDeviceToHost);
   cudaMemcpy2D(L.data(), 64 * 8, dA, P * 8, 64 * 8, 64, cudaMemcpyDeviceToHost);

@@ -19,7 +19,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path[:0] = [os.path.join(ROOT, "oracle"), ROOT]
 
-NREP, BURN, NSAMP, ALPHA = 32, 1000, 10001, 0.5
+NREP, BURN, NSAMP, ALPHA = 128, 1000, 10001, 0.5
 
 
 def stats(out):
