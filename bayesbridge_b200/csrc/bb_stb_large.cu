@@ -20,7 +20,7 @@ void stb_large_prepare(int P) {
 
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_trsm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
-  BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_colblock_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
+  BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_colblock_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stbl_colblock_smem()));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_update2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stbl_update2_smem()));
   BB_CUDA_CHECK(cudaFuncSetAttribute(wide_solve_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));
   BB_CUDA_CHECK(cudaFuncSetAttribute(wide_solve_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));   // N <= P there
@@ -53,7 +53,7 @@ static int launch_factor(double* A, double* W, int P, int nch, uint32_t* status,
   int n = 0;
   if (nblk <= SL_FUSED_MAXBLK) {
     for (int kb = 0; kb < nblk; ++kb) {
-      if (kb > 0) { stbl_colblock_kernel<<<dim3(nblk - kb, nch), 256, smem_sy, st>>>(A, W, P, kb, X); ++n; }
+      if (kb > 0) { stbl_colblock_kernel<<<dim3(nblk - kb, nch), 256, stbl_colblock_smem(), st>>>(A, W, P, kb, X); ++n; }
       stbl_potrf_kernel<<<nch, SL_T, stbl_potrf_smem(), st>>>(A, W, P, kb, status, X, 1); ++n;
     }
     return n;

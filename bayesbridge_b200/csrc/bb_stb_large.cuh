@@ -543,6 +543,57 @@ __global__ void __launch_bounds__(256, 2) stbl_update_kernel(double* Aall, int P
     }
 }
 
+// ---- cp.async staging of the colblock kernel: 64 rows x 32 columns of a column-major tile -> smem, k-major [32][SL_LD] ----
+// (LDGSTS: no register staging and no STS instructions on the warps that run the DMMAs; rows beyond the matrix are zero-filled
+//  through the src-size operand.)  V16: 16-byte copies (pairs of rows; needs an even leading dimension), else 8-byte copies.
+#ifndef BB_COLBLOCK_CPASYNC
+#define BB_COLBLOCK_CPASYNC 1
+#endif
+constexpr int CB_KC = 32;                                   // k depth of a stage
+constexpr int CB_STAGE = 2 * CB_KC * SL_LD;                 // doubles per stage: A chunk, then B chunk
+constexpr int CB_NSTAGE = 3;
+inline size_t stbl_colblock_smem() {
+  const size_t full = (size_t)2 * SL_NB * SL_LD * sizeof(double), ring = (size_t)CB_NSTAGE * CB_STAGE * sizeof(double);
+  return BB_COLBLOCK_CPASYNC ? (ring > full ? ring : full) : full;
+}
+template <bool V16> __device__ __forceinline__ void cb_copy_chunk(double* dst, const double* src, int P, int row0, int tid) {
+  // src: element (row0, first column of the chunk) of the tile; dst: [CB_KC][SL_LD]
+  if (V16) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int op = tid + 256 * q, rp = op & 31, k = op >> 5;
+      const int left = P - (row0 + 2 * rp);                 // rows of the matrix from this pair on
+      const int bytes = left >= 2 ? 16 : (left == 1 ? 8 : 0);
+      const double* g = bytes ? src + 2 * rp + (size_t)k * P : src;
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(smem_u32(dst + k * SL_LD + 2 * rp)), "l"(g), "r"(bytes) : "memory");
+    }
+  } else {
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const int op = tid + 256 * q, r = op & 63, k = op >> 6;
+      const int bytes = row0 + r < P ? 8 : 0;
+      const double* g = bytes ? src + r + (size_t)k * P : src;
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" :: "r"(smem_u32(dst + k * SL_LD + r)), "l"(g), "r"(bytes) : "memory");
+    }
+  }
+}
+// acc += A(64 x 32) B(64 x 32)' with the 16 x 32 warp tiles of tile_mma_16x32
+__device__ __forceinline__ void chunk_mma_16x32(const double* As, const double* Bs, double (&acc)[2][4][2], int lane, int warp) {
+  const int r0 = (warp & 3) * 16 + (lane >> 2), c0 = (warp >> 2) * 32 + (lane >> 2);
+#pragma unroll 4
+  for (int kk = 0; kk < CB_KC; kk += 4) {
+    const double* ak = As + (kk + (lane & 3)) * SL_LD;
+    const double* bk = Bs + (kk + (lane & 3)) * SL_LD;
+    const double a0 = ak[r0], a1 = ak[r0 + 8];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const double b = bk[c0 + 8 * t];
+      dmma_m8n8k4(acc[0][t][0], acc[0][t][1], a0, b);
+      dmma_m8n8k4(acc[1][t][0], acc[1][t][1], a1, b);
+    }
+  }
+}
+
 // ---- block column jb >= 1 in ONE kernel (P <= 512): the panel solve of block column jb - 1 and the left-looking update ----
 //   CTA = row tile ti >= jb of one chain:
 //     ti > jb :  L(ti,jb-1) = C(ti,jb-1) W_{jb-1}'            (its own tile of the previous panel, written back as final)
@@ -622,6 +673,34 @@ __global__ void __launch_bounds__(256) stbl_colblock_kernel(double* Aall, const 
 #pragma unroll
   for (int q = 0; q < 16; ++q) Bs[(kq + 4 * q) * SL_LD + r] = pb[q];
   __syncthreads();
+#if BB_COLBLOCK_CPASYNC
+  tile_mma_16x32(As, Bs, acc, lane, warp);
+  __syncthreads();
+  // the finished block columns k < jb - 1 in chunks of 32 columns through a 3-stage cp.async ring: chunk c + 2 is in flight
+  // while chunk c is multiplied, one barrier per chunk, no register staging (the LDG -> STS form ran the DMMA pipe at 71-77 %)
+  {
+    const int nchunk = 2 * kc;
+    const bool v16 = (P & 1) == 0;
+    auto issue = [&](int c) {
+      if (c < nchunk) {
+        double* st = smem + (c % CB_NSTAGE) * CB_STAGE;
+        const size_t col = (size_t)(c >> 1) * SL_NB + (size_t)(c & 1) * CB_KC;
+        if (v16) { cb_copy_chunk<true>(st, A + i0 + col * P, P, i0, tid); cb_copy_chunk<true>(st + CB_KC * SL_LD, A + j0 + col * P, P, j0, tid); }
+        else { cb_copy_chunk<false>(st, A + i0 + col * P, P, i0, tid); cb_copy_chunk<false>(st + CB_KC * SL_LD, A + j0 + col * P, P, j0, tid); }
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");   // (an empty group at the tail keeps the count uniform)
+    };
+    issue(0); issue(1);
+    for (int c = 0; c < nchunk; ++c) {
+      asm volatile("cp.async.wait_group 1;" ::: "memory");   // chunk c has landed (this thread's copies) ...
+      __syncthreads();                                        // ... everyone's; and everyone is done with chunk c - 1
+      issue(c + 2);
+      const double* st = smem + (c % CB_NSTAGE) * CB_STAGE;
+      chunk_mma_16x32(st, st + CB_KC * SL_LD, acc, lane, warp);
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+  }
+#else
   if (kc > 0) fetch(0);
   tile_mma_16x32(As, Bs, acc, lane, warp);
   __syncthreads();
@@ -634,6 +713,7 @@ __global__ void __launch_bounds__(256) stbl_colblock_kernel(double* Aall, const 
     tile_mma_16x32(As, Bs, acc, lane, warp);
     __syncthreads();
   }
+#endif
   const double fdiag = (X.lam && ti == jb) ? X.sig2[ch] / (X.tau[ch] * X.tau[ch]) : 0.0;
 #pragma unroll
   for (int a = 0; a < 2; ++a)
