@@ -7,13 +7,13 @@ from bayesbridge_b200 import synth, _lib
 name = sys.argv[1] if len(sys.argv) > 1 else "c3"
 X, y, _ = synth.make(name)
 N, P = X.shape
-nch, nsamp = (512, 101) if name == "c3" else (256, 21)
+nch, nsamp = {"c3": (512, 101), "c4": (1024, 5), "c2": (512, 201), "c1": (1, 20001)}.get(name, (256, 21))
 method = "triangle" if name in ("c1", "c3", "c5") else "stable"
 Xp = torch.from_numpy(np.asfortranarray(X).T.copy()).pin_memory(); yp = torch.from_numpy(y.copy()).pin_memory()
 beta = torch.empty((nch, nsamp, P), dtype=torch.float64).pin_memory()
 L = _lib.load()
 from bayesbridge_b200._lib import BB_STB, BB_TRI, dp, up
-hyp = bb.make_hyper(alpha=0.5); rt = C.c_double(0); status = np.zeros(nch, dtype=np.uint32)
+hyp = bb.make_hyper(alpha=0.25 if name == "c4" else 0.5); rt = C.c_double(0); status = np.zeros(nch, dtype=np.uint32)
 cast = lambda t: C.cast(t.data_ptr(), dp)
 for s in range(3):
     if s == 2: L.bb_set_verbose(2)
