@@ -21,6 +21,7 @@ void stb_large_prepare(int P) {
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_trsm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_colblock_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stbl_colblock_smem()));
+  BB_CUDA_CHECK(cudaFuncSetAttribute(wide_gram2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wide_gram2_smem()));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_update2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stbl_update2_smem()));
   BB_CUDA_CHECK(cudaFuncSetAttribute(wide_solve_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));
   BB_CUDA_CHECK(cudaFuncSetAttribute(wide_solve_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));   // N <= P there
@@ -105,7 +106,10 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
     // cores, its blocked Cholesky with the kernels below (dimension N), both substitutions and beta = sig (u + D^-1 X'w)
     const int N = L.m.N, nbn = (N + SL_NB - 1) / SL_NB, ntile = nbn * (nbn + 1) / 2;
     wide_draw_kernel<<<nch, 256, (size_t)P * sizeof(double), st>>>(L); ++n;
-    wide_gram_kernel<<<dim3(ntile, nch), WG_T, 0, st>>>(L); ++n;
+    static const bool gram_ldg = std::getenv("BB_WIDE_GRAM_LDG") != nullptr;   // the LDG -> STS form of round 2's first half
+    if (gram_ldg) wide_gram_kernel<<<dim3(ntile, nch), WG_T, 0, st>>>(L);
+    else wide_gram2_kernel<<<dim3(ntile, nch), 256, wide_gram2_smem(), st>>>(L);
+    ++n;
     n += launch_factor(L.A, L.W, N, nch, L.status, StblSrc{}, st);
     if (N <= SV_SMALL_P) wide_solve_kernel<512><<<nch, 512, stbl_solve_smem(N), st>>>(L);
     else wide_solve_kernel<1024><<<nch, 1024, stbl_solve_smem(N), st>>>(L);

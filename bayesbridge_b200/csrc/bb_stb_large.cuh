@@ -556,13 +556,14 @@ inline size_t stbl_colblock_smem() {
   const size_t full = (size_t)2 * SL_NB * SL_LD * sizeof(double), ring = (size_t)CB_NSTAGE * CB_STAGE * sizeof(double);
   return BB_COLBLOCK_CPASYNC ? (ring > full ? ring : full) : full;
 }
-template <bool V16> __device__ __forceinline__ void cb_copy_chunk(double* dst, const double* src, int P, int row0, int tid) {
-  // src: element (row0, first column of the chunk) of the tile; dst: [CB_KC][SL_LD]
+template <bool V16> __device__ __forceinline__ void cb_copy_chunk(double* dst, const double* src, int P, int row0, int tid, int kmax = CB_KC) {
+  // src: element (row0, first column of the chunk) of the tile, leading dimension P, rows < P valid, columns < kmax valid;
+  // dst: [CB_KC][SL_LD]
   if (V16) {
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const int op = tid + 256 * q, rp = op & 31, k = op >> 5;
-      const int left = P - (row0 + 2 * rp);                 // rows of the matrix from this pair on
+      const int left = k < kmax ? P - (row0 + 2 * rp) : 0;  // rows of the matrix from this pair on
       const int bytes = left >= 2 ? 16 : (left == 1 ? 8 : 0);
       const double* g = bytes ? src + 2 * rp + (size_t)k * P : src;
       asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(smem_u32(dst + k * SL_LD + 2 * rp)), "l"(g), "r"(bytes) : "memory");
@@ -571,7 +572,7 @@ template <bool V16> __device__ __forceinline__ void cb_copy_chunk(double* dst, c
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
       const int op = tid + 256 * q, r = op & 63, k = op >> 6;
-      const int bytes = row0 + r < P ? 8 : 0;
+      const int bytes = (row0 + r < P && k < kmax) ? 8 : 0;
       const double* g = bytes ? src + r + (size_t)k * P : src;
       asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" :: "r"(smem_u32(dst + k * SL_LD + r)), "l"(g), "r"(bytes) : "memory");
     }

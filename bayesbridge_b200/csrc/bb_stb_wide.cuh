@@ -121,6 +121,80 @@ __global__ void __launch_bounds__(WG_T) wide_gram_kernel(const StbLargeLaunch L)
     }
 }
 
+// ---- the same product through a 3-stage cp.async ring (round 2, default): 256 threads, 16 x 32 warp tiles, the operands are
+// chunks of 32 columns of X for the 64 rows of both tiles, copied k-major as they lie in memory (rows contiguous) with 16-byte
+// LDGSTS and no register staging; D^-1 is applied to the right-hand fragment on its way into the DMMA instead of to the
+// staged left operand.  One barrier per chunk.  (wide_gram_kernel above: LDG -> scale -> STS staging, two barriers per chunk,
+// FP64 tensor pipe 50 % active.)
+inline size_t wide_gram2_smem() { return (size_t)(CB_NSTAGE * CB_STAGE + CB_NSTAGE * CB_KC) * sizeof(double); }
+__global__ void __launch_bounds__(256, 2) wide_gram2_kernel(const StbLargeLaunch L) {
+  extern __shared__ double smem[];
+  double* dvs = smem + CB_NSTAGE * CB_STAGE;           // [CB_NSTAGE][CB_KC] D^-1 of the chunk's columns
+  const int P = L.m.P, N = L.m.N, ch = blockIdx.y;
+  int tIdx = blockIdx.x, bi = 0;
+  while ((bi + 1) * (bi + 2) / 2 <= tIdx) ++bi;
+  const int bj = tIdx - bi * (bi + 1) / 2;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const double f = L.tau[ch] * L.tau[ch] / L.sig2[ch];
+  const double* lam = L.lambda + (size_t)ch * P;
+  const double* X = L.m.X;
+  const int i0 = bi * SL_NB, j0 = bj * SL_NB;
+  double acc[2][4][2];
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int t = 0; t < 4; ++t) { acc[a][t][0] = 0.0; acc[a][t][1] = 0.0; }
+  const int nchunk = (P + CB_KC - 1) / CB_KC;
+  const bool v16 = (N & 1) == 0;
+  auto issue = [&](int c) {
+    if (c < nchunk) {
+      double* st = smem + (c % CB_NSTAGE) * CB_STAGE;
+      const int col = c * CB_KC, kmax = min(CB_KC, P - col);
+      if (v16) { cb_copy_chunk<true>(st, X + i0 + (size_t)col * N, N, i0, tid, kmax); cb_copy_chunk<true>(st + CB_KC * SL_LD, X + j0 + (size_t)col * N, N, j0, tid, kmax); }
+      else { cb_copy_chunk<false>(st, X + i0 + (size_t)col * N, N, i0, tid, kmax); cb_copy_chunk<false>(st + CB_KC * SL_LD, X + j0 + (size_t)col * N, N, j0, tid, kmax); }
+      if (tid < CB_KC) dvs[(c % CB_NSTAGE) * CB_KC + tid] = tid < kmax ? f / lam[col + tid] : 0.0;
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  issue(0); issue(1);
+  const int r0 = (warp & 3) * 16 + (lane >> 2), c0 = (warp >> 2) * 32 + (lane >> 2);
+  for (int c = 0; c < nchunk; ++c) {
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    __syncthreads();
+    issue(c + 2);
+    const double* As = smem + (c % CB_NSTAGE) * CB_STAGE;
+    const double* Bs = As + CB_KC * SL_LD;
+    const double* dv = dvs + (c % CB_NSTAGE) * CB_KC;
+#pragma unroll 4
+    for (int kk = 0; kk < CB_KC; kk += 4) {
+      const double* ak = As + (kk + (lane & 3)) * SL_LD;
+      const double* bk = Bs + (kk + (lane & 3)) * SL_LD;
+      const double d = dv[kk + (lane & 3)];
+      const double a0 = ak[r0], a1 = ak[r0 + 8];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const double b = bk[c0 + 8 * t] * d;
+        dmma_m8n8k4(acc[0][t][0], acc[0][t][1], a0, b);
+        dmma_m8n8k4(acc[1][t][0], acc[1][t][1], a1, b);
+      }
+    }
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  double* M = L.A + (size_t)ch * N * N;
+  const int wr = (warp & 3) * 16 + (lane >> 2), wc = (warp >> 2) * 32 + 2 * (lane & 3);
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const int r = i0 + wr + 8 * a;
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const int cc = j0 + wc + 8 * t + q;
+        if (r < N && cc < N) M[r + (size_t)cc * N] = acc[a][t][q] + (r == cc ? 1.0 : 0.0);
+      }
+    }
+}
+
 // ---- w = M^-1 r (both substitutions with the factor of M), beta = sig (u + D^-1 X' w) : one CTA per chain ----
 template <int NT> __global__ void __launch_bounds__(NT, 1024 / NT) wide_solve_kernel(const StbLargeLaunch L) {
   extern __shared__ double smem[];
