@@ -121,4 +121,12 @@ __device__ __forceinline__ void dmma_m8n8k4(double& c0, double& c1, double a, do
                : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
+// Programmatic dependent launch (sm_90+): a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may be
+// scheduled while its predecessor in the stream is still running; it must call pdl_wait() before it touches anything the
+// predecessor wrote (the wait returns when the predecessor grid has completed and its writes are visible).  pdl_trigger()
+// tells the scheduler that the NEXT kernel of the stream may be brought onto the SMs now.  Both are no-ops in a kernel that was
+// launched the ordinary way.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 }  // namespace bb

@@ -28,6 +28,23 @@ void stb_large_prepare(int P) {
   if ((size_t)P * sizeof(double) > 48 * 1024) BB_CUDA_CHECK(cudaFuncSetAttribute(wide_draw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((size_t)P * sizeof(double))));
 }
 
+// Launch with programmatic stream serialisation (the kernel calls pdl_wait() before its first dependent read and pdl_trigger()
+// before its last stores): the next kernel of the chain is brought onto the SMs during this one's tail instead of after it has
+// drained -- the P = 256 iteration is a chain of 11 dependent kernels of 20-50 us.  BB_STBL_PDL=0 launches the ordinary way.
+template <typename... KArgs, typename... Args>
+static void launch_chain(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  static const bool pdl = !(std::getenv("BB_STBL_PDL") && std::getenv("BB_STBL_PDL")[0] == '0');
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(st, &cap);
+  cfg.attrs = at; cfg.numAttrs = (pdl && cap == cudaStreamCaptureStatusNone) ? 1 : 0;
+  BB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, KArgs(args)...));
+}
+
 // block column kb > 0 brought up to date by the 64 x 64 kernel.  BB_STBL_TILE128=1: the row tiles below the diagonal tile in
 // pairs by the 128 x 64 kernel instead -- measured SLOWER at c4 (9.8 M against 10.3 M draws/s): its 64 accumulator registers
 // leave no room to keep the next panels' global loads in flight during the tile product, which the 64 x 64 kernel does.
@@ -54,8 +71,8 @@ static int launch_factor(double* A, double* W, int P, int nch, uint32_t* status,
   int n = 0;
   if (nblk <= SL_FUSED_MAXBLK) {
     for (int kb = 0; kb < nblk; ++kb) {
-      if (kb > 0) { stbl_colblock_kernel<<<dim3(nblk - kb, nch), 256, stbl_colblock_smem(), st>>>(A, W, P, kb, X); ++n; }
-      stbl_potrf_kernel<<<nch, SL_T, stbl_potrf_smem(), st>>>(A, W, P, kb, status, X, 1); ++n;
+      if (kb > 0) { launch_chain(stbl_colblock_kernel, dim3(nblk - kb, nch), dim3(256), stbl_colblock_smem(), st, A, W, P, kb, X); ++n; }
+      launch_chain(stbl_potrf_kernel, dim3(nch), dim3(SL_T), stbl_potrf_smem(), st, A, W, P, kb, status, X, 1); ++n;
     }
     return n;
   }
@@ -92,10 +109,10 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
     const int nstrips = (P + QD_R - 1) / QD_R;
     stbl_quad_kernel<<<dim3(nstrips, (nch + 31) / 32), 256, 0, st>>>(L, nstrips); ++n;
   }
-  stbl_scalar_kernel<<<nch, SL_T, smem_sc, st>>>(L); ++n;
+  launch_chain(stbl_scalar_kernel, dim3(nch), dim3(SL_T), smem_sc, st, L); ++n;
   if ((L.stages & 32) && !L.pre) {
     const int nsplit = stbl_lambda_nsplit(P, nch);
-    stbl_lambda_kernel<<<dim3(nsplit, nch), SL_T, stbl_lambda_smem(stbl_lambda_slice(P, nsplit)), st>>>(L, nsplit); ++n;
+    launch_chain(stbl_lambda_kernel, dim3(nsplit, nch), dim3(SL_T), stbl_lambda_smem(stbl_lambda_slice(P, nsplit)), st, L, nsplit); ++n;
   }
   if (L.pre || !beta_stage) {
     if (do_alpha) { stbl_alpha_kernel<<<(nch + 7) / 8, 256, 0, st>>>(L); ++n; }
@@ -124,8 +141,8 @@ int launch_stb_large_iter(StbLargeLaunch& L, bool beta_stage, cudaStream_t st) {
     stbl_build_kernel<<<dim3(64, nch), 256, 0, st>>>(L); ++n;
     n += launch_factor(L.A, L.W, P, nch, L.status, StblSrc{}, st);
   }
-  if (P <= SV_SMALL_P) stbl_solve_kernel<512><<<nch, 512, smem_sv, st>>>(L);
-  else stbl_solve_kernel<1024><<<nch, 1024, smem_sv, st>>>(L);
+  if (P <= SV_SMALL_P) launch_chain(stbl_solve_kernel<512>, dim3(nch), dim3(512), smem_sv, st, L);
+  else launch_chain(stbl_solve_kernel<1024>, dim3(nch), dim3(1024), smem_sv, st, L);
   ++n;
 #ifdef BB_STBL_PHASES
   {

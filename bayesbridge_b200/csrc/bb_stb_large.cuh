@@ -110,6 +110,7 @@ __global__ void __launch_bounds__(SL_T) stbl_scalar_kernel(const StbLargeLaunch 
   double* dl_s = smem;                       // [P] beta - bc
   double* red = dl_s + P;                    // [24]
   double* sc = red + 24;                     // tau, sig2
+  pdl_wait();
   const int ch = blockIdx.x; if (ch >= L.nchains) return;
   STBL_MARK(0, 0);
   const uint32_t gch = L.chain0 + (uint32_t)ch, t = stbl_iter(L);
@@ -164,6 +165,7 @@ __global__ void __launch_bounds__(SL_T) stbl_scalar_kernel(const StbLargeLaunch 
   }
   __syncthreads();
   STBL_MARK(0, 2);
+  pdl_trigger();
   if (tid == 0) { L.tau[ch] = sc[0]; L.sig2[ch] = sc[1]; L.alpha[ch] = alpha; }
   status = __reduce_or_sync(0xffffffffu, status);
   if (lane == 0 && status) atomicOr(L.status + ch, status);
@@ -191,6 +193,7 @@ __global__ void __launch_bounds__(SL_T) stbl_lambda_kernel(const StbLargeLaunch 
   int* qn_s = q_s + 2 * nmax;
   uint32_t* kk_s = reinterpret_cast<uint32_t*>(qn_s + 2);
   if (tid == 0) { qn_s[0] = 0; qn_s[1] = 0; }
+  pdl_wait();
   __syncthreads();
   STBL_MARK(0, 3);
   uint32_t status = 0;
@@ -198,6 +201,7 @@ __global__ void __launch_bounds__(SL_T) stbl_lambda_kernel(const StbLargeLaunch 
   lambda_stage_cta<SL_T>(tid, n, L.beta + (size_t)ch * P + j0, L.lambda + (size_t)ch * P + j0, tau, 0.5 * alpha, L.key,
                          L.chain0 + (uint32_t)ch, stbl_iter(L), rc_s, q_s, nmax, qn_s, kk_s, status, j0);
   STBL_MARK(0, 4);
+  pdl_trigger();
   status = __reduce_or_sync(0xffffffffu, status);
   if (lane == 0 && status) atomicOr(L.status + ch, status);
 }
@@ -302,6 +306,7 @@ __global__ void __launch_bounds__(SL_T, BB_POTRF_MINB) stbl_potrf_kernel(double*
   const bool from_src = X.src != nullptr && kb == 0;  // (later diagonal blocks have been written to A by stbl_colblock_kernel)
   const double* D0 = from_src ? X.src + (size_t)ch * X.stride : A;
   const bool dadd = from_src && X.lam != nullptr;
+  pdl_wait();
   const double fdiag = dadd ? X.sig2[ch] / (X.tau[ch] * X.tau[ch]) : 0.0;
   POTRF_MARK(0);
   const int fr = lane >> 2, fc = 2 * (lane & 3);      // accumulator fragment: row fr, columns fc, fc + 1
@@ -420,6 +425,7 @@ __global__ void __launch_bounds__(SL_T, BB_POTRF_MINB) stbl_potrf_kernel(double*
     __syncthreads();
   }
   POTRF_MARK(5);
+  pdl_trigger();
   double* W = Wall + ((size_t)ch * ((P + SL_NB - 1) / SL_NB) + kb) * SL_NB * SL_NB;   // kept per block column: the solve kernel uses them all
   for (int e = tid; e < SL_NB * SL_NB; e += SL_T) {    // W[e] = W(e % 64, e / 64); rows / columns beyond the matrix are zero
     const int r = e & (SL_NB - 1), c = e >> 6;
@@ -621,6 +627,7 @@ __global__ void __launch_bounds__(256) stbl_colblock_kernel(double* Aall, const 
   const bool ra = i0 + r < P, rb = j0 + r < P;
   const int wr = (warp & 3) * 16 + (lane >> 2), wc = (warp >> 2) * 32 + 2 * (lane & 3);   // fragment: rows wr + 8 a, columns wc + 8 t + {0,1}
   double pa[16], pb[16];
+  pdl_wait();
   // my tile of the previous panel (unsolved) and W_{jb-1}' go first: the solve heads the chain
   if (ti > jb) {
     const double* Cs = (X.src && kc == 0) ? Sm : A;
@@ -715,6 +722,7 @@ __global__ void __launch_bounds__(256) stbl_colblock_kernel(double* Aall, const 
     __syncthreads();
   }
 #endif
+  pdl_trigger();
   const double fdiag = (X.lam && ti == jb) ? X.sig2[ch] / (X.tau[ch] * X.tau[ch]) : 0.0;
 #pragma unroll
   for (int a = 0; a < 2; ++a)
@@ -940,6 +948,7 @@ template <int NT> __device__ __forceinline__ void stbl_backward(const double* A,
 template <int NT> __global__ void __launch_bounds__(NT, 1024 / NT) stbl_solve_kernel(const StbLargeLaunch L) {
   extern __shared__ double smem[];
   const int P = L.m.P, tid = threadIdx.x, ch = blockIdx.x;
+  pdl_wait();
   if (ch >= L.nchains) return;
   double* x = smem;                 // [P]; then D [64][65]: inverse W = L_kk^-1 of the current diagonal block (from stbl_potrf_kernel),
                                     // then ps [16][64]: partial sums of the 64 x 64 matrix-vector products (see stbl_forward)
@@ -958,6 +967,7 @@ template <int NT> __global__ void __launch_bounds__(NT, 1024 / NT) stbl_solve_ke
   STBL_MARK(1, 2);
   stbl_backward<NT>(A, Wg, P, 0, D_off, ps_off, tid); // beta = L^-T (w + sig eps)  (:565, :570-574)
   STBL_MARK(1, 3);
+  pdl_trigger();
   double* beta = L.beta + (size_t)ch * P;
   const long long slot = stbl_slot(L);
   for (int j = tid; j < P; j += NT) {
