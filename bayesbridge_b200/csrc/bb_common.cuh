@@ -126,7 +126,12 @@ __device__ __forceinline__ void dmma_m8n8k4(double& c0, double& c1, double a, do
 // predecessor wrote (the wait returns when the predecessor grid has completed and its writes are visible).  pdl_trigger()
 // tells the scheduler that the NEXT kernel of the stream may be brought onto the SMs now.  Both are no-ops in a kernel that was
 // launched the ordinary way.
+#ifdef BB_PDL_EARLY   // experiment: let the next kernel onto the SMs as soon as this one has started
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { }
+#else
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#endif
 
 }  // namespace bb
