@@ -28,6 +28,9 @@ unsigned long long g_seed = 20121027ULL;
 std::atomic<unsigned> g_scalar_calls{0};   // Philox `iter` word of the stand-alone scalar samplers: one per call since bb_set_seed
 int g_device = 0;
 int g_verbose = 0;
+#ifndef BB_QUAD_MINP
+#define BB_QUAD_MINP 512   // from here on d'X'Xd of the large-P stable path comes from stbl_quad_kernel (all chains of a sub-batch at once)
+#endif
 std::atomic<unsigned> g_scalar_status{0};  // status word (bb::Status bits) of the last stand-alone sampler call
 int g_wide_default = 0;                    // bb_set_wide_gaussian: the drivers opt their chains into BB_OPT_WIDE_GAUSSIAN where it applies
 int (*g_interrupt)(void) = nullptr;        // bb_set_interrupt: polled between chunks of the sampling loop on the calling thread
@@ -396,7 +399,7 @@ void chains_run(bb_chains* c, const bb_hyper* hh, unsigned iter0, int niter, int
     const size_t wblk = ((dimA + 63) / 64) * 64 * 64;
     if (!c->A) {
       c->A = dalloc<double>((size_t)c->nchains * dimA * dimA); c->W = dalloc<double>((size_t)c->nchains * wblk);
-      if (P >= 512 && !c->Q) c->Q = dalloc<double>((size_t)c->nchains * ((P + 31) / 32));
+      if (P >= BB_QUAD_MINP && !c->Q) c->Q = dalloc<double>((size_t)c->nchains * ((P + 31) / 32));
       if (c->wide) { c->U = dalloc<double>((size_t)c->nchains * P); c->R = dalloc<double>((size_t)c->nchains * Nw); }
     }
     // (Q: the batched d'X'Xd kernel pays from P = 512 on; at P = 256 the extra launch costs more than the per-chain loop: c5s 112 -> 109 M)
