@@ -126,19 +126,34 @@ __global__ void __launch_bounds__(SL_T) stbl_scalar_kernel(const StbLargeLaunch 
   for (int k = tid; k < P; k += SL_T) {
     pt += exp(alpha * log(fabs(beta[k])));
     if (do_sig2) {
-      if (L.Q == nullptr) {   // (X'X delta)_k: four partial sums, 16 loads in flight (one dependent chain of P L2 loads took 20 us at P = 256)
-        const double* xk = L.m.XX + k;
-        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-        int j = 0;
-#pragma unroll 4
-        for (; j + 3 < P; j += 4) {
-          s0 = fma(__ldg(xk + (size_t)j * P), dl_s[j], s0); s1 = fma(__ldg(xk + (size_t)(j + 1) * P), dl_s[j + 1], s1);
-          s2 = fma(__ldg(xk + (size_t)(j + 2) * P), dl_s[j + 2], s2); s3 = fma(__ldg(xk + (size_t)(j + 3) * P), dl_s[j + 3], s3);
-        }
-        for (; j < P; ++j) s0 = fma(__ldg(xk + (size_t)j * P), dl_s[j], s0);
-        pq = fma(dl_s[k], (s0 + s1) + (s2 + s3), pq);
-      }
       pg = fma(dl_s[k], __ldg(L.m.gc + k), pg);
+    }
+  }
+  if (do_sig2 && L.Q == nullptr) {
+    // d'X'Xd over the LOWER 32 x 32 tiles of X'X (symmetric: off-diagonal tiles count twice): 36 of 64 tiles at P = 256.  A warp
+    // per tile, lane = row of the tile (coalesced), the 32 columns of the tile in flight at once.  (One thread per row walking
+    // all P columns: 20 us at P = 256 as a single chain of L2 loads, 14 us with 16 loads in flight -- the CTA pulled all 512 KB
+    // of X'X through its SM either way.)
+    const int T = (P + 31) / 32, ntile = T * (T + 1) / 2;
+    for (int t = warp; t < ntile; t += SL_T / 32) {
+      int I = 0;
+      while ((I + 1) * (I + 2) / 2 <= t) ++I;
+      const int J = t - I * (I + 1) / 2;
+      const int row = 32 * I + lane, c0 = 32 * J;
+      const bool rv = row < P;
+      const double* xr = L.m.XX + (rv ? row : 0) + (size_t)c0 * P;
+      double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+      if (c0 + 32 <= P) {
+#pragma unroll
+        for (int c = 0; c < 32; c += 4) {
+          s0 = fma(__ldg(xr + (size_t)c * P), dl_s[c0 + c], s0); s1 = fma(__ldg(xr + (size_t)(c + 1) * P), dl_s[c0 + c + 1], s1);
+          s2 = fma(__ldg(xr + (size_t)(c + 2) * P), dl_s[c0 + c + 2], s2); s3 = fma(__ldg(xr + (size_t)(c + 3) * P), dl_s[c0 + c + 3], s3);
+        }
+      } else {
+        for (int c = 0; c0 + c < P; ++c) s0 = fma(__ldg(xr + (size_t)c * P), dl_s[c0 + c], s0);
+      }
+      const double v = rv ? dl_s[row] * ((s0 + s1) + (s2 + s3)) : 0.0;
+      pq += I == J ? v : 2.0 * v;
     }
   }
   if (do_sig2 && L.Q != nullptr) {   // d'X'Xd from stbl_quad_kernel's per-strip partial sums
