@@ -256,7 +256,7 @@ __device__ unsigned long long bb_lambda_stats[8];
 template <int NT>
 __device__ inline void lambda_stage_cta(const int tid, int P, const double* beta, double* lam_out, double tau, double alpha_half,
                                         const RngKey key, uint32_t gch, uint32_t t, RetConst* rc_s,
-                                        int* q_s, int qld, int* qn_s, uint32_t* kk_s, uint32_t& status, int j0 = 0) {
+                                        int* q_s, int qld, int* qn_s, uint32_t* kk_s, uint32_t& status, int j0 = 0, int gmax = 32) {
   // j0: index of beta[0] / lam_out[0] among the chain's coefficients (a CTA may serve a slice of them): the Philox item of
   // coefficient j is j0 + j, so the draws do not depend on how the coefficients are split over CTAs
   // `tid` = index of the thread among the NT threads that serve THIS chain (a CTA may hold several chains,
@@ -290,7 +290,7 @@ __device__ inline void lambda_stage_cta(const int tid, int P, const double* beta
     if (blockIdx.x == 0 && threadIdx.x == 0) bb_phase_cyc[12] += 1;
 #endif
     int G = 1;
-    while (G < 32 && n_act * (G * 2) <= NT) G *= 2;
+    while (G < gmax && n_act * (G * 2) <= NT) G *= 2;   // gmax < 32: less speculative look-ahead (the draws do not depend on it)
     const int per_pass = NT / G;
     const int sub = tid & (G - 1);
     const int nlvl = rs_levels(G);

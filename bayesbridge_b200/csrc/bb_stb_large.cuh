@@ -194,6 +194,9 @@ __global__ void __launch_bounds__(SL_T) stbl_scalar_kernel(const StbLargeLaunch 
 // once) starts at the first pass.  The draws do not depend on the split (Philox item = coefficient index).
 // The per-coefficient constants (RetConst) are kept in shared memory over the passes when the slice has at most SC_RC_MAXP entries.
 constexpr int SC_RC_MAXP = 1024;
+#ifndef BB_STBL_LAMBDA_GMAX
+#define BB_STBL_LAMBDA_GMAX 32
+#endif
 inline size_t stbl_lambda_smem(int nmax) {
   return (nmax <= SC_RC_MAXP ? (size_t)nmax * sizeof(RetConst) : 0) + ((size_t)3 * nmax + 2) * sizeof(int);
 }
@@ -214,7 +217,7 @@ __global__ void __launch_bounds__(SL_T) stbl_lambda_kernel(const StbLargeLaunch 
   uint32_t status = 0;
   const double tau = L.tau[ch], alpha = L.alpha[ch];      // as left by stbl_scalar_kernel (known values included)
   lambda_stage_cta<SL_T>(tid, n, L.beta + (size_t)ch * P + j0, L.lambda + (size_t)ch * P + j0, tau, 0.5 * alpha, L.key,
-                         L.chain0 + (uint32_t)ch, stbl_iter(L), rc_s, q_s, nmax, qn_s, kk_s, status, j0);
+                         L.chain0 + (uint32_t)ch, stbl_iter(L), rc_s, q_s, nmax, qn_s, kk_s, status, j0, BB_STBL_LAMBDA_GMAX);
   STBL_MARK(0, 4);
   pdl_trigger();
   status = __reduce_or_sync(0xffffffffu, status);
