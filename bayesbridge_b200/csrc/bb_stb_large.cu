@@ -21,6 +21,7 @@ void stb_large_prepare(int P) {
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_trsm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sy));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_colblock_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stbl_colblock_smem()));
+  BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_colblock_v1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stbl_colblock_smem()));
   BB_CUDA_CHECK(cudaFuncSetAttribute(wide_gram2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wide_gram2_smem()));
   BB_CUDA_CHECK(cudaFuncSetAttribute(stbl_update2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stbl_update2_smem()));
   BB_CUDA_CHECK(cudaFuncSetAttribute(wide_solve_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sv));
@@ -71,8 +72,14 @@ static int launch_factor(double* A, double* W, int P, int nch, uint32_t* status,
   int n = 0;
   if (nblk <= SL_FUSED_MAXBLK) {
     for (int kb = 0; kb < nblk; ++kb) {
-      if (kb > 0) { launch_chain(stbl_colblock_kernel, dim3(nblk - kb, nch), dim3(256), stbl_colblock_smem(), st, A, W, P, kb, X); ++n; }
-      launch_chain(stbl_potrf_kernel, dim3(nch), dim3(SL_T), stbl_potrf_smem(), st, A, W, P, kb, status, X, 1); ++n;
+      if (kb > 0) {
+        static const bool v1 = std::getenv("BB_STBL_COLBLOCK_V1") != nullptr;   // the solve-first form, for comparison
+        if (v1) launch_chain(stbl_colblock_v1_kernel, dim3(nblk - kb, nch), dim3(256), stbl_colblock_smem(), st, A, W, P, kb, X);
+        else launch_chain(stbl_colblock_kernel, dim3(nblk - kb, nch), dim3(256), stbl_colblock_smem(), st, A, W, P, kb, X);
+        ++n;
+      }
+      static const int early = (std::getenv("BB_STBL_EARLY") && std::getenv("BB_STBL_EARLY")[0] == '1') ? 2 : 1;   // 2: potrf releases the next colblock kernel at its start
+      launch_chain(stbl_potrf_kernel, dim3(nch), dim3(SL_T), stbl_potrf_smem(), st, A, W, P, kb, status, X, early); ++n;
     }
     return n;
   }

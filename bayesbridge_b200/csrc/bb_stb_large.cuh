@@ -325,6 +325,10 @@ __global__ void __launch_bounds__(SL_T, BB_POTRF_MINB) stbl_potrf_kernel(double*
   const double* D0 = from_src ? X.src + (size_t)ch * X.stride : A;
   const bool dadd = from_src && X.lam != nullptr;
   pdl_wait();
+  // from the fourth block column on the next kernel of the chain is stbl_colblock_kernel with a main loop (>= 6 chunks) that
+  // does not depend on this kernel: let it onto the SMs now (with less of a main loop its CTAs would only wait and hold
+  // registers and shared memory the other sub-batches' kernels need)
+  if (fuse_panel == 2 && k0 + SL_NB < P && kb >= 3) pdl_trigger();
   const double fdiag = dadd ? X.sig2[ch] / (X.tau[ch] * X.tau[ch]) : 0.0;
   POTRF_MARK(0);
   const int fr = lane >> 2, fc = 2 * (lane & 3);      // accumulator fragment: row fr, columns fc, fc + 1
@@ -627,7 +631,7 @@ __device__ __forceinline__ void chunk_mma_16x32(const double* As, const double* 
 // Against stbl_update_kernel + stbl_trsm_kernel (+ stbl_build_kernel): the same arithmetic, one launch per block column
 // instead of two, one pass less over the matrix -- at P = 256 the 64 x 64-tile kernels are bound by their latencies
 // (17 us for one to three tile products of 2 us), so the SM time goes with the number of CTA launches.
-__global__ void __launch_bounds__(256) stbl_colblock_kernel(double* Aall, const double* Wall, int P, int jb, const StblSrc X) {
+__global__ void __launch_bounds__(256) stbl_colblock_v1_kernel(double* Aall, const double* Wall, int P, int jb, const StblSrc X) {
   extern __shared__ double smem[];
   double* As = smem;
   double* Bs = smem + SL_NB * SL_LD;
@@ -740,6 +744,113 @@ __global__ void __launch_bounds__(256) stbl_colblock_kernel(double* Aall, const 
     __syncthreads();
   }
 #endif
+  pdl_trigger();
+  const double fdiag = (X.lam && ti == jb) ? X.sig2[ch] / (X.tau[ch] * X.tau[ch]) : 0.0;
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const int rr = i0 + wr + 8 * a, c = j0 + wc + 8 * t;
+      if (rr < P) {
+#pragma unroll
+        for (int q = 0; q < 2; ++q)
+          if (c + q < P) {
+            double v = Sm[rr + (size_t)(c + q) * P];
+            if (X.lam && rr == c + q) v += X.lam[(size_t)ch * P + rr] * fdiag;
+            A[rr + (size_t)(c + q) * P] = v - acc[a][t][q];
+          }
+      }
+    }
+}
+
+// ---- stbl_colblock_kernel, final form of round 2: the same work in the order  finished block columns -> panel solve -> last term.
+// Everything the ring reads (block columns k <= jb - 2) was complete before stbl_potrf_kernel(jb-1) STARTED, so with
+// programmatic dependent launch this kernel runs its main loop WHILE that potrf kernel (one latency-bound CTA per chain) is still
+// working, and waits for it (pdl_wait) only before it touches W_{jb-1} and L(jb,jb-1).  All operands travel by cp.async (no
+// register staging at all: 126 -> fewer registers live across the solve).  stbl_colblock_v1_kernel above (solve first) is kept
+// for comparison (BB_STBL_COLBLOCK_V1=1).
+__global__ void __launch_bounds__(256) stbl_colblock_kernel(double* Aall, const double* Wall, int P, int jb, const StblSrc X) {
+  extern __shared__ double smem[];
+  double* As = smem;                            // [64][SL_LD] k-major: C(ti,kc), then L(ti,kc)
+  double* Bs = smem + SL_NB * SL_LD;            // [64][SL_LD]: W_kc'
+  double* T3 = smem + 2 * SL_NB * SL_LD;        // [64][SL_LD]: L(jb,kc)   (the three tiles fill the ring's 3 stages exactly)
+  const int ch = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double* A = Aall + (size_t)ch * P * P;
+  const double* Sm = X.src ? X.src + (size_t)ch * X.stride : A;
+  const int ti = jb + blockIdx.x;
+  const int i0 = ti * SL_NB, j0 = jb * SL_NB, kc = jb - 1, c0 = kc * SL_NB;
+  const int wr = (warp & 3) * 16 + (lane >> 2), wc = (warp >> 2) * 32 + 2 * (lane & 3);   // fragment: rows wr + 8 a, columns wc + 8 t + {0,1}
+  const bool v16 = (P & 1) == 0;
+  double acc[2][4][2];
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int t = 0; t < 4; ++t) { acc[a][t][0] = 0.0; acc[a][t][1] = 0.0; }
+  // ---- the finished block columns k < jb - 1: 32-column chunks through the 3-stage cp.async ring ----
+  {
+    const int nchunk = 2 * kc;
+    auto issue = [&](int c) {
+      if (c < nchunk) {
+        double* st = smem + (c % CB_NSTAGE) * CB_STAGE;
+        const size_t col = (size_t)(c >> 1) * SL_NB + (size_t)(c & 1) * CB_KC;
+        if (v16) { cb_copy_chunk<true>(st, A + i0 + col * P, P, i0, tid); cb_copy_chunk<true>(st + CB_KC * SL_LD, A + j0 + col * P, P, j0, tid); }
+        else { cb_copy_chunk<false>(st, A + i0 + col * P, P, i0, tid); cb_copy_chunk<false>(st + CB_KC * SL_LD, A + j0 + col * P, P, j0, tid); }
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");   // (an empty group at the tail keeps the count uniform)
+    };
+    issue(0); issue(1);
+    for (int c = 0; c < nchunk; ++c) {
+      asm volatile("cp.async.wait_group 1;" ::: "memory");   // chunk c has landed (this thread's copies) ...
+      __syncthreads();                                        // ... everyone's; and everyone is done with chunk c - 1
+      issue(c + 2);
+      const double* st = smem + (c % CB_NSTAGE) * CB_STAGE;
+      chunk_mma_16x32(st, st + CB_KC * SL_LD, acc, lane, warp);
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();                                          // the ring's stages are free: they are reused as As / Bs / T3
+  }
+  // ---- block column kc = jb - 1: needs the potrf kernel of that block column ----
+  pdl_wait();
+  if (v16) { cb_copy_chunk<true>(T3, A + j0 + (size_t)c0 * P, P, j0, tid); cb_copy_chunk<true>(T3 + CB_KC * SL_LD, A + j0 + (size_t)(c0 + CB_KC) * P, P, j0, tid); }
+  else { cb_copy_chunk<false>(T3, A + j0 + (size_t)c0 * P, P, j0, tid); cb_copy_chunk<false>(T3 + CB_KC * SL_LD, A + j0 + (size_t)(c0 + CB_KC) * P, P, j0, tid); }
+  if (ti > jb) {
+    const double* Cs = ((X.src && kc == 0) ? Sm : A) + i0 + (size_t)c0 * P;
+    const double* W = Wall + ((size_t)ch * ((P + SL_NB - 1) / SL_NB) + kc) * SL_NB * SL_NB;
+    if (v16) { cb_copy_chunk<true>(As, Cs, P, i0, tid); cb_copy_chunk<true>(As + CB_KC * SL_LD, Cs + (size_t)CB_KC * P, P, i0, tid); }
+    else { cb_copy_chunk<false>(As, Cs, P, i0, tid); cb_copy_chunk<false>(As + CB_KC * SL_LD, Cs + (size_t)CB_KC * P, P, i0, tid); }
+    // W is a full 64 x 64 block, column-major with leading dimension 64: Bs[k][c] = W(c,k) = W[c + 64 k]
+    // (cb_copy_chunk's leading dimension and row limit are one parameter: a second call with the pointer advanced covers k >= 32)
+    cb_copy_chunk<true>(Bs, W, SL_NB, 0, tid); cb_copy_chunk<true>(Bs + CB_KC * SL_LD, W + CB_KC * SL_NB, SL_NB, 0, tid);
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
+  if (ti > jb) {
+    double dn[2][4][2];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int t = 0; t < 4; ++t) { dn[a][t][0] = 0.0; dn[a][t][1] = 0.0; }
+    tile_mma_16x32(As, Bs, dn, lane, warp);            // L(ti,kc) = C(ti,kc) W'
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const int rr = i0 + wr + 8 * a, c = c0 + wc + 8 * t;
+        if (rr < P) { A[rr + (size_t)c * P] = dn[a][t][0]; A[rr + (size_t)(c + 1) * P] = dn[a][t][1]; }
+      }
+    __syncthreads();                                   // everyone is done with C in As
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        As[(wc + 8 * t) * SL_LD + wr + 8 * a] = dn[a][t][0]; As[(wc + 8 * t + 1) * SL_LD + wr + 8 * a] = dn[a][t][1];
+      }
+    __syncthreads();
+    tile_mma_16x32(As, T3, acc, lane, warp);           // += L(ti,kc) L(jb,kc)'
+  } else {
+    tile_mma_16x32(T3, T3, acc, lane, warp);
+  }
   pdl_trigger();
   const double fdiag = (X.lam && ti == jb) ? X.sig2[ch] / (X.tau[ch] * X.tau[ch]) : 0.0;
 #pragma unroll
