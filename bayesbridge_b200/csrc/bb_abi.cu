@@ -414,6 +414,9 @@ void chains_run(bb_chains* c, const bb_hyper* hh, unsigned iter0, int niter, int
     // are independent chains, so they only meet again at the end of the call.  BB_STBL_SPLIT overrides the count (1..4).
     static const int split_env = std::getenv("BB_STBL_SPLIT") ? std::atoi(std::getenv("BB_STBL_SPLIT")) : 0;
     int nsub = c->nchains >= 64 ? 4 : (c->nchains >= 16 ? 2 : 1);   // measured: c4 (128 chains) 9.2 -> 9.4 M, c5s (256 chains) 68.6 -> 71.5 M draws/s from 2 to 4
+    // short systems (P <= 512: an iteration is a chain of latency-bound 64-CTA kernels): six sub-batches fill the SMs better
+    // (end of round 2, c5s: 4 / 5 / 6 / 8 sub-batches = 198 / 199 / 201 / 200 M draws/s; c4 wide, N = 500: 6 and 8 lost 2 %)
+    if (!c->wide && P <= 512 && c->nchains >= 96) nsub = 6;
     if (split_env >= 1 && split_env <= 8) nsub = std::min(split_env, c->nchains);
     if (nsub > 1 && !c->ev_fork) BB_CUDA_CHECK(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     for (int i = 0; i + 1 < nsub; ++i)
