@@ -528,9 +528,14 @@ __device__ __forceinline__ void bj_block_pair(double* __restrict__ W, double* __
   // Thread (i,j) needs the rotations of the pairs holding i and j: it computes both itself from the current copy of G
   // (two independent straight-line chains) instead of waiting for 8 threads to publish them: ONE barrier per inner round.
   const int r0 = within ? 0 : BJ_CROSS0;
-  for (int r = r0; r < BJ_N - 1; ++r) {
-    const double (*G)[BJ_N + 1] = sm.G[(r - r0) & 1];
-    const double (*Jc)[BJ_N + 1] = sm.Jm[(r - r0) & 1];
+#ifndef BJ_INNER_PASSES
+#define BJ_INNER_PASSES 1      // cyclic sweeps over the 16 x 16 Gram block per visit (2: measured in DESIGN 4.5)
+#endif
+  int step = 0;
+  for (int pass = 0; pass < BJ_INNER_PASSES; ++pass)
+  for (int r = r0; r < BJ_N - 1; ++r, ++step) {
+    const double (*G)[BJ_N + 1] = sm.G[step & 1];
+    const double (*Jc)[BJ_N + 1] = sm.Jm[step & 1];
     const int pl = sm.partner[r][lo_], ph = sm.partner[r][hi_];
     double cl, sl, ch, sh;
     {
@@ -547,12 +552,12 @@ __device__ __forceinline__ void bj_block_pair(double* __restrict__ W, double* __
     const int pj = j == lo_ ? pl : ph;
     const double cj = j == lo_ ? cl : ch, sj = j == lo_ ? sl : sh;
     const double jn = cj * Jc[i][j] + sj * Jc[i][pj];
-    sm.G[(r - r0 + 1) & 1][i][j] = gn; sm.Jm[(r - r0 + 1) & 1][i][j] = jn;
+    sm.G[(step + 1) & 1][i][j] = gn; sm.Jm[(step + 1) & 1][i][j] = jn;
     __syncthreads();
   }
   BJ_MARK(2);
   // ---- 3. B <- B J, V <- V J ----
-  const int buf = (BJ_N - 1 - r0) & 1;
+  const int buf = step & 1;
   bj_apply(W, M, M, P, I, J, sm, buf);
   if (V != nullptr) bj_apply(V, P, P, P, I, J, sm, buf);
   BJ_MARK(3);
